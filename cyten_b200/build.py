@@ -1,0 +1,57 @@
+"""Builds ``cyten_b200/libcyten_b200.so`` (the C-ABI library of include/cyten_b200.h) in-tree.
+
+nvcc cross-compiles for sm_100a without a GPU; the resulting .so is git-ignored but travels to the
+GPU box with the gpurun snapshot.  Usage: ``python -m cyten_b200.build [--force]``.
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+from pathlib import Path
+
+HERE = Path(__file__).resolve().parent
+CSRC = HERE / "csrc"
+OBJ = CSRC / "_obj"
+LIB = HERE / "libcyten_b200.so"
+SOURCES = ["core", "bookkeeping", "copy_blocks", "grouped_gemm", "factorize", "truncate"]
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+         "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default"]
+
+
+def _stale(target: Path, deps: list[Path]) -> bool:
+    if not target.exists():
+        return True
+    t = target.stat().st_mtime
+    return any(d.stat().st_mtime > t for d in deps)
+
+
+def build(force: bool = False, verbose: bool = False) -> Path:
+    OBJ.mkdir(exist_ok=True)
+    common = [CSRC / "common.cuh", HERE.parent / "include" / "cyten_b200.h"]
+    jobs = []
+    for name in SOURCES:
+        src, obj = CSRC / f"{name}.cu", OBJ / f"{name}.o"
+        if force or _stale(obj, [src, *common]):
+            jobs.append([NVCC, *FLAGS, *(["-Xptxas", "-v"] if verbose else []), "-c", str(src), "-o", str(obj)])
+
+    def run(cmd):
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"{' '.join(cmd)}\n{r.stdout}\n{r.stderr}")
+        return r.stderr
+
+    with ThreadPoolExecutor(max_workers=min(8, max(1, len(jobs)))) as ex:
+        for out in ex.map(run, jobs):
+            if verbose and out:
+                print(out)
+    objs = [OBJ / f"{n}.o" for n in SOURCES]
+    if force or jobs or _stale(LIB, objs):
+        run([NVCC, "-shared", "-o", str(LIB), *map(str, objs), "-lcudart"])
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -1,0 +1,366 @@
+// (a6) grouped per-sector contraction GEMMs on the FP64 tensor pipe.
+//
+//   C_t (M_t x N_t) = sum_{p in pairs(t)} A_p (M_t x K_p) * B_p (K_p x N_t)      (all row-major)
+//
+// replaces the matrix_dot / operator+ loop of abelian_compose_worker
+// (src/backends/abelian.cpp:1424-1450; NumpyBlockBackend::matrix_dot = np.dot, numpy.cpp:1219-1225).
+//
+// Blackwell has no f64 kind on tcgen05, so float64 / complex128 run on warp-level DMMA: on sm_100a
+// every mma.sync f64 shape lowers to DMMA.8x8x4 (checked with cuobjdump), which is what is issued
+// here directly.  One persistent CTA per SM pulls output tiles from a device work list (largest
+// block first, atomic ticket), and for each tile walks the FLATTENED k-loop over all matched
+// (A,B) block pairs of that output block: the sum over pairs is accumulated in registers, there is
+// no operator+ pass and no intermediate block.  Operands are staged global->shared with a
+// multi-stage cp.async pipeline (zero-filled at ragged edges; 16-byte copies when the leading
+// dimension is even, 8-byte otherwise -- blocks have arbitrary odd extents, so TMA tensor maps do
+// not apply), shared-memory rows are padded so every fragment load is bank-conflict free.
+// complex128 = 4 real DMMAs per fragment pair on split re/im accumulators.
+#include "common.cuh"
+
+namespace cyb {
+
+__device__ __forceinline__ void cp_async_8(void* smem, const void* g, bool pred)
+{
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    const int sz = pred ? 8 : 0;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" ::"r"(s), "l"(g), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_16(void* smem, const void* g, bool pred)
+{
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    const int sz = pred ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(s), "l"(g), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b)
+{
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+__device__ __forceinline__ double neg_bits(double x)
+{
+    return __longlong_as_double(__double_as_longlong(x) ^ (long long)0x8000000000000000ull);
+}
+
+struct GemmTables {
+    const int64_t* out_mn;        // [nblocks][2]
+    const int64_t* out_off;       // [nblocks]
+    const int64_t* out_pair_ptr;  // [nblocks + 1]
+    const int64_t* pairs;         // [npairs][3] = (a_off, b_off, K)
+    const int64_t* order;         // [nblocks] processing order (largest first)
+    const int64_t* tile_start;    // [nblocks + 1] prefix of tile counts in `order`
+    unsigned long long* ticket;   // dynamic tile counter
+    int64_t nblocks;
+};
+
+// single CTA: cost-sorted processing order, tile prefix, ticket reset
+template <int BM, int BN>
+__global__ void __launch_bounds__(1024) gemm_schedule_kernel(const int64_t* __restrict__ out_mn,
+                                                             const int64_t* __restrict__ out_pair_ptr,
+                                                             const int64_t* __restrict__ pairs,
+                                                             const int64_t* __restrict__ subset,
+                                                             int64_t nblocks, double* __restrict__ cost,
+                                                             int64_t* __restrict__ order,
+                                                             int64_t* __restrict__ tile_start,
+                                                             unsigned long long* __restrict__ ticket)
+{
+    __shared__ int64_t s_scan[33];
+    const int tid = threadIdx.x;
+    for (int64_t i = tid; i < nblocks; i += 1024) {
+        const int64_t blk = subset ? subset[i] : i;
+        double ksum = 0;
+        for (int64_t q = out_pair_ptr[blk]; q < out_pair_ptr[blk + 1]; ++q) ksum += (double)pairs[3 * q + 2];
+        const int64_t tm = (out_mn[2 * blk] + BM - 1) / BM, tn = (out_mn[2 * blk + 1] + BN - 1) / BN;
+        // per-tile cost decides the order (long k-loops first), ties keep table order
+        cost[i] = (tm * tn > 0) ? ksum : -1.0;
+    }
+    __syncthreads();
+    for (int64_t i = tid; i < nblocks; i += 1024) {
+        const double ci = cost[i];
+        int64_t rank = 0;
+        for (int64_t j = 0; j < nblocks; ++j) {
+            const double cj = cost[j];
+            rank += (cj > ci) || (cj == ci && j < i);
+        }
+        order[rank] = subset ? subset[i] : i;
+    }
+    __syncthreads();
+    int64_t carry = 0;
+    for (int64_t base = 0; base < nblocks; base += 1024) {
+        const int64_t i = base + tid;
+        int64_t v = 0;
+        if (i < nblocks) {
+            const int64_t blk = order[i];
+            v = ((out_mn[2 * blk] + BM - 1) / BM) * ((out_mn[2 * blk + 1] + BN - 1) / BN);
+        }
+        int64_t total;
+        int64_t pos = block_exclusive_scan<int64_t>(v, s_scan, &total);
+        if (i < nblocks) tile_start[i] = carry + pos;
+        carry += total;
+    }
+    if (tid == 0) { tile_start[nblocks] = carry; *ticket = 0ull; }
+}
+
+template <bool CPLX, int BM_, int BN_, int BK_, int WARPS_M_, int WARPS_N_, int STAGES_>
+struct GemmCfg {
+    static constexpr bool cplx = CPLX;
+    static constexpr int BM = BM_, BN = BN_, BK = BK_, WARPS_M = WARPS_M_, WARPS_N = WARPS_N_, STAGES = STAGES_;
+    static constexpr int THREADS = WARPS_M * WARPS_N * 32;
+    static constexpr int WM = BM / WARPS_M, WN = BN / WARPS_N;
+    static constexpr int MI = WM / 8, NI = WN / 8;
+    static constexpr int ES = CPLX ? 2 : 1;                 // doubles per element
+    // row strides in ELEMENTS; bank-conflict-free fragment loads need
+    //   real:    lda = 4 (mod 16) doubles,  ldb = 4 (mod 16)
+    //   complex: lda = 4 (mod 8) elements,  ldb = 2 (mod 8)
+    static constexpr int LDA = BK + 4;
+    static constexpr int LDB = CPLX ? BN + 2 : BN + 4;
+    static constexpr int A_STAGE = BM * LDA * ES;           // doubles
+    static constexpr int B_STAGE = BK * LDB * ES;           // doubles
+    static constexpr size_t SMEM = (size_t)STAGES * (A_STAGE + B_STAGE) * sizeof(double);
+    static_assert(BK % 4 == 0 && WM % 8 == 0 && WN % 8 == 0, "tile shape");
+    static_assert(CPLX ? (LDA % 8 == 4 && LDB % 8 == 2) : (LDA % 16 == 4 && LDB % 16 == 4), "padding");
+};
+
+template <class Cfg>
+__global__ void __launch_bounds__(Cfg::THREADS, 1)
+grouped_gemm_kernel(const double* __restrict__ A, const double* __restrict__ B, double* __restrict__ C,
+                    GemmTables T)
+{
+    constexpr int BM = Cfg::BM, BN = Cfg::BN, BK = Cfg::BK, STAGES = Cfg::STAGES;
+    constexpr int ES = Cfg::ES, LDA = Cfg::LDA, LDB = Cfg::LDB, MI = Cfg::MI, NI = Cfg::NI;
+    constexpr int THREADS = Cfg::THREADS;
+    constexpr bool CPLX = Cfg::cplx;
+    extern __shared__ __align__(16) double smem[];
+    double* sA = smem;
+    double* sB = smem + (size_t)STAGES * Cfg::A_STAGE;
+    __shared__ long long s_tile;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wm0 = (warp / Cfg::WARPS_N) * Cfg::WM, wn0 = (warp % Cfg::WARPS_N) * Cfg::WN;
+    const int lr = lane >> 2, lc = lane & 3;
+    const int64_t total_tiles = T.tile_start[T.nblocks];
+
+    for (;;) {
+        __syncthreads();
+        if (tid == 0) s_tile = (long long)atomicAdd(T.ticket, 1ull);
+        __syncthreads();
+        const int64_t tile = s_tile;
+        if (tile >= total_tiles) break;
+        // locate the output block of this tile
+        int64_t lo = 0, hi = T.nblocks;
+        while (hi - lo > 1) {
+            const int64_t mid = (lo + hi) >> 1;
+            if (T.tile_start[mid] <= tile) lo = mid; else hi = mid;
+        }
+        const int64_t blk = T.order[lo];
+        const int64_t M = T.out_mn[2 * blk], N = T.out_mn[2 * blk + 1];
+        const int64_t tiles_n = (N + BN - 1) / BN;
+        const int64_t local = tile - T.tile_start[lo];
+        const int64_t m0 = (local / tiles_n) * BM, n0 = (local % tiles_n) * BN;
+        const int64_t p_begin = T.out_pair_ptr[blk], p_end = T.out_pair_ptr[blk + 1];
+        int64_t n_iters = 0;
+        for (int64_t p = p_begin; p < p_end; ++p) n_iters += (T.pairs[3 * p + 2] + BK - 1) / BK;
+
+        // ---- loader state (flattened over pairs x k-chunks) ----
+        int64_t ld_p = p_begin, ld_k = 0;
+        int64_t ld_aoff = 0, ld_boff = 0, ld_K = 0;
+        if (ld_p < p_end) { ld_aoff = T.pairs[3 * ld_p]; ld_boff = T.pairs[3 * ld_p + 1]; ld_K = T.pairs[3 * ld_p + 2]; }
+        const bool vecB = (N % 2 == 0) || CPLX;
+
+        auto issue_load = [&](int stage) {
+            if (ld_p < p_end) {
+                double* dA = sA + (size_t)stage * Cfg::A_STAGE;
+                double* dB = sB + (size_t)stage * Cfg::B_STAGE;
+                const int64_t K = ld_K, k0 = ld_k;
+                const double* gA = A + (ld_aoff + m0 * K + k0) * ES;   // element (m0, k0)
+                const double* gB = B + (ld_boff + k0 * N + n0) * ES;   // element (k0, n0)
+                if (CPLX) {
+                    // one complex element = 16 bytes, always aligned
+                    for (int c = tid; c < BM * BK; c += THREADS) {
+                        const int r = c / BK, k = c % BK;
+                        const bool ok = (m0 + r < M) && (k0 + k < K);
+                        cp_async_16(dA + ((size_t)r * LDA + k) * 2, ok ? gA + ((int64_t)r * K + k) * 2 : A, ok);
+                    }
+                    for (int c = tid; c < BK * BN; c += THREADS) {
+                        const int k = c / BN, n = c % BN;
+                        const bool ok = (k0 + k < K) && (n0 + n < N);
+                        cp_async_16(dB + ((size_t)k * LDB + n) * 2, ok ? gB + ((int64_t)k * N + n) * 2 : B, ok);
+                    }
+                } else {
+                    if ((K & 1) == 0) {
+                        for (int c = tid; c < BM * (BK / 2); c += THREADS) {
+                            const int r = c / (BK / 2), k = (c % (BK / 2)) * 2;
+                            const bool ok = (m0 + r < M) && (k0 + k < K);
+                            cp_async_16(dA + (size_t)r * LDA + k, ok ? gA + (int64_t)r * K + k : A, ok);
+                        }
+                    } else {
+                        for (int c = tid; c < BM * BK; c += THREADS) {
+                            const int r = c / BK, k = c % BK;
+                            const bool ok = (m0 + r < M) && (k0 + k < K);
+                            cp_async_8(dA + (size_t)r * LDA + k, ok ? gA + (int64_t)r * K + k : A, ok);
+                        }
+                    }
+                    if (vecB) {
+                        for (int c = tid; c < BK * (BN / 2); c += THREADS) {
+                            const int k = c / (BN / 2), n = (c % (BN / 2)) * 2;
+                            const bool ok = (k0 + k < K) && (n0 + n < N);
+                            cp_async_16(dB + (size_t)k * LDB + n, ok ? gB + (int64_t)k * N + n : B, ok);
+                        }
+                    } else {
+                        for (int c = tid; c < BK * BN; c += THREADS) {
+                            const int k = c / BN, n = c % BN;
+                            const bool ok = (k0 + k < K) && (n0 + n < N);
+                            cp_async_8(dB + (size_t)k * LDB + n, ok ? gB + (int64_t)k * N + n : B, ok);
+                        }
+                    }
+                }
+                ld_k += BK;
+                if (ld_k >= K) {
+                    ++ld_p; ld_k = 0;
+                    if (ld_p < p_end) { ld_aoff = T.pairs[3 * ld_p]; ld_boff = T.pairs[3 * ld_p + 1]; ld_K = T.pairs[3 * ld_p + 2]; }
+                }
+            }
+            cp_async_commit();
+        };
+
+        // accumulators: real [MI][NI][2]; complex re and im planes
+        double acc[CPLX ? 2 : 1][MI][NI][2];
+#pragma unroll
+        for (int z = 0; z < (CPLX ? 2 : 1); ++z)
+#pragma unroll
+            for (int i = 0; i < MI; ++i)
+#pragma unroll
+                for (int j = 0; j < NI; ++j) { acc[z][i][j][0] = 0.0; acc[z][i][j][1] = 0.0; }
+
+#pragma unroll
+        for (int s = 0; s < STAGES - 1; ++s) issue_load(s);
+
+        for (int64_t it = 0; it < n_iters; ++it) {
+            cp_async_wait<STAGES - 2>();
+            __syncthreads();
+            issue_load((int)((it + STAGES - 1) % STAGES));
+            const int stage = (int)(it % STAGES);
+            const double* tA = sA + (size_t)stage * Cfg::A_STAGE;
+            const double* tB = sB + (size_t)stage * Cfg::B_STAGE;
+#pragma unroll
+            for (int kk = 0; kk < BK; kk += 4) {
+                if (!CPLX) {
+                    double a[MI], b[NI];
+#pragma unroll
+                    for (int i = 0; i < MI; ++i) a[i] = tA[(size_t)(wm0 + i * 8 + lr) * LDA + kk + lc];
+#pragma unroll
+                    for (int j = 0; j < NI; ++j) b[j] = tB[(size_t)(kk + lc) * LDB + wn0 + j * 8 + lr];
+#pragma unroll
+                    for (int i = 0; i < MI; ++i)
+#pragma unroll
+                        for (int j = 0; j < NI; ++j) dmma884(acc[0][i][j][0], acc[0][i][j][1], a[i], b[j]);
+                } else {
+                    double2 a[MI], b[NI];
+#pragma unroll
+                    for (int i = 0; i < MI; ++i)
+                        a[i] = *reinterpret_cast<const double2*>(tA + ((size_t)(wm0 + i * 8 + lr) * LDA + kk + lc) * 2);
+#pragma unroll
+                    for (int j = 0; j < NI; ++j)
+                        b[j] = *reinterpret_cast<const double2*>(tB + ((size_t)(kk + lc) * LDB + wn0 + j * 8 + lr) * 2);
+#pragma unroll
+                    for (int i = 0; i < MI; ++i) {
+                        const double nai = neg_bits(a[i].y);
+#pragma unroll
+                        for (int j = 0; j < NI; ++j) {
+                            dmma884(acc[0][i][j][0], acc[0][i][j][1], a[i].x, b[j].x);
+                            dmma884(acc[0][i][j][0], acc[0][i][j][1], nai, b[j].y);
+                            dmma884(acc[CPLX ? 1 : 0][i][j][0], acc[CPLX ? 1 : 0][i][j][1], a[i].x, b[j].y);
+                            dmma884(acc[CPLX ? 1 : 0][i][j][0], acc[CPLX ? 1 : 0][i][j][1], a[i].y, b[j].x);
+                        }
+                    }
+                }
+            }
+        }
+        cp_async_wait<0>();
+
+        // ---- epilogue: registers -> global ----
+        double* Cb = C + T.out_off[blk] * ES;
+#pragma unroll
+        for (int i = 0; i < MI; ++i) {
+            const int64_t r = m0 + wm0 + i * 8 + lr;
+            if (r >= M) continue;
+#pragma unroll
+            for (int j = 0; j < NI; ++j) {
+                const int64_t c = n0 + wn0 + j * 8 + lc * 2;
+                if (!CPLX) {
+                    double* p = Cb + r * N + c;
+                    if (c + 1 < N && ((N & 1) == 0)) {
+                        *reinterpret_cast<double2*>(p) = make_double2(acc[0][i][j][0], acc[0][i][j][1]);
+                    } else {
+                        if (c < N) p[0] = acc[0][i][j][0];
+                        if (c + 1 < N) p[1] = acc[0][i][j][1];
+                    }
+                } else {
+                    double* p = Cb + (r * N + c) * 2;
+                    if (c < N) *reinterpret_cast<double2*>(p) = make_double2(acc[0][i][j][0], acc[CPLX ? 1 : 0][i][j][0]);
+                    if (c + 1 < N) *reinterpret_cast<double2*>(p + 2) = make_double2(acc[0][i][j][1], acc[CPLX ? 1 : 0][i][j][1]);
+                }
+            }
+        }
+    }
+}
+
+using CfgR = GemmCfg<false, 128, 128, 16, 2, 4, 4>;   // 8 warps, warp tile 64x32, 4-stage pipeline
+using CfgC = GemmCfg<true, 128, 64, 8, 4, 2, 4>;      // 8 warps, warp tile 32x32 complex
+
+template <class Cfg>
+static int launch_gemm(const void* a, const void* b, void* c, GemmTables T, cudaStream_t stream)
+{
+    static bool configured = false;
+    if (!configured) {
+        CYB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+        configured = true;
+    }
+    grouped_gemm_kernel<Cfg><<<sm_count(), Cfg::THREADS, Cfg::SMEM, stream>>>(
+        static_cast<const double*>(a), static_cast<const double*>(b), static_cast<double*>(c), T);
+    CYB_LAUNCH_CHECK();
+    return CYB_OK;
+}
+
+}  // namespace cyb
+
+using namespace cyb;
+
+extern "C" {
+
+int cyb_grouped_gemm(const void* a, const void* b, void* c, int dtype, const int64_t* out_mn,
+                     const int64_t* out_off, const int64_t* out_pair_ptr, const int64_t* pairs,
+                     const int64_t* block_subset, int64_t nblocks,
+                     cyb_stream_t stream_)
+{
+
+    CYB_REQUIRE(dtype == CYB_F64 || dtype == CYB_C128, "grouped_gemm: bad dtype %d", dtype);
+    CYB_REQUIRE(nblocks >= 0, "grouped_gemm: nblocks < 0");
+    if (nblocks == 0) return CYB_OK;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    // scratch: cost[n] (double), order[n], tile_start[n+1], ticket
+    const size_t n = (size_t)nblocks;
+    Scratch ws(sizeof(int64_t) * (3 * n + 4), stream);
+    if (!ws.ptr) return CYB_ERR_CUDA;
+    double* cost = ws.as<double>();
+    int64_t* order = ws.as<int64_t>(sizeof(int64_t) * n);
+    int64_t* tile_start = ws.as<int64_t>(sizeof(int64_t) * 2 * n);
+    unsigned long long* ticket = ws.as<unsigned long long>(sizeof(int64_t) * (3 * n + 2));
+    GemmTables T;
+    T.out_mn = out_mn; T.out_off = out_off; T.out_pair_ptr = out_pair_ptr; T.pairs = pairs;
+    T.order = order; T.tile_start = tile_start; T.ticket = ticket; T.nblocks = nblocks;
+    if (dtype == CYB_F64) {
+        gemm_schedule_kernel<CfgR::BM, CfgR::BN><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost, order, tile_start, ticket);
+        CYB_LAUNCH_CHECK();
+        return launch_gemm<CfgR>(a, b, c, T, stream);
+    } else {
+        gemm_schedule_kernel<CfgC::BM, CfgC::BN><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost, order, tile_start, ticket);
+        CYB_LAUNCH_CHECK();
+        return launch_gemm<CfgC>(a, b, c, T, stream);
+    }
+}
+
+}  // extern "C"
