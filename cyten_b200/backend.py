@@ -1,0 +1,702 @@
+"""``B200AbelianBackend``: the hot-path operations of the reference's ``AbelianBackend``, driven from
+Python, executed by the CUDA kernels behind ``libcyten_b200.so``.
+
+Method names, argument meaning and result conventions follow ``cyten::AbelianBackend``
+(src/backends/abelian.cpp; interface include/cyten/backends/tensor_backend.h:85-421):
+``permute_legs`` (:988-1006), ``combine_legs`` (:1022-1219), ``split_legs`` (:3235-3436),
+``compose`` (:1222-1515), ``svd`` (:3461-3568), ``qr`` (:3084-3151), ``eigh`` (:1759-1788),
+``truncate_singular_values`` (:3623-3638).  A tensor here is anything with ``.data``
+(:class:`AbelianBackendData`), ``.codomain`` / ``.domain`` (:class:`TensorProduct`) -- see
+``cyten_b200.tensors``.
+
+There is no CPU path: every data-touching step is a kernel launch through the C-ABI.
+"""
+from __future__ import annotations
+
+import contextlib
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from .data import AbelianBackendData, aligned_offsets, ptr, stream_ptr, to_device_i64, ALIGN
+from .spaces import (AbelianLegPipe, ElementarySpace, TensorProduct, find_row_differences,
+                     make_stride)
+
+MAX_RANK = _lib.MAX_RANK
+
+
+def conventional_leg_order(codomain: TensorProduct, domain: TensorProduct):
+    """``[*codomain, *reversed(domain)]``: the axis order of every block."""
+    return [*codomain.factors, *reversed(domain.factors)]
+
+
+def _c_strides(shapes: np.ndarray) -> np.ndarray:
+    """Row-major element strides for a batch of shapes (n, r)."""
+    n, r = shapes.shape
+    st = np.ones((n, r), dtype=np.int64)
+    for a in range(r - 2, -1, -1):
+        st[:, a] = st[:, a + 1] * shapes[:, a + 1]
+    return st
+
+
+class B200AbelianBackend:
+    """Abelian block-sparse backend on one B200."""
+
+    def __init__(self, device="cuda:0", _library=None):
+        """``_library`` is a test hook: an object with the C-ABI's functions (``call(name, *args)``),
+        used by the CPU test-suite to drive this host logic with the numpy oracle.  The product path
+        never passes it: the CUDA library is mandatory and the device must be a GPU."""
+        self.device = torch.device(device)
+        if _library is None:
+            if self.device.type != "cuda":
+                raise _lib.CytenB200Error("B200AbelianBackend needs a CUDA device (no CPU fallback)")
+            _lib.load()
+            self._lib_call = _lib.call
+            self._plan_ws = lambda na, nb: self._plan_ws(na, nb)
+        else:
+            self._lib_call = _library.call
+            self._plan_ws = _library.cyb_compose_plan_workspace
+        self.launches = 0   # number of cyten_b200 kernel-launching C-ABI calls (bench bookkeeping)
+        self.last_info = None
+
+    def _ctx(self):
+        return torch.cuda.device(self.device) if self.device.type == "cuda" else contextlib.nullcontext()
+
+    def _stream(self):
+        return stream_ptr(self.device) if self.device.type == "cuda" else C.c_void_p(0)
+
+    # ------------------------------------------------------------------------------------------
+    # small device-bookkeeping wrappers (a1)
+    # ------------------------------------------------------------------------------------------
+    def _call(self, name, *args):
+        self.launches += 1
+        self._lib_call(name, *args)
+
+    def lexsort(self, rows: np.ndarray) -> np.ndarray:
+        """Device ``np.lexsort(rows.T)`` (BlockInds::lexsort_indices, block_inds.cpp:290-299)."""
+        rows = np.ascontiguousarray(rows, dtype=np.int64)
+        n, r = rows.shape
+        if n <= 1 or r == 0:
+            return np.arange(n, dtype=np.int64)
+        with self._ctx():
+            d_rows = to_device_i64(rows, self.device)
+            d_perm = torch.empty(n, dtype=torch.int64, device=self.device)
+            self._call("cyb_lexsort_rows", ptr(d_rows), n, r, ptr(d_perm), self._stream())
+            return d_perm.cpu().numpy()
+
+    def row_differences(self, rows: np.ndarray) -> np.ndarray:
+        """Device ``find_row_differences(include_len=True)`` (block_inds.cpp:308-336)."""
+        rows = np.ascontiguousarray(rows, dtype=np.int64)
+        n, r = rows.shape
+        if n == 0:
+            return np.zeros(1, dtype=np.int64)
+        with self._ctx():
+            d_rows = to_device_i64(rows, self.device)
+            d_out = torch.empty(n + 2, dtype=torch.int64, device=self.device)
+            self._call("cyb_row_differences", ptr(d_rows), n, r, ptr(d_out),
+                       C.c_void_p(d_out.data_ptr() + 8 * (n + 1)), self._stream())
+            out = d_out.cpu().numpy()
+        return out[:int(out[n + 1])].copy()
+
+    def _copy_blocks(self, src_buf, dst_buf, jobs: np.ndarray, cyb_dtype: int, conj: bool = False):
+        """jobs: int64 (njobs, 27) rows = cyb_copy_job."""
+        njobs = len(jobs)
+        if njobs == 0:
+            return
+        with self._ctx():
+            d_jobs = to_device_i64(jobs, self.device)
+            self._call("cyb_copy_blocks", ptr(src_buf), ptr(dst_buf), ptr(d_jobs), njobs, cyb_dtype,
+                       int(conj), C.c_void_p(0), 0, self._stream())
+
+    @staticmethod
+    def _make_jobs(src_off, dst_off, shapes, src_strides, dst_strides) -> np.ndarray:
+        n, r = shapes.shape
+        if r > MAX_RANK:
+            raise _lib.CytenB200Error(f"blocks of rank {r} > {MAX_RANK} are not supported")
+        jobs = np.zeros((n, _lib.COPY_JOB_WORDS), dtype=np.int64)
+        jobs[:, 0] = src_off
+        jobs[:, 1] = dst_off
+        jobs[:, 2] = r
+        jobs[:, 3:3 + r] = shapes
+        jobs[:, 3 + MAX_RANK:3 + MAX_RANK + r] = src_strides
+        jobs[:, 3 + 2 * MAX_RANK:3 + 2 * MAX_RANK + r] = dst_strides
+        return jobs
+
+    # ------------------------------------------------------------------------------------------
+    # (a3) permute_legs
+    # ------------------------------------------------------------------------------------------
+    def permute_legs(self, a, codomain_idcs, domain_idcs, new_codomain=None, new_domain=None,
+                     mixes_codomain_domain=None, levels=None, bend_right=None) -> AbelianBackendData:
+        """abelian.cpp:988-1006: permute the axes of every block, the columns of block_inds, re-sort."""
+        data: AbelianBackendData = a.data
+        axes_perm = [int(i) for i in codomain_idcs] + [int(i) for i in reversed(list(domain_idcs))]
+        r = data.block_inds.shape[1]
+        if sorted(axes_perm) != list(range(r)):
+            raise ValueError("codomain_idcs + domain_idcs must be a permutation of the legs")
+        new_bi = data.block_inds[:, axes_perm]
+        order = self.lexsort(new_bi)
+        new_bi = new_bi[order]
+        old_shapes = data.shapes
+        new_shapes = old_shapes[:, axes_perm][order]
+        res = AbelianBackendData.empty(data.dtype, self.device, new_bi, new_shapes)
+        if data.num_blocks:
+            src_strides = _c_strides(old_shapes)[:, axes_perm][order]
+            jobs = self._make_jobs(data.offsets[order], res.offsets, new_shapes, src_strides,
+                                   _c_strides(new_shapes))
+            self._copy_blocks(data.buf, res.buf, jobs, data.cyb_dtype)
+        return res
+
+    # ------------------------------------------------------------------------------------------
+    # (a4) combine_legs
+    # ------------------------------------------------------------------------------------------
+    def combine_legs(self, tensor, leg_idcs_combine, pipes, new_codomain: TensorProduct,
+                     new_domain: TensorProduct) -> AbelianBackendData:
+        """abelian.cpp:1022-1219.  ``leg_idcs_combine``: list of contiguous ascending index groups,
+        ``pipes[g]``: the AbelianLegPipe of group g (as it appears in new_codomain / new_domain)."""
+        data: AbelianBackendData = tensor.data
+        num_legs = data.block_inds.shape[1]
+        num_codomain = tensor.codomain.num_factors
+        old_legs = conventional_leg_order(tensor.codomain, tensor.domain)
+        groups = [[int(i) for i in g] for g in leg_idcs_combine]
+        for p in pipes:
+            if not isinstance(p, AbelianLegPipe):
+                raise ValueError("abelian backend requires AbelianLegPipe")
+        num_result_legs = num_legs - sum(len(g) - 1 for g in groups)
+        t_bi = data.block_inds
+        n_old = data.num_blocks
+        res_bi = np.zeros((n_old, num_result_legs), dtype=np.int64)
+        map_rows = []       # per group: row of pipe.block_ind_map for every old block
+        new_axis_of_group = []
+        old_to_new_axis = np.zeros(num_legs, dtype=np.int64)
+        cstyles = []
+        i = j = 0
+        for g, pipe in zip(groups, pipes):
+            while j < g[0]:
+                res_bi[:, i] = t_bi[:, j]
+                old_to_new_axis[j] = i
+                i += 1
+                j += 1
+            in_domain = g[0] >= num_codomain
+            cstyles.append(pipe.combine_cstyle != in_domain)
+            bi_group = t_bi[:, g[0]:g[-1] + 1]
+            if in_domain:
+                bi_group = bi_group[:, ::-1]
+            multi = bi_group @ pipe.sector_strides
+            rows = pipe._inv_fusion_outcomes_sort[multi]
+            map_rows.append(rows)
+            res_bi[:, i] = pipe.block_ind_map[rows, -1]
+            new_axis_of_group.append(i)
+            for k in g:
+                old_to_new_axis[k] = i
+            i += 1
+            j += len(g)
+        while j < num_legs:
+            res_bi[:, i] = t_bi[:, j]
+            old_to_new_axis[j] = i
+            i += 1
+            j += 1
+        # sort (duplicates stay adjacent), then dedupe -> new blocks
+        sort = self.lexsort(res_bi)
+        res_bi = res_bi[sort]
+        map_rows = [m[sort] for m in map_rows]
+        diffs = self.row_differences(res_bi)
+        new_bi = res_bi[diffs[:-1]]
+        new_legs = conventional_leg_order(new_codomain, new_domain)
+        new_shapes = np.stack([np.asarray(l.multiplicities)[new_bi[:, ax]] for ax, l in enumerate(new_legs)],
+                              axis=1) if num_result_legs else np.zeros((len(new_bi), 0), np.int64)
+        res = AbelianBackendData.empty(data.dtype, self.device, new_bi, new_shapes, zero=True)
+        if n_old == 0:
+            return res
+        # every old block -> a box inside its new block
+        new_block_of_old = np.repeat(np.arange(len(new_bi)), np.diff(diffs))
+        old_shapes = data.shapes[sort]
+        new_strides = _c_strides(new_shapes)[new_block_of_old]          # (n_old, num_result_legs)
+        dst_strides = np.zeros((n_old, num_legs), dtype=np.int64)
+        dst_off = res.offsets[new_block_of_old].copy()
+        in_group = np.zeros(num_legs, dtype=bool)
+        for g, pipe, rows, cst, ax in zip(groups, pipes, map_rows, cstyles, new_axis_of_group):
+            in_group[g] = True
+            gshape = old_shapes[:, g[0]:g[-1] + 1]
+            # position inside the combined axis: C-order over the group's axes (F-order if !cstyle)
+            inner = np.ones_like(gshape)
+            if cst:
+                for k in range(len(g) - 2, -1, -1):
+                    inner[:, k] = inner[:, k + 1] * gshape[:, k + 1]
+            else:
+                for k in range(1, len(g)):
+                    inner[:, k] = inner[:, k - 1] * gshape[:, k - 1]
+            dst_strides[:, g[0]:g[-1] + 1] = inner * new_strides[:, ax:ax + 1]
+            dst_off += pipe.block_ind_map[rows, 0] * new_strides[:, ax]
+        for k in range(num_legs):
+            if not in_group[k]:
+                dst_strides[:, k] = new_strides[:, old_to_new_axis[k]]
+        jobs = self._make_jobs(data.offsets[sort], dst_off, old_shapes, _c_strides(old_shapes), dst_strides)
+        self._copy_blocks(data.buf, res.buf, jobs, data.cyb_dtype)
+        return res
+
+    # ------------------------------------------------------------------------------------------
+    # (a5) split_legs
+    # ------------------------------------------------------------------------------------------
+    def split_legs(self, a, leg_idcs, new_codomain: TensorProduct, new_domain: TensorProduct
+                   ) -> AbelianBackendData:
+        """abelian.cpp:3235-3436: every old block is cut into the boxes listed by the pipes'
+        block_ind_map; each box becomes one new block (reshaped, F-style groups axis-reversed)."""
+        data: AbelianBackendData = a.data
+        a_num_legs = data.block_inds.shape[1]
+        num_codomain = a.codomain.num_factors
+        old_legs = conventional_leg_order(a.codomain, a.domain)
+        leg_idcs = [int(i) for i in leg_idcs]
+        pipes = [old_legs[i] for i in leg_idcs]
+        for p in pipes:
+            if not isinstance(p, AbelianLegPipe):
+                raise ValueError("split_legs: leg is not an AbelianLegPipe")
+        new_legs = conventional_leg_order(new_codomain, new_domain)
+        res_num_legs = len(new_legs)
+        n_old = data.num_blocks
+        if n_old == 0:
+            return AbelianBackendData.empty(data.dtype, self.device, np.zeros((0, res_num_legs), np.int64),
+                                            np.zeros((0, res_num_legs), np.int64))
+        old_bi = data.block_inds
+        n_split = len(leg_idcs)
+        beg = np.stack([p.block_ind_map_slices[old_bi[:, i]] for p, i in zip(pipes, leg_idcs)], axis=1)
+        cnt = np.stack([p.block_ind_map_slices[old_bi[:, i] + 1] for p, i in zip(pipes, leg_idcs)], axis=1) - beg
+        per_old = np.prod(cnt, axis=1)
+        old_rows = np.repeat(np.arange(n_old), per_old)
+        n_new = len(old_rows)
+        # map_rows[:, j]: row of pipes[j].block_ind_map; C-order enumeration inside each old block
+        start = np.concatenate([[0], np.cumsum(per_old)])[:-1]
+        local = np.arange(n_new) - np.repeat(start, per_old)
+        map_rows = np.zeros((n_new, n_split), dtype=np.int64)
+        cnt_rep = cnt[old_rows]
+        rem = local.copy()
+        for jj in range(n_split - 1, -1, -1):
+            map_rows[:, jj] = rem % cnt_rep[:, jj] + beg[old_rows, jj]
+            rem //= cnt_rep[:, jj]
+        new_bi = np.zeros((n_new, res_num_legs), dtype=np.int64)
+        src_beg = np.zeros((n_new, a_num_legs), dtype=np.int64)
+        # per NEW axis: which old axis it lives in and its stride multiplier inside that axis
+        new_axis_old = np.zeros(res_num_legs, dtype=np.int64)
+        groups_new = []
+        shift = 0
+        jp = 0
+        for i_leg in range(a_num_legs):
+            if i_leg in leg_idcs:
+                pipe = pipes[jp]
+                in_domain = i_leg >= num_codomain
+                k, k2 = i_leg + shift, i_leg + shift + pipe.num_legs
+                bmap = pipe.block_ind_map[map_rows[:, jp]]
+                cols = bmap[:, 2:2 + pipe.num_legs]
+                new_bi[:, k:k2] = cols[:, ::-1] if in_domain else cols
+                src_beg[:, i_leg] = bmap[:, 0]
+                new_axis_old[k:k2] = i_leg
+                groups_new.append((k, k2, pipe.combine_cstyle != in_domain))
+                shift += pipe.num_legs - 1
+                jp += 1
+            else:
+                new_bi[:, i_leg + shift] = old_bi[old_rows, i_leg]
+                new_axis_old[i_leg + shift] = i_leg
+        new_shapes = np.stack([np.asarray(l.multiplicities)[new_bi[:, ax]] for ax, l in enumerate(new_legs)], axis=1)
+        order = self.lexsort(new_bi)
+        new_bi, new_shapes, old_rows, src_beg = new_bi[order], new_shapes[order], old_rows[order], src_beg[order]
+        res = AbelianBackendData.empty(data.dtype, self.device, new_bi, new_shapes)
+        old_strides = _c_strides(data.shapes)[old_rows]                 # (n_new, a_num_legs)
+        src_strides = old_strides[:, new_axis_old].copy()               # (n_new, res_num_legs)
+        for (k, k2, cst) in groups_new:
+            gshape = new_shapes[:, k:k2]
+            inner = np.ones_like(gshape)
+            if cst:
+                for q in range(k2 - k - 2, -1, -1):
+                    inner[:, q] = inner[:, q + 1] * gshape[:, q + 1]
+            else:
+                for q in range(1, k2 - k):
+                    inner[:, q] = inner[:, q - 1] * gshape[:, q - 1]
+            src_strides[:, k:k2] *= inner
+        src_off = data.offsets[old_rows] + np.sum(src_beg * old_strides, axis=1)
+        jobs = self._make_jobs(src_off, res.offsets, new_shapes, src_strides, _c_strides(new_shapes))
+        self._copy_blocks(data.buf, res.buf, jobs, data.cyb_dtype)
+        return res
+
+    # ------------------------------------------------------------------------------------------
+    # (a6) compose
+    # ------------------------------------------------------------------------------------------
+    def _fuse_charges(self, d_bi, nrows, ncols, cols, legs, symmetry):
+        """Device fused charge of the legs ``legs`` (block_inds columns ``cols``) per row."""
+        nsym = symmetry.sector_ind_len
+        out = torch.zeros((max(nrows, 1), nsym), dtype=torch.int64, device=self.device)
+        if len(legs) == 0 or nrows == 0:
+            return out
+        sectors = np.concatenate([l.sector_decomposition for l in legs], axis=0)
+        sector_ptr = np.concatenate([[0], np.cumsum([l.num_sectors for l in legs])])[:-1]
+        d_cols = to_device_i64(np.asarray(cols), self.device)
+        d_sec = to_device_i64(sectors, self.device)
+        d_sptr = to_device_i64(sector_ptr, self.device)
+        d_mod = to_device_i64(symmetry.moduli_array(), self.device)
+        self._call("cyb_fuse_charges", ptr(d_bi), nrows, ncols, ptr(d_cols), len(legs), ptr(d_sec),
+                   ptr(d_sptr), ptr(d_mod), nsym, ptr(out), self._stream())
+        return out
+
+    def compose_plan(self, a, b):
+        """Device planner of abelian_compose_worker (abelian.cpp:1238-1469): returns the host copies
+        of the result tables plus the device work list for :meth:`_run_gemm`."""
+        A: AbelianBackendData = a.data
+        B: AbelianBackendData = b.data
+        a_keep = a.codomain.num_factors
+        ncontr = a.domain.num_factors
+        if ncontr != b.codomain.num_factors:
+            raise ValueError("compose: a.domain and b.codomain have different numbers of legs")
+        b_keep = b.domain.num_factors
+        na, nb = A.num_blocks, B.num_blocks
+        ra, rb = a_keep + ncontr, ncontr + b_keep
+        sym = a.codomain.symmetry
+        dev = self.device
+        a_shapes, b_shapes = A.shapes, B.shapes
+        a_mk = np.stack([np.prod(a_shapes[:, :a_keep], axis=1), np.prod(a_shapes[:, a_keep:], axis=1)], axis=1)
+        b_kn = np.stack([np.prod(b_shapes[:, :ncontr], axis=1), np.prod(b_shapes[:, ncontr:], axis=1)], axis=1)
+        contr_nsec = np.asarray([l.num_sectors for l in b.codomain.factors], dtype=np.int64)
+        with self._ctx():
+            d_abi, d_bbi = A.dev("block_inds"), B.dev("block_inds")
+            # coupled charges: codomain legs of a (columns 0..a_keep-1); domain legs of b: factor f
+            # sits in column rb-1-f (abelian.cpp:1384-1418)
+            qa = self._fuse_charges(d_abi, na, ra, list(range(a_keep)), a.codomain.factors, sym)
+            qb = self._fuse_charges(d_bbi, nb, rb, [rb - 1 - f for f in range(b_keep)], b.domain.factors, sym)
+            d_nsec, d_amk, d_bkn = (to_device_i64(contr_nsec, dev), to_device_i64(a_mk, dev),
+                                    to_device_i64(b_kn, dev))
+            ws_bytes = self._plan_ws(na, nb)
+            d_ws = torch.empty(ws_bytes // 8 + 1, dtype=torch.int64, device=dev)
+            rr = a_keep + b_keep
+            cap_out = min(na * nb, 8 * (na + nb) + 64)
+            cap_pairs = min(na * nb, 32 * (na + nb) + 64)
+            for attempt in range(2):
+                d_tab = torch.empty(8 + cap_out * (rr + 5) + (cap_out + 1) + 3 * cap_pairs,
+                                    dtype=torch.int64, device=dev)
+                o = 0
+
+                def take(n):
+                    nonlocal o
+                    t = d_tab[o:o + n]
+                    o += n
+                    return t
+                d_header, d_out_bi, d_rowcol = take(8), take(cap_out * rr), take(cap_out * 2)
+                d_mn, d_off, d_pp, d_pairs = take(cap_out * 2), take(cap_out), take(cap_out + 1), take(3 * cap_pairs)
+                self._call("cyb_compose_plan", ptr(d_abi), na, ra, a_keep, ptr(d_bbi), nb, rb, ncontr,
+                           ptr(d_nsec), ptr(qa), ptr(qb), sym.sector_ind_len, ptr(d_amk), ptr(d_bkn),
+                           ptr(A.dev("offsets")), ptr(B.dev("offsets")), ALIGN, cap_out, cap_pairs,
+                           ptr(d_header), ptr(d_out_bi), ptr(d_rowcol), ptr(d_mn), ptr(d_off), ptr(d_pp),
+                           ptr(d_pairs), ptr(d_ws), ws_bytes, self._stream())
+                header = d_header.cpu().numpy()
+                if header[3]:
+                    break
+                cap_out, cap_pairs = int(header[0]) + 1, int(header[1]) + 1   # exact counts, retry once
+            else:
+                raise _lib.CytenB200Error("compose_plan: table capacity exceeded "
+                                          f"({header[0]} blocks, {header[1]} pairs)")
+            n_out = int(header[0])
+            out_bi = d_out_bi[:n_out * rr].cpu().numpy().reshape(n_out, rr)
+            out_mn = d_mn[:n_out * 2].cpu().numpy().reshape(n_out, 2)
+            out_off = d_off[:n_out].cpu().numpy()
+            rowcol = d_rowcol[:n_out * 2].cpu().numpy().reshape(n_out, 2)
+        plan = dict(n_out=n_out, n_pairs=int(header[1]), total_elems=int(header[2]), mkn=int(header[4]),
+                    out_bi=out_bi, out_mn=out_mn, out_off=out_off, rowcol=rowcol,
+                    d_mn=d_mn, d_off=d_off, d_pp=d_pp, d_pairs=d_pairs, _keep=(d_tab,))
+        return plan
+
+    def compose(self, a, b, subset=None) -> AbelianBackendData:
+        """abelian.cpp:1222-1234 + 1238-1469: block-sparse matrix product over the matched
+        contracted sectors = plan kernel + ONE grouped DMMA GEMM launch."""
+        A: AbelianBackendData = a.data
+        B: AbelianBackendData = b.data
+        a_keep, ncontr, b_keep = a.codomain.num_factors, a.domain.num_factors, b.domain.num_factors
+        if ncontr == 0:
+            raise NotImplementedError("compose without contracted legs (outer product)")
+        res_dtype = "complex128" if "complex128" in (A.dtype, B.dtype) else "float64"
+        rr = a_keep + b_keep
+        if A.num_blocks == 0 or B.num_blocks == 0:
+            return AbelianBackendData.empty(res_dtype, self.device, np.zeros((0, rr), np.int64),
+                                            np.zeros((0, rr), np.int64))
+        if A.dtype != res_dtype:
+            a = _Retyped(a, self._to_dtype(A, res_dtype))
+            A = a.data
+        if B.dtype != res_dtype:
+            b = _Retyped(b, self._to_dtype(B, res_dtype))
+            B = b.data
+        if ncontr > 1:
+            # A's trailing axes are the contracted legs in REVERSED order; bring B's leading axes
+            # into the same order (abelian.cpp:1362-1381) with one batched copy
+            perm = list(range(ncontr - 1, -1, -1)) + list(range(ncontr, ncontr + b_keep))
+            shp = B.shapes[:, perm]
+            Bp = AbelianBackendData(B.dtype, self.device, torch.empty_like(B.buf), B.block_inds, B.offsets, B.shapes)
+            jobs = self._make_jobs(B.offsets, B.offsets, shp, _c_strides(B.shapes)[:, perm], _c_strides(shp))
+            self._copy_blocks(B.buf, Bp.buf, jobs, B.cyb_dtype)
+            b = _Retyped(b, Bp)
+            B = Bp
+        plan = self.compose_plan(a, b)
+        n_out = plan["n_out"]
+        legs = conventional_leg_order(a.codomain, b.domain)
+        out_bi = plan["out_bi"]
+        shapes = (np.stack([np.asarray(l.multiplicities)[out_bi[:, ax]] for ax, l in enumerate(legs)], axis=1)
+                  if rr else np.zeros((n_out, 0), np.int64))
+        tdt = torch.complex128 if res_dtype == "complex128" else torch.float64
+        buf = torch.empty(max(plan["total_elems"], ALIGN), dtype=tdt, device=self.device)
+        res = AbelianBackendData(res_dtype, self.device, buf, out_bi, plan["out_off"], shapes)
+        self._run_gemm(A, B, res, plan, subset)
+        res._dev_tables["offsets"] = plan["d_off"][:n_out]
+        return res
+
+    def _run_gemm(self, A, B, res, plan, subset=None):
+        n_out = plan["n_out"]
+        if n_out == 0:
+            return
+        with self._ctx():
+            if subset is None:
+                d_sub, n = None, n_out
+            else:
+                d_sub, n = to_device_i64(np.asarray(subset), self.device), len(subset)
+            self._call("cyb_grouped_gemm", ptr(A.buf), ptr(B.buf), ptr(res.buf), res.cyb_dtype,
+                       ptr(plan["d_mn"]), ptr(plan["d_off"]), ptr(plan["d_pp"]), ptr(plan["d_pairs"]),
+                       ptr(d_sub), n, self._stream())
+
+    def _to_dtype(self, data: AbelianBackendData, dtype: str) -> AbelianBackendData:
+        tdt = torch.complex128 if dtype == "complex128" else torch.float64
+        return AbelianBackendData(dtype, self.device, data.buf.to(tdt), data.block_inds, data.offsets, data.shapes)
+
+    # ------------------------------------------------------------------------------------------
+    # (a7, a9, a10) per-sector factorisations
+    # ------------------------------------------------------------------------------------------
+    def _matched_sectors(self, a, new_leg):
+        """The merge-walk over common coupled sectors shared by svd / qr (abelian.cpp:3488-3541):
+        yields (j, n, k, block index or -1): j/k index cod0/dom0, n indexes new_leg."""
+        cod0, dom0 = a.codomain.factors[0], a.domain.factors[0]
+        sc, sd = a.codomain.sector_decomposition, a.domain.sector_decomposition
+        lut_d = {tuple(s): k for k, s in enumerate(sd.tolist())}
+        where = {(int(r[0]), int(r[1])): i for i, r in enumerate(a.data.block_inds)}
+        out = []
+        n_enum = 0
+        for j, sec in enumerate(sc.tolist()):
+            k = lut_d.get(tuple(sec))
+            if k is None:
+                continue
+            n = n_enum
+            n_enum += 1
+            jj = j if cod0.sector_order == "sorted" else cod0.sector_decomposition_where(sec)
+            kk = k if dom0.sector_order == "sorted" else dom0.sector_decomposition_where(sec)
+            nn = n if new_leg.sector_order == "sorted" else new_leg.sector_decomposition_where(sec)
+            out.append((jj, nn, kk, where.get((jj, kk), -1)))
+        return out
+
+    def _sorted_data(self, dtype, block_inds, shapes):
+        """Allocates an arena for the given blocks in lexsorted order; returns (data, position of
+        every input row in the arena)."""
+        block_inds = np.asarray(block_inds, dtype=np.int64).reshape(len(shapes), -1)
+        shapes = np.asarray(shapes, dtype=np.int64).reshape(len(block_inds), -1)
+        order = self.lexsort(block_inds) if len(block_inds) else np.zeros(0, np.int64)
+        inv = np.empty(len(order), dtype=np.int64)
+        inv[order] = np.arange(len(order))
+        return AbelianBackendData.empty(dtype, self.device, block_inds[order], shapes[order]), inv
+
+    def _fill_eye(self, data: AbelianBackendData, which):
+        which = np.asarray(which, dtype=np.int64)
+        if len(which) == 0:
+            return
+        with self._ctx():
+            d_dims = to_device_i64(data.shapes[which], self.device)
+            d_off = to_device_i64(data.offsets[which], self.device)
+            self._call("cyb_fill_eye", ptr(data.buf), ptr(d_dims), ptr(d_off), len(which), data.cyb_dtype,
+                       self._stream())
+
+    def svd(self, a, new_co_domain: TensorProduct, algorithm=None):
+        """abelian.cpp:3461-3568: thin SVD of every present coupled sector in ONE batched launch;
+        absent sectors get identity slices in U / Vh and no S block.  Returns (U, S, Vh) data."""
+        A: AbelianBackendData = a.data
+        new_leg = new_co_domain.factors[0]
+        cod0, dom0 = a.codomain.factors[0], a.domain.factors[0]
+        rows = self._matched_sectors(a, new_leg)
+        u_bi = [(j, n) for j, n, k, i in rows]
+        vh_bi = [(n, k) for j, n, k, i in rows]
+        u_shapes = [(cod0.multiplicities[j], new_leg.multiplicities[n]) for j, n, k, i in rows]
+        vh_shapes = [(new_leg.multiplicities[n], dom0.multiplicities[k]) for j, n, k, i in rows]
+        present = [t for t, r in enumerate(rows) if r[3] >= 0]
+        s_bi = [(rows[t][1], rows[t][1]) for t in present]
+        s_shapes = [(new_leg.multiplicities[rows[t][1]],) for t in present]
+        U, u_pos = self._sorted_data(A.dtype, np.asarray(u_bi).reshape(-1, 2), np.asarray(u_shapes).reshape(-1, 2))
+        Vh, vh_pos = self._sorted_data(A.dtype, np.asarray(vh_bi).reshape(-1, 2), np.asarray(vh_shapes).reshape(-1, 2))
+        S, s_pos = self._sorted_data("float64", np.asarray(s_bi).reshape(-1, 2), np.asarray(s_shapes).reshape(-1, 1))
+        S.block_inds = np.asarray(S.block_inds).reshape(-1, 2)
+        absent = [t for t, r in enumerate(rows) if r[3] < 0]
+        self._fill_eye(U, u_pos[absent])
+        self._fill_eye(Vh, vh_pos[absent])
+        info = None
+        if present:
+            desc = np.zeros((len(present), 6), dtype=np.int64)
+            for q, t in enumerate(present):
+                i = rows[t][3]
+                m, n = A.shapes[i]
+                if min(m, n) != S.shapes[s_pos[q], 0]:
+                    raise _lib.CytenB200Error("svd: new leg multiplicity != min(m, n)")
+                desc[q] = (m, n, A.offsets[i], U.offsets[u_pos[t]], S.offsets[s_pos[q]], Vh.offsets[vh_pos[t]])
+            with self._ctx():
+                info = torch.zeros(len(present), dtype=torch.int64, device=self.device)
+                self._call("cyb_batched_svd", ptr(A.buf), ptr(U.buf), ptr(S.buf), ptr(Vh.buf),
+                           desc.ctypes.data_as(C.c_void_p), len(present), A.cyb_dtype, ptr(info), self._stream())
+        self.last_info = info
+        return U, S, Vh
+
+    def qr(self, a, new_co_domain: TensorProduct):
+        """abelian.cpp:3084-3151: thin QR per present sector (batched); identity slices for Q of
+        absent sectors, no R block there."""
+        A: AbelianBackendData = a.data
+        new_leg = new_co_domain.factors[0]
+        cod0, dom0 = a.codomain.factors[0], a.domain.factors[0]
+        rows = self._matched_sectors(a, new_leg)
+        present = [t for t, r in enumerate(rows) if r[3] >= 0]
+        absent = [t for t, r in enumerate(rows) if r[3] < 0]
+        q_bi = np.asarray([(j, n) for j, n, k, i in rows]).reshape(-1, 2)
+        q_shapes = np.asarray([(cod0.multiplicities[j], new_leg.multiplicities[n]) for j, n, k, i in rows]).reshape(-1, 2)
+        r_bi = np.asarray([(rows[t][1], rows[t][2]) for t in present]).reshape(-1, 2)
+        r_shapes = np.asarray([(new_leg.multiplicities[rows[t][1]], dom0.multiplicities[rows[t][2]]) for t in present]).reshape(-1, 2)
+        Q, q_pos = self._sorted_data(A.dtype, q_bi, q_shapes)
+        R, r_pos = self._sorted_data(A.dtype, r_bi, r_shapes)
+        self._fill_eye(Q, q_pos[absent])
+        if present:
+            desc = np.zeros((len(present), 6), dtype=np.int64)
+            for q, t in enumerate(present):
+                i = rows[t][3]
+                m, n = A.shapes[i]
+                desc[q] = (m, n, A.offsets[i], Q.offsets[q_pos[t]], R.offsets[r_pos[q]], 0)
+            with self._ctx():
+                self._call("cyb_batched_qr", ptr(A.buf), ptr(Q.buf), ptr(R.buf),
+                           desc.ctypes.data_as(C.c_void_p), len(present), A.cyb_dtype, self._stream())
+        return Q, R
+
+    def eigh(self, a, new_leg_dual: bool, sort=None):
+        """abelian.cpp:1759-1788: per-sector Hermitian eigendecomposition; V starts as eye_data
+        (abelian.cpp:1790-1826) and is overwritten where ``a`` has blocks.  Returns (W, V, new_leg)."""
+        if sort not in (None, "<"):
+            raise NotImplementedError("eigh: only ascending eigenvalue order (sort=None or '<')")
+        A: AbelianBackendData = a.data
+        dom0 = a.domain.factors[0]
+        new_leg = a.domain.as_ElementarySpace(new_leg_dual)
+        nsec = dom0.num_sectors
+        v_bi = np.stack([np.arange(nsec), np.arange(nsec)], axis=1).astype(np.int64)
+        v_shapes = np.stack([dom0.multiplicities, dom0.multiplicities], axis=1)
+        V = AbelianBackendData.empty(A.dtype, self.device, v_bi, v_shapes)
+        w_shapes = A.shapes[:, :1]
+        W = AbelianBackendData.empty("float64", self.device, A.block_inds, w_shapes)
+        has = np.zeros(nsec, dtype=bool)
+        has[A.block_inds[:, 0]] = True
+        self._fill_eye(V, np.nonzero(~has)[0])
+        info = None
+        if A.num_blocks:
+            desc = np.zeros((A.num_blocks, 6), dtype=np.int64)
+            for i in range(A.num_blocks):
+                m, n = A.shapes[i]
+                desc[i] = (m, n, A.offsets[i], 0, W.offsets[i], V.offsets[A.block_inds[i, 0]])
+            with self._ctx():
+                info = torch.zeros(A.num_blocks, dtype=torch.int64, device=self.device)
+                self._call("cyb_batched_eigh", ptr(A.buf), ptr(W.buf), ptr(V.buf),
+                           desc.ctypes.data_as(C.c_void_p), A.num_blocks, A.cyb_dtype, ptr(info), self._stream())
+        self.last_info = info
+        return W, V, new_leg
+
+    # ------------------------------------------------------------------------------------------
+    # (a8) truncation
+    # ------------------------------------------------------------------------------------------
+    def diagonal_to_dense(self, S: AbelianBackendData, leg: ElementarySpace, scale: float = 1.0) -> torch.Tensor:
+        """diagonal_tensor_to_block (abelian.cpp:1678-1692): zeros(leg.dim) with every block written
+        at its sector's slice; optionally scaled."""
+        dense = torch.zeros(max(leg.dim, 1), dtype=torch.float64, device=self.device)
+        if S.num_blocks:
+            sl = leg.slices[S.block_inds[:, 0], 0]
+            shapes = S.shapes[:, :1]
+            jobs = self._make_jobs(S.offsets, sl, shapes, np.ones_like(shapes), np.ones_like(shapes))
+            self._copy_blocks(S.buf, dense, jobs, _lib.CYB_F64)
+            if scale != 1.0:
+                self._call("cyb_axpby", ptr(dense), ptr(dense), leg.dim, _lib.CYB_F64, float(scale), 0.0, self._stream())
+        return dense
+
+    def truncate_singular_values(self, S: AbelianBackendData, leg: ElementarySpace, chi_max=None,
+                                 chi_min=1, degeneracy_tol=0.0, trunc_cut=0.0, svd_min=None,
+                                 minimize_error=True, scale: float = 1.0, gather=None):
+        """abelian.cpp:3623-3638 + tensor_backend.cpp:138-242 + mask_from_block (abelian.cpp:2584-2639).
+
+        Returns (keep mask over the leg's basis [host bool], small_leg, err, new_norm).
+        ``gather`` is the multi-GPU hook: a callable that all-gathers the dense S vector."""
+        dense = self.diagonal_to_dense(S, leg, scale)
+        if gather is not None:
+            dense = gather(dense)
+        n = leg.dim
+        with self._ctx():
+            keep = torch.zeros(max(n, 1), dtype=torch.uint8, device=self.device)
+            result = torch.zeros(4, dtype=torch.float64, device=self.device)
+            self._call("cyb_truncate_select", ptr(dense), n, -1 if chi_max is None else int(chi_max),
+                       int(chi_min), float(degeneracy_tol), float(trunc_cut),
+                       -1.0 if svd_min is None else float(svd_min), int(bool(minimize_error)),
+                       ptr(keep), ptr(result), self._stream())
+            keep_h = keep[:n].cpu().numpy().astype(bool)
+            res_h = result.cpu().numpy()
+        mults, secs = [], []
+        for bi_large in range(leg.num_sectors):
+            b0, b1 = leg.slices[bi_large]
+            cnt = int(keep_h[b0:b1].sum())
+            if cnt:
+                mults.append(cnt)
+                secs.append(leg.defining_sectors[bi_large])
+        secs = np.asarray(secs, dtype=np.int64).reshape(-1, leg.symmetry.sector_ind_len)
+        small_leg = ElementarySpace(leg.symmetry, secs, np.asarray(mults, dtype=np.int64), leg.is_dual)
+        return keep_h, small_leg, float(res_h[0]), float(res_h[1])
+
+    def apply_keep_mask(self, T: AbelianBackendData, axis: int, leg_col: int, leg: ElementarySpace,
+                        keep: np.ndarray, small_leg: ElementarySpace) -> AbelianBackendData:
+        """Projects a rank-2 (or rank-1 diagonal) block tensor onto the kept basis states of ``leg``
+        (block_inds column ``leg_col``): _mask_contract / apply_mask_to_DiagonalTensor
+        (abelian.cpp:2483-2582, 645-673).  Sectors without kept states are dropped and the leg's
+        block indices are renumbered to ``small_leg``."""
+        large_of_small = [i for i in range(leg.num_sectors) if keep[leg.slices[i, 0]:leg.slices[i, 1]].any()]
+        renum = -np.ones(leg.num_sectors, dtype=np.int64)
+        renum[large_of_small] = np.arange(len(large_of_small))
+        sel = np.nonzero(renum[T.block_inds[:, leg_col]] >= 0)[0]
+        diag = T.shapes.shape[1] == 1
+        new_bi = T.block_inds[sel].copy()
+        if diag:
+            new_bi[:, :] = renum[new_bi[:, :1]]
+        else:
+            new_bi[:, leg_col] = renum[new_bi[:, leg_col]]
+        idx_lists = [np.nonzero(keep[leg.slices[s, 0]:leg.slices[s, 1]])[0] for s in T.block_inds[sel, leg_col]]
+        new_shapes = T.shapes[sel].copy()
+        ax = 0 if diag else axis
+        new_shapes[:, ax] = [len(ix) for ix in idx_lists]
+        res, pos = self._sorted_data(T.dtype, new_bi, new_shapes)
+        if len(sel) == 0:
+            return res
+        idx_ptr = np.concatenate([[0], np.cumsum([len(ix) for ix in idx_lists])])
+        desc = np.zeros((len(sel), 6), dtype=np.int64)
+        for q, i in enumerate(sel):
+            m, n = (T.shapes[i, 0], 1) if diag else T.shapes[i]
+            desc[q] = (m, n, T.offsets[i], res.offsets[pos[q]], idx_ptr[q], len(idx_lists[q]))
+        with self._ctx():
+            d_desc = to_device_i64(desc, self.device)
+            d_idx = to_device_i64(np.concatenate(idx_lists) if idx_ptr[-1] else np.zeros(1, np.int64), self.device)
+            self._call("cyb_gather_rows_cols", ptr(T.buf), ptr(res.buf), ptr(d_desc), ptr(d_idx), len(sel),
+                       0 if diag else axis, T.cyb_dtype, self._stream())
+        return res
+
+    def norm(self, data: AbelianBackendData) -> float:
+        """Frobenius norm over all blocks (abelian.cpp:2780-2791).  The arena padding between blocks
+        is uninitialised, so the sum runs block by block."""
+        esz = 16 if data.dtype == "complex128" else 8
+        with self._ctx():
+            out = torch.zeros(1, dtype=torch.float64, device=self.device)
+            tot = torch.zeros(1, dtype=torch.float64, device=self.device)
+            for off, size in zip(data.offsets, data.sizes):
+                self._call("cyb_sumsq", C.c_void_p(data.buf.data_ptr() + int(off) * esz), int(size),
+                           data.cyb_dtype, ptr(out), self._stream())
+                tot += out
+            return float(tot.sqrt().item())
+
+
+class _Retyped:
+    """A tensor view with replaced data (used for dtype promotion / re-laid-out operands)."""
+
+    def __init__(self, t, data):
+        self.data, self.codomain, self.domain = data, t.codomain, t.domain
