@@ -54,7 +54,7 @@ class B200AbelianBackend:
                 raise _lib.CytenB200Error("B200AbelianBackend needs a CUDA device (no CPU fallback)")
             _lib.load()
             self._lib_call = _lib.call
-            self._plan_ws = lambda na, nb: self._plan_ws(na, nb)
+            self._plan_ws = lambda na, nb: _lib.load().cyb_compose_plan_workspace(na, nb)
         else:
             self._lib_call = _library.call
             self._plan_ws = _library.cyb_compose_plan_workspace

@@ -369,7 +369,7 @@ jacobi_svd_kernel(const void* __restrict__ a_, void* __restrict__ o0_, double* _
             }
         }
     }
-    if (gtid == 0) info[mat] = converged ? sweeps_done : -sweeps_done;
+    if (gtid == 0) info[mat] = converged ? (sweeps_done > 0 ? sweeps_done : 1) : -(sweeps_done > 0 ? sweeps_done : 1);
     (void)m;
 }
 
