@@ -1,0 +1,401 @@
+#!/usr/bin/env python3
+"""Benchmark of the abelian block-sparse hot path (BASELINE.json metric:
+"U(1) tdot GFLOP/s and block truncated-SVD ms at chi=4096").
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--chi 4096]
+
+One *step* = one pass of the hot path over one synthetic input: the two-site DMRG effective-Hamiltonian
+matvec  LP.W.W.RP.theta  (toycodes/tenpy_toycodes/d_dmrg.py:70-88: 5 permute_legs + 4 compose, i.e.
+4 tdot-style contractions) on random U(1) tensors with the bond leg of BASELINE.md section 3.
+``value`` = algorithmic flops of the 4 composes (sum 2*M*K*N over the reference's matrix_dot list,
+abelian.cpp:1424-1446) / device time of the whole step, inputs resident in HBM.  The truncated SVD of
+theta at the same chi is timed separately and reported as ``svd_ms``.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "u1_tdot_gflops"
+UNIT = "GFLOP/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--chi", type=int, default=4096)
+    ap.add_argument("--svd-chi", type=int, default=None)
+    ap.add_argument("--no-svd", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-chi", type=int, default=None, help="bond dimension of the bounded CPU sample")
+    return ap.parse_args()
+
+
+# ---- clocks sampling ---------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def measured_peaks():
+    f = ROOT / "MEASURED_PEAKS.json"
+    if f.exists():
+        d = json.loads(f.read_text())
+        return d.get("hbm_gbs", 6650.0), "measured"
+    return 6650.0, "fallback"
+
+
+# ---- reference arm: the UNMODIFIED reference (oracle/_ref) on the host cores ------------------------------
+def build_reference_heff(chi):
+    sys.path.insert(0, str(ROOT / "oracle" / "_ref"))
+    import cyten as ct
+    from cyten_b200.workloads import HEFF_LABELS, HEFF_SEEDS, HEffective, heff_spaces, random_blocks
+    be = ct.get_backend("abelian", "numpy")
+    sym = ct.u1_symmetry
+
+    def conv(leg):
+        return ct.ElementarySpace.from_defining_sectors(sym, leg.defining_sectors, leg.multiplicities, is_dual=leg.is_dual)
+    T = {}
+    for name, (cod, dom) in heff_spaces(chi).items():
+        bi, blocks = random_blocks(cod, dom, HEFF_SEEDS[name])
+        data = ct.backends.AbelianBackendData(dtype=ct.Dtype.float64, device="cpu",
+                                              blocks=[be.block_backend.as_block(b) for b in blocks],
+                                              block_inds=ct.backends.BlockInds(bi) if hasattr(ct.backends, "BlockInds") else bi,
+                                              is_sorted=True)
+        T[name] = ct.SymmetricTensor(data, [conv(l) for l in cod], [conv(l) for l in dom], backend=be,
+                                     labels=HEFF_LABELS[name])
+
+    class Ops:
+        permute_legs = staticmethod(lambda t, codomain=None, domain=None: ct.permute_legs(t, codomain, domain, bend_right=None))
+        compose = staticmethod(ct.compose)
+    return HEffective(T["LP"], T["RP"], T["W1"], T["W2"], Ops), T["theta"], ct
+
+
+def cpu_matvec_time(chi, kind, repeats=1):
+    """Seconds per matvec of the CPU implementation (kind 'reference' = oracle/_ref, 'port' = numpy oracle)."""
+    if kind == "reference":
+        H, theta, _ = build_reference_heff(chi)
+    else:
+        from cyten_b200.backend import B200AbelianBackend
+        from cyten_b200.workloads import build_heff
+        from oracle import cabi_numpy
+        H, theta, _, _ = build_heff(chi, B200AbelianBackend("cpu", _library=cabi_numpy))
+    H.matvec(theta)   # warm-up
+    best = float("inf")
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        H.matvec(theta)
+        best = min(best, time.perf_counter() - t0)
+    return best
+
+
+def reference_available():
+    return bool(list((ROOT / "oracle" / "_ref" / "cyten").glob("_core*.so")))
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    kind = "reference" if reference_available() else "port"
+    chi = args.chi
+    cores = os.cpu_count() or 1
+    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    os.environ.setdefault("OPENBLAS_NUM_THREADS", str(cores))
+    flops = flops_of_matvec(chi)
+    if kind == "reference":
+        H, theta, _ = build_reference_heff(chi)
+    else:
+        from cyten_b200.backend import B200AbelianBackend
+        from cyten_b200.workloads import build_heff
+        from oracle import cabi_numpy
+        H, theta, _, _ = build_heff(chi, B200AbelianBackend("cpu", _library=cabi_numpy))
+    for _ in range(min(args.warmup, 1)):
+        H.matvec(theta)
+    steps = max(1, min(args.steps, 3))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        H.matvec(theta)
+    dt = (time.perf_counter() - t0) / steps
+    val = flops / dt / 1e9
+    line = {"metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": min(args.warmup, 1),
+            "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "impl": "reference",
+            "config": {"workload": f"U(1) DMRG two-site H_eff matvec (4 tdot + 5 permute_legs), chi={chi}, D=5, d=2, float64"},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind,
+                             "sample": f"{steps} matvec(s) at chi={chi} on the host cores"},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+_FLOPS_CACHE = {}
+
+
+def flops_of_matvec(chi):
+    """2 * sum M*K*N over the matrix_dot lists of the 4 composes (abelian.cpp:1424-1446).  Depends on
+    block_inds + multiplicities only: a plan-only (dry_run) pass of the host logic over the numpy oracle."""
+    if chi in _FLOPS_CACHE:
+        return _FLOPS_CACHE[chi]
+    import torch
+    from cyten_b200 import tensors as ops
+    from cyten_b200.backend import B200AbelianBackend, conventional_leg_order
+    from cyten_b200.data import AbelianBackendData
+    from cyten_b200.spaces import TensorProduct
+    from cyten_b200.tensors import SymmetricTensor, valid_block_inds
+    from cyten_b200.workloads import HEFF_LABELS, HEffective, heff_spaces
+    from oracle import cabi_numpy
+    be = B200AbelianBackend("cpu", _library=cabi_numpy)
+    be.dry_run = True
+    be.plan_mkn = []
+    T = {}
+    for name, (cod, dom) in heff_spaces(chi).items():
+        cod, dom = TensorProduct(cod), TensorProduct(dom)
+        bi = valid_block_inds(cod, dom)
+        legs = conventional_leg_order(cod, dom)
+        shapes = np.stack([np.asarray(l.multiplicities)[bi[:, ax]] for ax, l in enumerate(legs)], axis=1)
+        T[name] = SymmetricTensor(be._empty("float64", "cpu", bi, shapes), cod, dom, be, HEFF_LABELS[name])
+    HEffective(T["LP"], T["RP"], T["W1"], T["W2"], ops).matvec(T["theta"])
+    _FLOPS_CACHE[chi] = 2.0 * float(sum(be.plan_mkn))
+    return _FLOPS_CACHE[chi]
+
+
+# ---- the B200 arm -------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from cyten_b200 import tensors as ct
+    from cyten_b200.backend import B200AbelianBackend
+    from cyten_b200.workloads import build_heff, random_blocks, CONFIG_LEGS
+    from cyten_b200.tensors import SymmetricTensor
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device(f"cuda:{local}")
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    be = B200AbelianBackend(dev)
+    if world > 1:
+        from cyten_b200.sharding import attach_process_group
+        attach_process_group(be, dist.group.WORLD)
+    chi = args.chi
+    H, theta, host, sp = build_heff(chi, be)
+    flops = None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # warm-up (also yields the algorithmic flop count from the device planner)
+    be.plan_mkn = []
+    for _ in range(max(args.warmup, 3)):
+        be.plan_mkn = []
+        y = H.matvec(theta)
+    flops = 2.0 * float(sum(be.plan_mkn))
+    be.plan_mkn = None
+    l2_flush = torch.empty(192 * 1024 * 1024, dtype=torch.uint8, device=dev)
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    # ---- timed region: K steps, device time, L2 flushed between steps (flush excluded via events) ----
+    be.gemm_events = []
+    be.gemm_event_flops = []
+    be.launches = 0
+    step_ms = []
+    barrier()
+    for _ in range(args.steps):
+        l2_flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        y = H.matvec(theta)
+        e1.record()
+        step_ms.append((e0, e1))
+    barrier()
+    launches = be.launches
+    total_ms = sum(a.elapsed_time(b) for a, b in step_ms)
+    gemm_ms = [a.elapsed_time(b) for a, b in be.gemm_events]
+    gemm_flops = be.gemm_event_flops
+    be.gemm_events = None
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    ms_per_step = total_ms / args.steps
+    value = flops / (ms_per_step * 1e-3) / 1e9
+
+    # ---- end to end: theta from pinned host memory every step, result back to the host ----
+    bi_t, blocks_t = host["theta"]
+    pinned = torch.empty(theta.data.buf.numel(), dtype=torch.float64).pin_memory()
+    hostbuf = pinned.numpy()
+    for b, off in zip(blocks_t, theta.data.offsets):
+        hostbuf[off:off + b.size] = b.reshape(-1)
+    out_host = None
+    e2e_steps = max(1, min(args.steps, 5))
+    barrier()
+    t0 = time.perf_counter()
+    h2d = d2h = 0
+    for _ in range(e2e_steps):
+        theta.data.buf.copy_(pinned, non_blocking=True)
+        h2d = pinned.numel() * 8
+        y = H.matvec(theta)
+        if out_host is None or out_host.numel() != y.data.buf.numel():
+            out_host = torch.empty(y.data.buf.numel(), dtype=torch.float64).pin_memory()
+        out_host.copy_(y.data.buf, non_blocking=True)
+        d2h = out_host.numel() * 8
+        torch.cuda.synchronize()
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / e2e_steps
+    te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_val = flops / float(te.item()) / 1e9
+
+    # ---- truncated SVD of theta = tdot(B, B) at chi (BASELINE config 3) ----
+    svd_ms = svd_info = None
+    if not args.no_svd:
+        from cyten_b200.workloads import mps_tensor, u1_bond_leg, u1_phys_leg
+        schi = args.svd_chi or chi
+        Q, sigma = CONFIG_LEGS[schi]
+        v, p = u1_bond_leg(schi, Q, sigma), u1_phys_leg()
+        A, B = mps_tensor(v, p, v, be, seed=7), mps_tensor(v, p, v, be, seed=8)
+        th = ct.tdot(A, B, [2], [0])
+        gather = getattr(be, "gather_hook", None)
+        ct.truncated_svd(th, chi_max=schi, svd_min=1e-14, gather=gather)   # warm-up
+        times = []
+        for _ in range(2):
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            U, S, Vh, err, _ = ct.truncated_svd(th, chi_max=schi, svd_min=1e-14, gather=gather)
+            e1.record()
+            barrier()
+            times.append(e0.elapsed_time(e1))
+        ts = torch.tensor([min(times)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+        svd_ms = float(ts.item())
+        svd_info = {"chi": schi, "kept": int(S.data.shapes.sum()), "err": err,
+                    "sweeps_max": int(be.last_info.abs().max().item()) if be.last_info is not None else None}
+    clocks = sampler.stop() if rank == 0 else None
+
+    if rank == 0:
+        # ---- roofline of the dominant kernel (grouped DMMA GEMM): FP64 tensor peak ----
+        g_ms = float(np.mean(gemm_ms)) if gemm_ms else None
+        g_fl = float(np.mean(gemm_flops)) if gemm_flops else None
+        peak_tf, peak_src = fp64_peak_tflops(dev)
+        roof = None
+        if g_ms:
+            ach = g_fl / (g_ms * 1e-3) / 1e12
+            roof = {"bound": "tensor", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf,
+                    "traffic": None, "kernel": "grouped_gemm_kernel (DMMA f64)", "peak_source": peak_src,
+                    "gemm_share_of_step": sum(gemm_ms) / total_ms if total_ms else None}
+        cpu = None
+        if not args.no_cpu_baseline and world == 1:
+            cpu = cpu_baseline(args)
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic",
+                "config": {"workload": f"U(1) DMRG two-site H_eff matvec (4 tdot + 5 permute_legs), chi={chi}, D=5, d=2, float64",
+                           "l2": "192 MiB buffer written between timed steps", "flops_per_step": flops,
+                           "sharding": "output sectors LPT over ranks + allgather" if world > 1 else "single GPU"},
+                "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+                "gpu_launches": launches, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
+                "svd_ms": svd_ms, "svd": svd_info}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def fp64_peak_tflops(dev):
+    """FP64 tensor (DMMA) peak: MEASURED_PEAKS.json carries only bf16 + HBM, so the denominator is
+    measured here with a cuBLAS DGEMM 8192^3 (best of 5, CUDA events) -- 'of measured (cuBLAS DGEMM)'."""
+    import torch
+    n = 8192
+    a = torch.randn(n, n, dtype=torch.float64, device=dev)
+    b = torch.randn(n, n, dtype=torch.float64, device=dev)
+    torch.matmul(a, b)
+    best = float("inf")
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        torch.matmul(a, b)
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    return 2.0 * n ** 3 / (best * 1e-3) / 1e12, "cuBLAS DGEMM 8192^3 measured in this run"
+
+
+def cpu_baseline(args):
+    cores = os.cpu_count() or 1
+    kind = "reference" if reference_available() else "port"
+    chi = args.cpu_chi or min(args.chi, 4096)
+    try:
+        dt = cpu_matvec_time(chi, kind)
+    except Exception as e:   # the reference .so may not load on an odd box: fall back to the port
+        kind = "port"
+        dt = cpu_matvec_time(chi, kind)
+    fl = flops_of_matvec(chi)
+    return {"value": fl / dt / 1e9, "unit": UNIT, "cores": cores, "kind": kind, "ms_per_step": dt * 1e3,
+            "sample": f"1 H_eff matvec at chi={chi} (after 1 warm-up), AbelianBackend+NumpyBlockBackend on the host cores"}
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -60,6 +60,19 @@ class B200AbelianBackend:
             self._plan_ws = _library.cyb_compose_plan_workspace
         self.launches = 0   # number of cyten_b200 kernel-launching C-ABI calls (bench bookkeeping)
         self.last_info = None
+        self.dry_run = False        # plan-only mode: tables are computed, arenas are not touched
+        self.plan_mkn = None        # bench hook: list collecting sum(M*K*N) of every compose
+        self.gemm_events = None     # bench hook: list of (start, end) CUDA events around the GEMM launch
+        self.gemm_event_flops = []
+        self.shard = None           # multi-GPU hook, see cyten_b200.sharding
+
+    def _empty(self, dtype, device, block_inds, shapes, zero=False):
+        if self.dry_run:
+            shapes = np.asarray(shapes, dtype=np.int64).reshape(len(block_inds), -1)
+            sizes = np.prod(shapes, axis=1) if shapes.shape[1] else np.ones(len(shapes), np.int64)
+            offs, _ = aligned_offsets(sizes)
+            return AbelianBackendData(dtype, device, torch.empty(ALIGN, dtype=torch.float64), block_inds, offs, shapes)
+        return AbelianBackendData.empty(dtype, device, block_inds, shapes, zero=zero)
 
     def _ctx(self):
         return torch.cuda.device(self.device) if self.device.type == "cuda" else contextlib.nullcontext()
@@ -103,7 +116,7 @@ class B200AbelianBackend:
     def _copy_blocks(self, src_buf, dst_buf, jobs: np.ndarray, cyb_dtype: int, conj: bool = False):
         """jobs: int64 (njobs, 27) rows = cyb_copy_job."""
         njobs = len(jobs)
-        if njobs == 0:
+        if njobs == 0 or self.dry_run:
             return
         with self._ctx():
             d_jobs = to_device_i64(jobs, self.device)
@@ -140,7 +153,7 @@ class B200AbelianBackend:
         new_bi = new_bi[order]
         old_shapes = data.shapes
         new_shapes = old_shapes[:, axes_perm][order]
-        res = AbelianBackendData.empty(data.dtype, self.device, new_bi, new_shapes)
+        res = self._empty(data.dtype, self.device, new_bi, new_shapes)
         if data.num_blocks:
             src_strides = _c_strides(old_shapes)[:, axes_perm][order]
             jobs = self._make_jobs(data.offsets[order], res.offsets, new_shapes, src_strides,
@@ -206,7 +219,7 @@ class B200AbelianBackend:
         new_legs = conventional_leg_order(new_codomain, new_domain)
         new_shapes = np.stack([np.asarray(l.multiplicities)[new_bi[:, ax]] for ax, l in enumerate(new_legs)],
                               axis=1) if num_result_legs else np.zeros((len(new_bi), 0), np.int64)
-        res = AbelianBackendData.empty(data.dtype, self.device, new_bi, new_shapes, zero=True)
+        res = self._empty(data.dtype, self.device, new_bi, new_shapes, zero=True)
         if n_old == 0:
             return res
         # every old block -> a box inside its new block
@@ -256,7 +269,7 @@ class B200AbelianBackend:
         res_num_legs = len(new_legs)
         n_old = data.num_blocks
         if n_old == 0:
-            return AbelianBackendData.empty(data.dtype, self.device, np.zeros((0, res_num_legs), np.int64),
+            return self._empty(data.dtype, self.device, np.zeros((0, res_num_legs), np.int64),
                                             np.zeros((0, res_num_legs), np.int64))
         old_bi = data.block_inds
         n_split = len(leg_idcs)
@@ -300,7 +313,7 @@ class B200AbelianBackend:
         new_shapes = np.stack([np.asarray(l.multiplicities)[new_bi[:, ax]] for ax, l in enumerate(new_legs)], axis=1)
         order = self.lexsort(new_bi)
         new_bi, new_shapes, old_rows, src_beg = new_bi[order], new_shapes[order], old_rows[order], src_beg[order]
-        res = AbelianBackendData.empty(data.dtype, self.device, new_bi, new_shapes)
+        res = self._empty(data.dtype, self.device, new_bi, new_shapes)
         old_strides = _c_strides(data.shapes)[old_rows]                 # (n_new, a_num_legs)
         src_strides = old_strides[:, new_axis_old].copy()               # (n_new, res_num_legs)
         for (k, k2, cst) in groups_new:
@@ -413,7 +426,7 @@ class B200AbelianBackend:
         res_dtype = "complex128" if "complex128" in (A.dtype, B.dtype) else "float64"
         rr = a_keep + b_keep
         if A.num_blocks == 0 or B.num_blocks == 0:
-            return AbelianBackendData.empty(res_dtype, self.device, np.zeros((0, rr), np.int64),
+            return self._empty(res_dtype, self.device, np.zeros((0, rr), np.int64),
                                             np.zeros((0, rr), np.int64))
         if A.dtype != res_dtype:
             a = _Retyped(a, self._to_dtype(A, res_dtype))
@@ -438,7 +451,9 @@ class B200AbelianBackend:
         shapes = (np.stack([np.asarray(l.multiplicities)[out_bi[:, ax]] for ax, l in enumerate(legs)], axis=1)
                   if rr else np.zeros((n_out, 0), np.int64))
         tdt = torch.complex128 if res_dtype == "complex128" else torch.float64
-        buf = torch.empty(max(plan["total_elems"], ALIGN), dtype=tdt, device=self.device)
+        if self.plan_mkn is not None:
+            self.plan_mkn.append(plan["mkn"])
+        buf = torch.empty(ALIGN if self.dry_run else max(plan["total_elems"], ALIGN), dtype=tdt, device=self.device)
         res = AbelianBackendData(res_dtype, self.device, buf, out_bi, plan["out_off"], shapes)
         self._run_gemm(A, B, res, plan, subset)
         res._dev_tables["offsets"] = plan["d_off"][:n_out]
@@ -446,8 +461,12 @@ class B200AbelianBackend:
 
     def _run_gemm(self, A, B, res, plan, subset=None):
         n_out = plan["n_out"]
-        if n_out == 0:
+        if n_out == 0 or self.dry_run:
             return
+        timed = self.gemm_events is not None and self.device.type == "cuda"
+        if timed:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
         with self._ctx():
             if subset is None:
                 d_sub, n = None, n_out
@@ -456,6 +475,10 @@ class B200AbelianBackend:
             self._call("cyb_grouped_gemm", ptr(A.buf), ptr(B.buf), ptr(res.buf), res.cyb_dtype,
                        ptr(plan["d_mn"]), ptr(plan["d_off"]), ptr(plan["d_pp"]), ptr(plan["d_pairs"]),
                        ptr(d_sub), n, self._stream())
+        if timed:
+            e1.record()
+            self.gemm_events.append((e0, e1))
+            self.gemm_event_flops.append((8.0 if res.dtype == "complex128" else 2.0) * plan["mkn"])
 
     def _to_dtype(self, data: AbelianBackendData, dtype: str) -> AbelianBackendData:
         tdt = torch.complex128 if dtype == "complex128" else torch.float64
@@ -493,11 +516,11 @@ class B200AbelianBackend:
         order = self.lexsort(block_inds) if len(block_inds) else np.zeros(0, np.int64)
         inv = np.empty(len(order), dtype=np.int64)
         inv[order] = np.arange(len(order))
-        return AbelianBackendData.empty(dtype, self.device, block_inds[order], shapes[order]), inv
+        return self._empty(dtype, self.device, block_inds[order], shapes[order]), inv
 
     def _fill_eye(self, data: AbelianBackendData, which):
         which = np.asarray(which, dtype=np.int64)
-        if len(which) == 0:
+        if len(which) == 0 or self.dry_run:
             return
         with self._ctx():
             d_dims = to_device_i64(data.shapes[which], self.device)
@@ -580,9 +603,9 @@ class B200AbelianBackend:
         nsec = dom0.num_sectors
         v_bi = np.stack([np.arange(nsec), np.arange(nsec)], axis=1).astype(np.int64)
         v_shapes = np.stack([dom0.multiplicities, dom0.multiplicities], axis=1)
-        V = AbelianBackendData.empty(A.dtype, self.device, v_bi, v_shapes)
+        V = self._empty(A.dtype, self.device, v_bi, v_shapes)
         w_shapes = A.shapes[:, :1]
-        W = AbelianBackendData.empty("float64", self.device, A.block_inds, w_shapes)
+        W = self._empty("float64", self.device, A.block_inds, w_shapes)
         has = np.zeros(nsec, dtype=bool)
         has[A.block_inds[:, 0]] = True
         self._fill_eye(V, np.nonzero(~has)[0])

@@ -52,3 +52,74 @@ def compose_flops(plan, dtype="float64") -> float:
     """Algorithmic flops of a compose: ``sum c*M*K*N`` over the reference's matrix_dot list
     (abelian.cpp:1424-1446), c = 2 real / 8 complex."""
     return (8.0 if dtype == "complex128" else 2.0) * float(plan["mkn"])
+
+
+# ---- host-side block generation (shared by the GPU arm, the oracle arm and the reference arm) ----
+def random_blocks(codomain, domain, seed=0, dtype="float64"):
+    """(block_inds, blocks) of a tensor with all symmetry-allowed blocks, N(0,1) entries."""
+    from .backend import conventional_leg_order
+    from .tensors import valid_block_inds
+    codomain = codomain if isinstance(codomain, TensorProduct) else TensorProduct(list(codomain))
+    if not isinstance(domain, TensorProduct):
+        domain = TensorProduct(list(domain), symmetry=codomain.symmetry)
+    bi = valid_block_inds(codomain, domain)
+    legs = conventional_leg_order(codomain, domain)
+    rng = np.random.default_rng(seed)
+    blocks = []
+    for row in bi:
+        shape = tuple(int(l.multiplicities[b]) for l, b in zip(legs, row))
+        x = rng.standard_normal(shape)
+        if dtype == "complex128":
+            x = x + 1j * rng.standard_normal(shape)
+        blocks.append(x)
+    return bi, blocks
+
+
+def heff_spaces(chi: int, Q: int | None = None, sigma: float | None = None):
+    """Legs of the two-site effective Hamiltonian (toycodes/tenpy_toycodes/d_dmrg.py:40-88) in the
+    already-bent form HEffective.__init__ produces:
+      theta: [v, p] <- [v, p*]      LP: [v, w*] <- [v]      W1 = W2: [p, w*] <- [w*, p]      RP: [v, w] <- [v]
+    """
+    if Q is None:
+        Q, sigma = CONFIG_LEGS[chi]
+    v, p, w = u1_bond_leg(chi, Q, sigma), u1_phys_leg(), u1_mpo_leg()
+    return dict(theta=([v, p], [v, p.dual]), LP=([v, w.dual], [v]), W1=([p, w.dual], [w.dual, p]),
+                W2=([p, w.dual], [w.dual, p]), RP=([v, w], [v]))
+
+
+HEFF_LABELS = dict(theta=["vL", "p0", "p1", "vR"], LP=["vL", "wL*", "vL*"], W1=["p0", "wC", "p0*", "wL"],
+                   W2=["p1", "wR", "p1*", "wC"], RP=["vR*", "wR*", "vR"])
+HEFF_SEEDS = dict(theta=1, LP=2, W1=3, W2=4, RP=5)
+
+
+class HEffective:
+    """Two-site DMRG effective Hamiltonian; ``matvec`` is the call sequence of
+    ``HEffective.matvec`` (d_dmrg.py:70-88): 5 x permute_legs interleaved with 4 x compose."""
+
+    def __init__(self, LP, RP, W1, W2, ops):
+        self.LP, self.RP, self.W1, self.W2, self.ct = LP, RP, W1, W2, ops
+
+    def matvec(self, theta):
+        ct = self.ct
+        x = ct.permute_legs(theta, ["vL"], ["vR", "p1", "p0"])
+        x = ct.compose(self.LP, x)                                  # vL wL* p0 p1 vR
+        x = ct.permute_legs(x, ["wL*", "p0"], ["vL", "vR", "p1"])
+        x = ct.compose(self.W1, x)                                  # p0 wC p1 vR vL
+        x = ct.permute_legs(x, ["wC", "p1"], ["p0", "vL", "vR"])
+        x = ct.compose(self.W2, x)                                  # p1 wR vR vL p0
+        x = ct.permute_legs(x, ["vL", "p0", "p1"], ["vR", "wR"])
+        x = ct.compose(x, self.RP)                                  # vL p0 p1 vR
+        x = ct.permute_legs(x, domain=["vR", "p1"])
+        return x
+
+
+def build_heff(chi: int, backend, dtype="float64", Q=None, sigma=None):
+    """(HEffective, theta) on ``backend`` plus the host blocks of theta (for the end-to-end arm)."""
+    from . import tensors as ops
+    sp = heff_spaces(chi, Q, sigma)
+    T, host = {}, {}
+    for name, (cod, dom) in sp.items():
+        bi, blocks = random_blocks(cod, dom, HEFF_SEEDS[name], dtype)
+        host[name] = (bi, blocks)
+        T[name] = SymmetricTensor.from_numpy_blocks(blocks, bi, cod, dom, backend, labels=HEFF_LABELS[name], dtype=dtype)
+    return HEffective(T["LP"], T["RP"], T["W1"], T["W2"], ops), T["theta"], host, sp
