@@ -528,13 +528,17 @@ class B200AbelianBackend:
             self._call("cyb_fill_eye", ptr(data.buf), ptr(d_dims), ptr(d_off), len(which), data.cyb_dtype,
                        self._stream())
 
-    def svd(self, a, new_co_domain: TensorProduct, algorithm=None):
+    def svd(self, a, new_co_domain: TensorProduct, algorithm=None, only_rows=None):
         """abelian.cpp:3461-3568: thin SVD of every present coupled sector in ONE batched launch;
-        absent sectors get identity slices in U / Vh and no S block.  Returns (U, S, Vh) data."""
+        absent sectors get identity slices in U / Vh and no S block.  Returns (U, S, Vh) data.
+        ``only_rows`` (multi-GPU sharding): positions in the matched-sector walk this rank owns; the
+        other sectors are left to their owners (no block here)."""
         A: AbelianBackendData = a.data
         new_leg = new_co_domain.factors[0]
         cod0, dom0 = a.codomain.factors[0], a.domain.factors[0]
         rows = self._matched_sectors(a, new_leg)
+        if only_rows is not None:
+            rows = [rows[t] for t in only_rows]
         u_bi = [(j, n) for j, n, k, i in rows]
         vh_bi = [(n, k) for j, n, k, i in rows]
         u_shapes = [(cod0.multiplicities[j], new_leg.multiplicities[n]) for j, n, k, i in rows]
@@ -640,14 +644,32 @@ class B200AbelianBackend:
 
     def truncate_singular_values(self, S: AbelianBackendData, leg: ElementarySpace, chi_max=None,
                                  chi_min=1, degeneracy_tol=0.0, trunc_cut=0.0, svd_min=None,
-                                 minimize_error=True, scale: float = 1.0, gather=None):
+                                 minimize_error=True, scale: float = 1.0):
         """abelian.cpp:3623-3638 + tensor_backend.cpp:138-242 + mask_from_block (abelian.cpp:2584-2639).
 
-        Returns (keep mask over the leg's basis [host bool], small_leg, err, new_norm).
-        ``gather`` is the multi-GPU hook: a callable that all-gathers the dense S vector."""
+        Returns (keep mask over the leg's basis [host bool], small_leg, err, new_norm)."""
         dense = self.diagonal_to_dense(S, leg, scale)
-        if gather is not None:
-            dense = gather(dense)
+        return self._select(dense, leg, chi_max, chi_min, degeneracy_tol, trunc_cut, svd_min, minimize_error)
+
+    def truncate_dense(self, dense: torch.Tensor, leg: ElementarySpace, chi_max=None, chi_min=1,
+                       degeneracy_tol=0.0, trunc_cut=0.0, svd_min=None, minimize_error=True):
+        """Truncation of the NORMALISED singular values given as the dense vector over ``leg``
+        (decompositions.cpp:672-709: ``S / norm(S)`` goes into truncate_singular_values).  Used where the
+        vector was assembled by the multi-GPU all_gather.  Returns (keep, small_leg, err, new_norm, S_norm)."""
+        n = leg.dim
+        with self._ctx():
+            out = torch.zeros(1, dtype=torch.float64, device=self.device)
+            self._call("cyb_sumsq", ptr(dense), n, _lib.CYB_F64, ptr(out), self._stream())
+            S_norm = float(out.sqrt().item())
+            if S_norm > 0:
+                self._call("cyb_axpby", ptr(dense), ptr(dense), n, _lib.CYB_F64, 1.0 / S_norm, 0.0, self._stream())
+        return (*self._select(dense, leg, chi_max, chi_min, degeneracy_tol, trunc_cut, svd_min, minimize_error), S_norm)
+
+    def scale_inplace(self, data: AbelianBackendData, factor: float):
+        self._call("cyb_axpby", ptr(data.buf), ptr(data.buf), data.buf.numel(), data.cyb_dtype, float(factor), 0.0,
+                   self._stream())
+
+    def _select(self, dense, leg, chi_max, chi_min, degeneracy_tol, trunc_cut, svd_min, minimize_error):
         n = leg.dim
         with self._ctx():
             keep = torch.zeros(max(n, 1), dtype=torch.uint8, device=self.device)

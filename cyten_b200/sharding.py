@@ -1,0 +1,270 @@
+"""Multi-GPU sharding of the abelian hot path: one process per GPU, charge sectors partitioned by
+longest-processing-time-first (LPT) on flop cost.
+
+The unit of distribution is the *block*: a block-sparse tensor that holds only a subset of its
+symmetry-allowed blocks is still a valid tensor, and the full tensor is the SUM over ranks of the
+rank-local subsets.  Every hot-path operation is (bi)linear in the blocks, so
+
+* ``tdot`` / ``compose``: shard the operand along the sectors of a leg that stays OPEN -- every output
+  block (``abelian.cpp:1424-1459``: independent per (row_a, col_b)) is then computed by exactly one rank,
+  with no data-path collective;
+* a chain of contractions (the DMRG ``H_eff`` matvec) stays rank-local for as long as the sharding leg
+  stays open; when it is finally contracted the rank-local results are partial sums over that leg's
+  sectors and ONE ``all_reduce`` on the common arena layout finishes the chain;
+* ``svd`` / ``qr`` / ``eigh``: one independent factorisation per coupled sector
+  (``abelian.cpp:3499-3541``), LPT by ``m*n*min(m,n)``; the only exchange step is the ``all_gather`` of the
+  per-sector singular values (<= d*chi doubles) so that every rank evaluates the identical global cut
+  (``tensor_backend.cpp:166-241``) and keeps the same per-sector dimensions.
+
+``torch.distributed`` (NCCL over NVLink on the GPUs, gloo in the CPU tests) is only the plumbing.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import tensors as ct
+from .backend import B200AbelianBackend, conventional_leg_order, _c_strides
+from .data import AbelianBackendData
+from .spaces import TensorProduct
+from .tensors import DiagonalTensor, SymmetricTensor, valid_block_inds
+
+
+# ---- LPT ------------------------------------------------------------------------------------------
+def lpt_assign(costs, nparts: int) -> np.ndarray:
+    """Greedy longest-processing-time-first: items by descending cost (ties: lower index first) go to
+    the currently least-loaded part (ties: lower part id).  Deterministic, so every rank computes the
+    same assignment without communication.  Returns ``owner[len(costs)]``."""
+    costs = np.asarray(costs, dtype=np.float64)
+    order = np.lexsort((np.arange(len(costs)), -costs))
+    load = np.zeros(nparts, dtype=np.float64)
+    owner = np.zeros(len(costs), dtype=np.int64)
+    for i in order:
+        p = int(np.argmin(load))
+        owner[i] = p
+        load[p] += costs[i]
+    return owner
+
+
+def lpt_imbalance(costs, owner, nparts: int) -> float:
+    """max load / mean load (1.0 = perfect)."""
+    load = np.bincount(owner, weights=np.asarray(costs, dtype=np.float64), minlength=nparts)
+    return float(load.max() / max(load.mean(), 1e-300))
+
+
+class ProcessGroup:
+    """Rank / world / group triple; ``group=None`` with world 1 is the single-GPU case."""
+
+    def __init__(self, group=None):
+        self.group = group
+        if group is None and not (dist.is_available() and dist.is_initialized()):
+            self.rank, self.world = 0, 1
+        else:
+            self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+
+    def all_reduce(self, t: torch.Tensor):
+        if self.world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        return t
+
+    def all_gather_into(self, out: torch.Tensor, t: torch.Tensor):
+        if self.world > 1:
+            dist.all_gather_into_tensor(out, t, group=self.group)
+        else:
+            out.copy_(t)
+        return out
+
+
+def attach_process_group(backend: B200AbelianBackend, group=None) -> ProcessGroup:
+    pg = ProcessGroup(group)
+    backend.shard = pg
+    return pg
+
+
+# ---- block subsets ---------------------------------------------------------------------------------
+def take_blocks(T: SymmetricTensor, which) -> SymmetricTensor:
+    """The tensor holding only blocks ``which`` (ascending positions) of T, in a new arena (one batched
+    copy launch)."""
+    be = T.backend
+    which = np.asarray(which, dtype=np.int64)
+    d = T.data
+    res = be._empty(d.dtype, be.device, d.block_inds[which], d.shapes[which])
+    if len(which):
+        sizes = d.sizes[which].reshape(-1, 1)
+        ones = np.ones_like(sizes)
+        jobs = be._make_jobs(d.offsets[which], res.offsets, sizes, ones, ones)
+        be._copy_blocks(d.buf, res.buf, jobs, d.cyb_dtype)
+    return SymmetricTensor(res, T.codomain, T.domain, be, T.labels)
+
+
+def sector_owner_of_leg(T: SymmetricTensor, leg, world: int):
+    """LPT owner of every sector of leg ``leg`` (label or index) of T; cost of a sector = number of
+    elements in the blocks carrying it (proportional to the flops those blocks cause downstream)."""
+    ax = T.get_leg_idcs([leg])[0]
+    nsec = conventional_leg_order(T.codomain, T.domain)[ax].num_sectors
+    cost = np.bincount(T.data.block_inds[:, ax], weights=T.data.sizes.astype(np.float64), minlength=nsec)
+    return ax, lpt_assign(cost, world), cost
+
+
+def shard_by_leg(T: SymmetricTensor, leg, pg: ProcessGroup):
+    """Rank-local part of T: the blocks whose sector on ``leg`` is owned by this rank.
+    Returns (local tensor, owner table of the leg's sectors)."""
+    ax, owner, _ = sector_owner_of_leg(T, leg, pg.world)
+    mine = np.nonzero(owner[T.data.block_inds[:, ax]] == pg.rank)[0]
+    return take_blocks(T, mine), owner
+
+
+def expand_to_full(T: SymmetricTensor) -> SymmetricTensor:
+    """T re-laid-out on the arena of ALL symmetry-allowed blocks (valid_block_inds,
+    abelian.cpp:329-399), absent blocks zero: the layout every rank shares."""
+    be = T.backend
+    full_bi = valid_block_inds(T.codomain, T.domain)
+    legs = conventional_leg_order(T.codomain, T.domain)
+    shapes = (np.stack([np.asarray(l.multiplicities)[full_bi[:, ax]] for ax, l in enumerate(legs)], axis=1)
+              if legs else np.zeros((len(full_bi), 0), np.int64))
+    res = be._empty(T.data.dtype, be.device, full_bi, shapes, zero=True)
+    d = T.data
+    if d.num_blocks:
+        # position of every local block in the full (lexsorted) list: packed-key lookup
+        nsec = np.asarray([l.num_sectors for l in legs], dtype=np.int64)
+        strides = np.concatenate([[1], np.cumprod(nsec[:-1])]).astype(np.int64)   # last column primary
+        key_full = full_bi @ strides
+        pos = np.searchsorted(key_full, d.block_inds @ strides)
+        if not np.array_equal(key_full[pos], d.block_inds @ strides):
+            raise ValueError("expand_to_full: tensor has blocks that violate the charge rule")
+        sizes = d.sizes.reshape(-1, 1)
+        ones = np.ones_like(sizes)
+        jobs = be._make_jobs(d.offsets, res.offsets[pos], sizes, ones, ones)
+        be._copy_blocks(d.buf, res.buf, jobs, d.cyb_dtype)
+    return SymmetricTensor(res, T.codomain, T.domain, be, T.labels)
+
+
+def all_reduce_blocks(T: SymmetricTensor, pg: ProcessGroup) -> SymmetricTensor:
+    """Sum of the rank-local tensors, replicated on every rank (one all_reduce of the arena)."""
+    full = expand_to_full(T)
+    if not T.backend.dry_run:
+        pg.all_reduce(full.data.buf)
+    return full
+
+
+def all_gather_blocks(T: SymmetricTensor, pg: ProcessGroup) -> SymmetricTensor:
+    """Replicates a tensor whose blocks are DISJOINTLY distributed over the ranks.  With disjoint
+    supports the sum equals the union, and x + 0 is exact, so this is the all_reduce above."""
+    return all_reduce_blocks(T, pg)
+
+
+# ---- sharded operations ----------------------------------------------------------------------------
+def tdot_sharded(A: SymmetricTensor, B: SymmetricTensor, legs1, legs2, pg: ProcessGroup, shard_leg=None):
+    """``tdot`` with the OUTPUT blocks partitioned over the ranks: B is sharded along the sectors of one
+    of its open legs (default: its last open leg), so each output block is computed by exactly one rank
+    (no collective).  Returns the rank-local part of the result."""
+    l2 = B.get_leg_idcs(legs2 if isinstance(legs2, (list, tuple)) else [legs2])
+    if shard_leg is None:
+        shard_leg = [i for i in range(B.num_legs) if i not in l2][-1]
+    B_loc, _ = shard_by_leg(B, shard_leg, pg)
+    return ct.tdot(A, B_loc, legs1, legs2)
+
+
+class ShardedHEffective:
+    """The two-site H_eff matvec (d_dmrg.py:70-88) on a theta sharded along ``vR``: the first three
+    contractions leave ``vR`` open and are rank-local; the last one contracts ``vR`` with RP, so each
+    rank holds a partial sum over its ``vR`` sectors and one all_reduce finishes the matvec."""
+
+    def __init__(self, H, pg: ProcessGroup, shard_leg="vR"):
+        self.H, self.pg, self.shard_leg = H, pg, shard_leg
+
+    def shard(self, theta: SymmetricTensor) -> SymmetricTensor:
+        return shard_by_leg(theta, self.shard_leg, self.pg)[0]
+
+    def matvec_local(self, theta_local: SymmetricTensor) -> SymmetricTensor:
+        return self.H.matvec(theta_local)
+
+    def matvec(self, theta_local: SymmetricTensor) -> SymmetricTensor:
+        """Replicated ``H_eff . theta`` from the rank-local shard of theta."""
+        return all_reduce_blocks(self.matvec_local(theta_local), self.pg)
+
+
+def svd_costs(tens: SymmetricTensor) -> np.ndarray:
+    s = tens.data.shapes
+    return (s[:, 0] * s[:, 1] * np.minimum(s[:, 0], s[:, 1])).astype(np.float64)
+
+
+def gather_singular_values(be: B200AbelianBackend, s: AbelianBackendData, leg, owner_of_sector, pg: ProcessGroup):
+    """NCCL ``all_gather`` of the per-sector singular values (section 8(e)): every rank contributes its
+    sectors' values as one padded segment; the result is the dense S vector over ``leg`` (internal basis
+    order, diagonal_tensor_to_block, abelian.cpp:1678-1692), identical on every rank."""
+    mults = np.asarray(leg.multiplicities, dtype=np.int64)
+    nsec = leg.num_sectors
+    per_rank = [np.nonzero(owner_of_sector == r)[0] for r in range(pg.world)]
+    seg_len = [int(mults[idx].sum()) for idx in per_rank]
+    pad = max(max(seg_len), 1)
+    send = torch.zeros(pad, dtype=torch.float64, device=be.device)
+    # pack my blocks in ascending sector order
+    mine = per_rank[pg.rank]
+    start_in_seg = {int(sec): int(o) for sec, o in zip(mine, np.concatenate([[0], np.cumsum(mults[mine])])[:-1])}
+    if s.num_blocks:
+        sizes = s.shapes[:, :1]
+        dst = np.asarray([start_in_seg[int(sec)] for sec in s.block_inds[:, 0]], dtype=np.int64)
+        ones = np.ones_like(sizes)
+        be._copy_blocks(s.buf, send, be._make_jobs(s.offsets, dst, sizes, ones, ones), 0)
+    recv = torch.empty(pad * pg.world, dtype=torch.float64, device=be.device)
+    pg.all_gather_into(recv, send)
+    dense = torch.zeros(max(leg.dim, 1), dtype=torch.float64, device=be.device)
+    src, dst, sz = [], [], []
+    for r, idx in enumerate(per_rank):
+        o = 0
+        for sec in idx:
+            src.append(r * pad + o)
+            dst.append(int(leg.slices[sec, 0]))
+            sz.append(int(mults[sec]))
+            o += int(mults[sec])
+    if sz:
+        sz = np.asarray(sz, dtype=np.int64).reshape(-1, 1)
+        ones = np.ones_like(sz)
+        be._copy_blocks(recv, dense, be._make_jobs(np.asarray(src), np.asarray(dst), sz, ones, ones), 0)
+    return dense
+
+
+def truncated_svd_sharded(T: SymmetricTensor, pg: ProcessGroup, new_labels=("a", "b", "c", "d"),
+                          new_leg_dual=False, normalize_to=None, chi_max=None, chi_min=1, degeneracy_tol=0.0,
+                          trunc_cut=0.0, svd_min=0.0):
+    """``truncated_svd`` (decompositions.cpp:672-709) with the coupled sectors LPT-partitioned over the
+    ranks.  T is replicated; each rank factorises its sectors, the singular values are all-gathered, the
+    global cut is evaluated identically everywhere, and each rank projects ITS blocks of U, S, Vh.
+    Returns rank-local (U, S, Vh) (disjoint block sets; ``all_gather_blocks`` replicates them), err,
+    renormalize, and the sector owner table."""
+    be: B200AbelianBackend = T.backend
+    tens, new_co_domain, cc, cd = ct._decomposition_prepare(T, new_leg_dual)
+    leg = new_co_domain.factors[0]
+    rows = be._matched_sectors(tens, leg)
+    # cost per new-leg sector; sectors without a theta block cost nothing and go to rank 0's tail
+    cost = np.zeros(leg.num_sectors, dtype=np.float64)
+    blk_cost = svd_costs(tens)
+    for (j, n, k, i) in rows:
+        if i >= 0:
+            cost[n] = blk_cost[i]
+    owner = lpt_assign(cost, pg.world)
+    owned_rows = [t for t, r in enumerate(rows) if owner[r[1]] == pg.rank]
+    u, s, vh = be.svd(tens, new_co_domain, only_rows=owned_rows)
+    dense = gather_singular_values(be, s, leg, owner, pg)
+    keep, small_leg, err, new_norm, S_norm = be.truncate_dense(dense, leg, chi_max=chi_max, chi_min=chi_min,
+                                                               degeneracy_tol=degeneracy_tol, trunc_cut=trunc_cut,
+                                                               svd_min=svd_min)
+    u = be.apply_keep_mask(u, 1, 1, leg, keep, small_leg)
+    s = be.apply_keep_mask(s, 0, 0, leg, keep, small_leg)
+    vh = be.apply_keep_mask(vh, 0, 0, leg, keep, small_leg)
+    small = TensorProduct([small_leg])
+    a, b, c, d = new_labels
+    U = SymmetricTensor(u, tens.codomain, small, be, [*tens.labels[:1], a])
+    S = DiagonalTensor(s, small_leg, be, [b, c])
+    Vh = SymmetricTensor(vh, small, tens.domain, be, [d, *tens.labels[1:]])
+    renormalize = 1.0
+    if normalize_to is not None:
+        renormalize = normalize_to / S_norm / new_norm
+        be.scale_inplace(s, renormalize)
+    if cc:
+        U = ct.split_legs(U, [0])
+    if cd:
+        Vh = ct.split_legs(Vh, [1])
+    return U, S, Vh, err, renormalize, owner

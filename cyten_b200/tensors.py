@@ -273,7 +273,7 @@ def svd(T: SymmetricTensor, new_labels=("a", "b", "c", "d"), new_leg_dual=False)
 
 def truncated_svd(T: SymmetricTensor, new_labels=("a", "b", "c", "d"), new_leg_dual=False,
                   normalize_to=None, chi_max=None, chi_min=1, degeneracy_tol=0.0, trunc_cut=0.0,
-                  svd_min=0.0, gather=None):
+                  svd_min=0.0):
     """decompositions.cpp:672-709: svd, truncation of the NORMALISED singular values with one global
     cut, projection of U, S, Vh.  Returns (U, S, Vh, err, renormalize)."""
     tens, new_co_domain, cc, cd = _decomposition_prepare(T, new_leg_dual)
@@ -283,7 +283,7 @@ def truncated_svd(T: SymmetricTensor, new_labels=("a", "b", "c", "d"), new_leg_d
     S_norm = be.norm(s)
     keep, small_leg, err, new_norm = be.truncate_singular_values(
         s, leg, chi_max=chi_max, chi_min=chi_min, degeneracy_tol=degeneracy_tol, trunc_cut=trunc_cut,
-        svd_min=svd_min, scale=(1.0 / S_norm if S_norm > 0 else 1.0), gather=gather)
+        svd_min=svd_min, scale=(1.0 / S_norm if S_norm > 0 else 1.0))
     u = be.apply_keep_mask(u, 1, 1, leg, keep, small_leg)
     s = be.apply_keep_mask(s, 0, 0, leg, keep, small_leg)
     vh = be.apply_keep_mask(vh, 0, 0, leg, keep, small_leg)
@@ -295,9 +295,7 @@ def truncated_svd(T: SymmetricTensor, new_labels=("a", "b", "c", "d"), new_leg_d
     renormalize = 1.0
     if normalize_to is not None:
         renormalize = normalize_to / S_norm / new_norm
-        from .data import ptr
-        be._call("cyb_axpby", ptr(s.buf), ptr(s.buf), s.buf.numel(), s.cyb_dtype, float(renormalize), 0.0,
-                 be._stream())
+        be.scale_inplace(s, renormalize)
     if cc:
         U = split_legs(U, [0])
     if cd:
