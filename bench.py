@@ -135,6 +135,50 @@ def cpu_matvec_time(chi, kind, repeats=1):
     return best
 
 
+def build_reference_theta(chi):
+    """theta = tdot(A, B) of two random MPS tensors on the reference's numpy backend (same blocks as the
+    GPU arm: workloads.random_blocks seeds 7 / 8)."""
+    sys.path.insert(0, str(ROOT / "oracle" / "_ref"))
+    import cyten as ct
+    from cyten_b200.workloads import CONFIG_LEGS, random_blocks, u1_bond_leg, u1_phys_leg
+    be = ct.get_backend("abelian", "numpy")
+    sym = ct.u1_symmetry
+    Q, sigma = CONFIG_LEGS[chi]
+    v, p = u1_bond_leg(chi, Q, sigma), u1_phys_leg()
+
+    def conv(leg):
+        return ct.ElementarySpace.from_defining_sectors(sym, leg.defining_sectors, leg.multiplicities, is_dual=leg.is_dual)
+    ts = []
+    for seed in (7, 8):
+        bi, blocks = random_blocks([v, p], [v], seed)
+        data = ct.backends.AbelianBackendData(dtype=ct.Dtype.float64, device="cpu",
+                                              blocks=[be.block_backend.as_block(b) for b in blocks],
+                                              block_inds=ct.backends.BlockInds(bi) if hasattr(ct.backends, "BlockInds") else bi,
+                                              is_sorted=True)
+        ts.append(ct.SymmetricTensor(data, [conv(v), conv(p)], [conv(v)], backend=be, labels=["vL", "p", "vR"]))
+    return ct.tdot(ts[0], ts[1], ["vR"], ["vL"]), ct
+
+
+def cpu_svd_time(chi, kind):
+    """Seconds for one truncated_svd(theta, chi_max=chi, svd_min=1e-14) on the host cores."""
+    if kind == "reference":
+        theta, ct = build_reference_theta(chi)
+        t0 = time.perf_counter()
+        ct.truncated_svd(theta, chi_max=chi, svd_min=1e-14)
+        return time.perf_counter() - t0
+    from cyten_b200 import tensors as ops
+    from cyten_b200.backend import B200AbelianBackend
+    from cyten_b200.workloads import CONFIG_LEGS, mps_tensor, u1_bond_leg, u1_phys_leg
+    from oracle import cabi_numpy
+    be = B200AbelianBackend("cpu", _library=cabi_numpy)
+    Q, sigma = CONFIG_LEGS[chi]
+    v, p = u1_bond_leg(chi, Q, sigma), u1_phys_leg()
+    th = ops.tdot(mps_tensor(v, p, v, be, seed=7), mps_tensor(v, p, v, be, seed=8), [2], [0])
+    t0 = time.perf_counter()
+    ops.truncated_svd(th, chi_max=chi, svd_min=1e-14)
+    return time.perf_counter() - t0
+
+
 def reference_available():
     return bool(list((ROOT / "oracle" / "_ref" / "cyten").glob("_core*.so")))
 
@@ -164,6 +208,9 @@ def run_reference(args):
         H.matvec(theta)
     dt = (time.perf_counter() - t0) / steps
     val = flops / dt / 1e9
+    svd_ms = None
+    if not args.no_svd:
+        svd_ms = cpu_svd_time(args.svd_chi or chi, kind) * 1e3
     line = {"metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": min(args.warmup, 1),
             "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "impl": "reference",
@@ -171,7 +218,7 @@ def run_reference(args):
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind,
                              "sample": f"{steps} matvec(s) at chi={chi} on the host cores"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
+            "gpu_launches": 0, "svd_ms": svd_ms}
     print(json.dumps(line))
 
 
@@ -211,9 +258,9 @@ def run_b200(args):
     import torch
     import torch.distributed as dist
     from cyten_b200 import tensors as ct
+    from cyten_b200 import sharding as sh
     from cyten_b200.backend import B200AbelianBackend
-    from cyten_b200.workloads import build_heff, random_blocks, CONFIG_LEGS
-    from cyten_b200.tensors import SymmetricTensor
+    from cyten_b200.workloads import build_heff, CONFIG_LEGS
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -223,24 +270,38 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     be = B200AbelianBackend(dev)
-    if world > 1:
-        from cyten_b200.sharding import attach_process_group
-        attach_process_group(be, dist.group.WORLD)
+    pg = sh.attach_process_group(be, dist.group.WORLD if world > 1 else None)
     chi = args.chi
-    H, theta, host, sp = build_heff(chi, be)
-    flops = None
+    H, theta_full, host, sp = build_heff(chi, be)
+    SH = sh.ShardedHEffective(H, pg)
+    # multi-GPU: theta lives sharded along the sectors of vR (LPT by block volume); the matvec chain is
+    # rank-local until vR is contracted, then one all_reduce of the (small) result arena
+    theta = SH.shard(theta_full) if world > 1 else theta_full
+
+    def step():
+        return SH.matvec(theta) if world > 1 else H.matvec(theta)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # warm-up (also yields the algorithmic flop count from the device planner)
+    def total_over_ranks(x, op=None):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=op or dist.ReduceOp.SUM)
+        return float(t.item())
+
+    # cold pass (plans are built on device here) -- timed separately, reported as ms_first_call
+    barrier()
+    t0 = time.perf_counter()
     be.plan_mkn = []
+    y = step()
+    torch.cuda.synchronize()
+    first_call_ms = (time.perf_counter() - t0) * 1e3
+    flops = total_over_ranks(2.0 * float(sum(be.plan_mkn)))     # algorithmic flops of the whole job
     for _ in range(max(args.warmup, 3)):
-        be.plan_mkn = []
-        y = H.matvec(theta)
-    flops = 2.0 * float(sum(be.plan_mkn))
+        y = step()
     be.plan_mkn = None
     l2_flush = torch.empty(192 * 1024 * 1024, dtype=torch.uint8, device=dev)
 
@@ -251,54 +312,63 @@ def run_b200(args):
     be.gemm_events = []
     be.gemm_event_flops = []
     be.launches = 0
-    step_ms = []
+    step_ev = []
     barrier()
     for _ in range(args.steps):
         l2_flush.zero_()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        y = H.matvec(theta)
+        y = step()
         e1.record()
-        step_ms.append((e0, e1))
+        step_ev.append((e0, e1))
     barrier()
     launches = be.launches
-    total_ms = sum(a.elapsed_time(b) for a, b in step_ms)
+    total_ms = sum(a.elapsed_time(b) for a, b in step_ev)
     gemm_ms = [a.elapsed_time(b) for a, b in be.gemm_events]
-    gemm_flops = be.gemm_event_flops
+    gemm_flops = list(be.gemm_event_flops)
     be.gemm_events = None
-    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms = float(t.item())
+    total_ms = total_over_ranks(total_ms, dist.ReduceOp.MAX if world > 1 else None)
     ms_per_step = total_ms / args.steps
     value = flops / (ms_per_step * 1e-3) / 1e9
 
+    # ---- the same step with the plan cache disabled (bookkeeping recomputed on device every call) ----
+    be.plan_cache = False
+    step()
+    barrier()
+    ev = []
+    for _ in range(min(args.steps, 3)):
+        l2_flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        step()
+        e1.record()
+        ev.append((e0, e1))
+    barrier()
+    noplan_ms = total_over_ranks(sum(a.elapsed_time(b) for a, b in ev) / len(ev), dist.ReduceOp.MAX if world > 1 else None)
+    be.plan_cache = True
+
     # ---- end to end: theta from pinned host memory every step, result back to the host ----
-    bi_t, blocks_t = host["theta"]
     pinned = torch.empty(theta.data.buf.numel(), dtype=torch.float64).pin_memory()
-    hostbuf = pinned.numpy()
-    for b, off in zip(blocks_t, theta.data.offsets):
-        hostbuf[off:off + b.size] = b.reshape(-1)
+    pinned.copy_(theta.data.buf)
+    torch.cuda.synchronize()
     out_host = None
-    e2e_steps = max(1, min(args.steps, 5))
+    e2e_steps = max(1, min(args.steps, 10))
+    step()
     barrier()
     t0 = time.perf_counter()
     h2d = d2h = 0
     for _ in range(e2e_steps):
         theta.data.buf.copy_(pinned, non_blocking=True)
         h2d = pinned.numel() * 8
-        y = H.matvec(theta)
+        y = step()
         if out_host is None or out_host.numel() != y.data.buf.numel():
             out_host = torch.empty(y.data.buf.numel(), dtype=torch.float64).pin_memory()
         out_host.copy_(y.data.buf, non_blocking=True)
         d2h = out_host.numel() * 8
         torch.cuda.synchronize()
     barrier()
-    e2e_s = (time.perf_counter() - t0) / e2e_steps
-    te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_val = flops / float(te.item()) / 1e9
+    e2e_s = total_over_ranks((time.perf_counter() - t0) / e2e_steps, dist.ReduceOp.MAX if world > 1 else None)
+    e2e_val = flops / e2e_s / 1e9
 
     # ---- truncated SVD of theta = tdot(B, B) at chi (BASELINE config 3) ----
     svd_ms = svd_info = None
@@ -309,46 +379,57 @@ def run_b200(args):
         v, p = u1_bond_leg(schi, Q, sigma), u1_phys_leg()
         A, B = mps_tensor(v, p, v, be, seed=7), mps_tensor(v, p, v, be, seed=8)
         th = ct.tdot(A, B, [2], [0])
-        gather = getattr(be, "gather_hook", None)
-        ct.truncated_svd(th, chi_max=schi, svd_min=1e-14, gather=gather)   # warm-up
+        th.data.buf
+
+        def do_svd():
+            if world > 1:
+                return sh.truncated_svd_sharded(th, pg, chi_max=schi, svd_min=1e-14)[:5]
+            return ct.truncated_svd(th, chi_max=schi, svd_min=1e-14)
+        do_svd()   # warm-up
         times = []
-        for _ in range(2):
+        for _ in range(3):
             barrier()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-            U, S, Vh, err, _ = ct.truncated_svd(th, chi_max=schi, svd_min=1e-14, gather=gather)
+            U, S, Vh, err, _ = do_svd()
             e1.record()
             barrier()
             times.append(e0.elapsed_time(e1))
-        ts = torch.tensor([min(times)], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(ts, op=dist.ReduceOp.MAX)
-        svd_ms = float(ts.item())
-        svd_info = {"chi": schi, "kept": int(S.data.shapes.sum()), "err": err,
-                    "sweeps_max": int(be.last_info.abs().max().item()) if be.last_info is not None else None}
+        svd_ms = total_over_ranks(min(times), dist.ReduceOp.MAX if world > 1 else None)
+        kept = int(total_over_ranks(float(S.data.shapes.sum()))) if world > 1 else int(S.data.shapes.sum())
+        svd_info = {"chi": schi, "kept": kept, "err": err,
+                    "sweeps_max": int(be.last_info.abs().max().item()) if be.last_info is not None and be.last_info.numel() else None}
     clocks = sampler.stop() if rank == 0 else None
 
     if rank == 0:
         # ---- roofline of the dominant kernel (grouped DMMA GEMM): FP64 tensor peak ----
-        g_ms = float(np.mean(gemm_ms)) if gemm_ms else None
-        g_fl = float(np.mean(gemm_flops)) if gemm_flops else None
+        # per-launch mean over the launches that carry > 5 % of the step's flops (the tensor-core
+        # GEMMs; the MPO applications are HBM-bound and run on the streaming kernel)
+        fat = [(m, f) for m, f in zip(gemm_ms, gemm_flops) if f > 0.05 * max(gemm_flops)] if gemm_ms else []
         peak_tf, peak_src = fp64_peak_tflops(dev)
         roof = None
-        if g_ms:
+        if fat:
+            g_ms = float(np.mean([m for m, _ in fat]))
+            g_fl = float(np.mean([f for _, f in fat]))
             ach = g_fl / (g_ms * 1e-3) / 1e12
             roof = {"bound": "tensor", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf,
                     "traffic": None, "kernel": "grouped_gemm_kernel (DMMA f64)", "peak_source": peak_src,
+                    "launch_ms": g_ms, "launch_flops": g_fl,
                     "gemm_share_of_step": sum(gemm_ms) / total_ms if total_ms else None}
         cpu = None
         if not args.no_cpu_baseline and world == 1:
             cpu = cpu_baseline(args)
-        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3) + 1,
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic",
                 "config": {"workload": f"U(1) DMRG two-site H_eff matvec (4 tdot + 5 permute_legs), chi={chi}, D=5, d=2, float64",
                            "l2": "192 MiB buffer written between timed steps", "flops_per_step": flops,
-                           "sharding": "output sectors LPT over ranks + allgather" if world > 1 else "single GPU"},
-                "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+                           "plan_cache": {"enabled": True, "hits": be.plan_hits, "misses": be.plan_misses,
+                                          "ms_per_step_without": noplan_ms, "ms_first_call": first_call_ms},
+                           "sharding": ("theta sharded along vR sectors (LPT), rank-local chain, one all_reduce per matvec"
+                                        if world > 1 else "single GPU")},
+                "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "ms_per_step": e2e_s * 1e3},
                 "gpu_launches": launches, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
                 "svd_ms": svd_ms, "svd": svd_info}
         print(json.dumps(line))
@@ -385,8 +466,15 @@ def cpu_baseline(args):
         kind = "port"
         dt = cpu_matvec_time(chi, kind)
     fl = flops_of_matvec(chi)
-    return {"value": fl / dt / 1e9, "unit": UNIT, "cores": cores, "kind": kind, "ms_per_step": dt * 1e3,
-            "sample": f"1 H_eff matvec at chi={chi} (after 1 warm-up), AbelianBackend+NumpyBlockBackend on the host cores"}
+    svd_ms = None
+    if not args.no_svd:
+        try:
+            svd_ms = cpu_svd_time(args.svd_chi or chi, kind) * 1e3
+        except Exception as e:
+            svd_ms = f"failed: {e!r}"
+    return {"value": fl / dt / 1e9, "unit": UNIT, "cores": cores, "kind": kind, "ms_per_step": dt * 1e3, "svd_ms": svd_ms,
+            "sample": f"1 H_eff matvec at chi={chi} (after 1 warm-up) + 1 truncated_svd(theta) at chi={args.svd_chi or chi}, "
+                      "AbelianBackend+NumpyBlockBackend on the host cores"}
 
 
 def main():

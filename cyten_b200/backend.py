@@ -55,9 +55,21 @@ class B200AbelianBackend:
             _lib.load()
             self._lib_call = _lib.call
             self._plan_ws = lambda na, nb: _lib.load().cyb_compose_plan_workspace(na, nb)
+            self._copy_ws = lambda n: _lib.load().cyb_copy_blocks_workspace(n)
+            self._gemm_ws = lambda n: _lib.load().cyb_grouped_gemm_workspace(n)
         else:
             self._lib_call = _library.call
             self._plan_ws = _library.cyb_compose_plan_workspace
+            self._copy_ws = _library.cyb_copy_blocks_workspace
+            self._gemm_ws = _library.cyb_grouped_gemm_workspace
+        # Plans: the integer bookkeeping of an operation (sorted block_inds, copy job lists, GEMM work
+        # lists and tile schedules) depends only on the structure of its operands (block_inds + legs),
+        # not on the block contents.  It is computed ON DEVICE on the first call and replayed for every
+        # later call with the same structure (the Lanczos / sweep loops of DMRG call the same
+        # contraction thousands of times); a replay is pure kernel launches with no host<->device sync.
+        self.plan_cache = True
+        self._plans = {}
+        self.plan_hits = self.plan_misses = 0
         self.launches = 0   # number of cyten_b200 kernel-launching C-ABI calls (bench bookkeeping)
         self.last_info = None
         self.dry_run = False        # plan-only mode: tables are computed, arenas are not touched
@@ -123,6 +135,47 @@ class B200AbelianBackend:
             self._call("cyb_copy_blocks", ptr(src_buf), ptr(dst_buf), ptr(d_jobs), njobs, cyb_dtype,
                        int(conj), C.c_void_p(0), 0, self._stream())
 
+    def _prepare_copy(self, jobs: np.ndarray):
+        """Uploads a job list and builds its device schedule once; returns (njobs, workspace)."""
+        njobs = len(jobs)
+        if njobs == 0 or self.dry_run:
+            return (0, None)
+        with self._ctx():
+            d_jobs = to_device_i64(jobs, self.device)
+            nbytes = int(self._copy_ws(njobs))
+            d_ws = torch.empty(nbytes // 8 + 1, dtype=torch.int64, device=self.device)
+            self._call("cyb_copy_blocks_prepare", ptr(d_jobs), njobs, ptr(d_ws), nbytes, self._stream())
+        return (njobs, d_ws)
+
+    def _run_copy(self, src_buf, dst_buf, prepared, cyb_dtype: int, conj: bool = False):
+        njobs, d_ws = prepared
+        if njobs == 0 or self.dry_run:
+            return
+        with self._ctx():
+            self._call("cyb_copy_blocks_run", ptr(src_buf), ptr(dst_buf), ptr(d_ws), njobs, cyb_dtype, int(conj),
+                       self._stream())
+
+    def _plan_get(self, key):
+        if not self.plan_cache:
+            return None
+        plan = self._plans.get(key)
+        if plan is None:
+            self.plan_misses += 1
+        else:
+            self.plan_hits += 1
+        return plan
+
+    def _plan_put(self, key, plan):
+        if self.plan_cache:
+            self._plans[key] = plan
+        return plan
+
+    def _new_buf(self, dtype: str, total: int) -> torch.Tensor:
+        tdt = torch.complex128 if dtype == "complex128" else torch.float64
+        if self.dry_run:
+            return torch.empty(ALIGN, dtype=tdt)
+        return torch.empty(max(int(total), ALIGN), dtype=tdt, device=self.device)
+
     @staticmethod
     def _make_jobs(src_off, dst_off, shapes, src_strides, dst_strides) -> np.ndarray:
         n, r = shapes.shape
@@ -142,23 +195,49 @@ class B200AbelianBackend:
     # ------------------------------------------------------------------------------------------
     def permute_legs(self, a, codomain_idcs, domain_idcs, new_codomain=None, new_domain=None,
                      mixes_codomain_domain=None, levels=None, bend_right=None) -> AbelianBackendData:
-        """abelian.cpp:988-1006: permute the axes of every block, the columns of block_inds, re-sort."""
+        """abelian.cpp:988-1006: permute the axes of every block, the columns of block_inds, re-sort.
+
+        The integer part (column permutation + device lexsort + job list) is a cached plan; the data
+        movement is deferred until a consumer asks for the arena (the reference's numpy blocks are lazy
+        views at the same place), so that ``compose`` can fold it into its own operand re-layout.  A
+        permutation that leaves the block axis order unchanged (legs only bent between codomain and
+        domain) moves no data at all."""
         data: AbelianBackendData = a.data
         axes_perm = [int(i) for i in codomain_idcs] + [int(i) for i in reversed(list(domain_idcs))]
         r = data.block_inds.shape[1]
         if sorted(axes_perm) != list(range(r)):
             raise ValueError("codomain_idcs + domain_idcs must be a permutation of the legs")
-        new_bi = data.block_inds[:, axes_perm]
-        order = self.lexsort(new_bi)
-        new_bi = new_bi[order]
-        old_shapes = data.shapes
-        new_shapes = old_shapes[:, axes_perm][order]
-        res = self._empty(data.dtype, self.device, new_bi, new_shapes)
-        if data.num_blocks:
-            src_strides = _c_strides(old_shapes)[:, axes_perm][order]
-            jobs = self._make_jobs(data.offsets[order], res.offsets, new_shapes, src_strides,
-                                   _c_strides(new_shapes))
-            self._copy_blocks(data.buf, res.buf, jobs, data.cyb_dtype)
+        if axes_perm == list(range(r)):
+            if data.is_pending:
+                data.buf   # materialise once, the alias shares the arena
+            res = AbelianBackendData(data.dtype, self.device, data.buf, data.block_inds, data.offsets,
+                                     data.shapes, sig=data._sig)
+            res._dev_tables = data._dev_tables
+            return res
+        key = ("permute", data.sig, tuple(axes_perm))
+        plan = self._plan_get(key)
+        if plan is None:
+            new_bi = data.block_inds[:, axes_perm]
+            order = self.lexsort(new_bi)
+            new_bi = new_bi[order]
+            old_shapes = data.shapes
+            new_shapes = old_shapes[:, axes_perm][order]
+            sizes = np.prod(new_shapes, axis=1).astype(np.int64) if r else np.ones(len(new_shapes), np.int64)
+            offs, total = aligned_offsets(sizes)
+            jobs = self._make_jobs(data.offsets[order], offs, new_shapes,
+                                   _c_strides(old_shapes)[:, axes_perm][order], _c_strides(new_shapes))
+            plan = self._plan_put(key, dict(bi=new_bi, shapes=new_shapes, offsets=offs, total=total, order=order,
+                                            copy=self._prepare_copy(jobs), sig=None))
+        backend = self
+
+        def materialise():
+            buf = backend._new_buf(data.dtype, plan["total"])
+            backend._run_copy(data.buf, buf, plan["copy"], data.cyb_dtype)
+            return buf
+        res = AbelianBackendData(data.dtype, self.device, None, plan["bi"], plan["offsets"], plan["shapes"],
+                                 sig=plan["sig"], pending=(materialise, (data, tuple(axes_perm), plan["order"])))
+        if plan["sig"] is None:
+            plan["sig"] = res.sig
         return res
 
     # ------------------------------------------------------------------------------------------
@@ -417,7 +496,8 @@ class B200AbelianBackend:
 
     def compose(self, a, b, subset=None) -> AbelianBackendData:
         """abelian.cpp:1222-1234 + 1238-1469: block-sparse matrix product over the matched
-        contracted sectors = plan kernel + ONE grouped DMMA GEMM launch."""
+        contracted sectors = (cached) device plan + ONE grouped GEMM call (DMMA kernel for the blocks
+        with M > 8, streaming kernel for the skinny ones)."""
         A: AbelianBackendData = a.data
         B: AbelianBackendData = b.data
         a_keep, ncontr, b_keep = a.codomain.num_factors, a.domain.num_factors, b.domain.num_factors
@@ -434,47 +514,90 @@ class B200AbelianBackend:
         if B.dtype != res_dtype:
             b = _Retyped(b, self._to_dtype(B, res_dtype))
             B = b.data
-        if ncontr > 1:
-            # A's trailing axes are the contracted legs in REVERSED order; bring B's leading axes
-            # into the same order (abelian.cpp:1362-1381) with one batched copy
-            perm = list(range(ncontr - 1, -1, -1)) + list(range(ncontr, ncontr + b_keep))
-            shp = B.shapes[:, perm]
-            Bp = AbelianBackendData(B.dtype, self.device, torch.empty_like(B.buf), B.block_inds, B.offsets, B.shapes)
-            jobs = self._make_jobs(B.offsets, B.offsets, shp, _c_strides(B.shapes)[:, perm], _c_strides(shp))
-            self._copy_blocks(B.buf, Bp.buf, jobs, B.cyb_dtype)
-            b = _Retyped(b, Bp)
-            B = Bp
-        plan = self.compose_plan(a, b)
-        n_out = plan["n_out"]
-        legs = conventional_leg_order(a.codomain, b.domain)
-        out_bi = plan["out_bi"]
-        shapes = (np.stack([np.asarray(l.multiplicities)[out_bi[:, ax]] for ax, l in enumerate(legs)], axis=1)
-                  if rr else np.zeros((n_out, 0), np.int64))
-        tdt = torch.complex128 if res_dtype == "complex128" else torch.float64
+        sub_key = None if subset is None else tuple(int(x) for x in subset)
+        key = ("compose", A.sig, B.sig, a.codomain.sig, a.domain.sig, b.domain.sig, sub_key)
+        plan = self._plan_get(key)
+        if plan is None:
+            plan = self.compose_plan(a, b)
+            n_out = plan["n_out"]
+            legs = conventional_leg_order(a.codomain, b.domain)
+            out_bi = plan["out_bi"]
+            plan["shapes"] = (np.stack([np.asarray(l.multiplicities)[out_bi[:, ax]] for ax, l in enumerate(legs)], axis=1)
+                              if rr else np.zeros((n_out, 0), np.int64))
+            plan["sig"] = None
+            plan["nrun"] = n_out if subset is None else len(subset)
+            plan["gemm_ws"] = None
+            if plan["nrun"] and not self.dry_run:
+                with self._ctx():
+                    d_sub = None if subset is None else to_device_i64(np.asarray(subset), self.device)
+                    nbytes = int(self._gemm_ws(plan["nrun"]))
+                    ws = torch.empty(nbytes // 8 + 1, dtype=torch.int64, device=self.device)
+                    self._call("cyb_grouped_gemm_prepare", _lib.CYB_C128 if res_dtype == "complex128" else _lib.CYB_F64,
+                               ptr(plan["d_mn"]), ptr(plan["d_pp"]), ptr(plan["d_pairs"]), ptr(d_sub), plan["nrun"],
+                               ptr(ws), nbytes, self._stream())
+                    plan["gemm_ws"] = ws
+            self._plan_put(key, plan)
         if self.plan_mkn is not None:
             self.plan_mkn.append(plan["mkn"])
-        buf = torch.empty(ALIGN if self.dry_run else max(plan["total_elems"], ALIGN), dtype=tdt, device=self.device)
-        res = AbelianBackendData(res_dtype, self.device, buf, out_bi, plan["out_off"], shapes)
-        self._run_gemm(A, B, res, plan, subset)
-        res._dev_tables["offsets"] = plan["d_off"][:n_out]
+        # A's trailing axes are the contracted legs in REVERSED order; bring B's leading axes into the
+        # same order (abelian.cpp:1362-1381) -- one batched copy, fused with a pending permute_legs of B
+        b_buf = self._compose_operand_b(B, ncontr, b_keep) if ncontr > 1 else B.buf
+        buf = self._new_buf(res_dtype, plan["total_elems"])
+        res = AbelianBackendData(res_dtype, self.device, buf, plan["out_bi"], plan["out_off"], plan["shapes"],
+                                 sig=plan["sig"])
+        if plan["sig"] is None:
+            plan["sig"] = res.sig
+        self._run_gemm(A.buf, b_buf, res, plan)
+        res._dev_tables["offsets"] = plan["d_off"][:plan["n_out"]]
         return res
 
-    def _run_gemm(self, A, B, res, plan, subset=None):
-        n_out = plan["n_out"]
-        if n_out == 0 or self.dry_run:
+    def _compose_operand_b(self, B: AbelianBackendData, ncontr: int, b_keep: int) -> torch.Tensor:
+        """Arena with every block of B re-laid-out to axes ``[reversed(contracted), kept]`` (same block
+        offsets).  If B is a not-yet-materialised permute_legs of some parent tensor, the permutation
+        and the reversal are done in ONE pass straight from the parent's arena."""
+        perm = list(range(ncontr - 1, -1, -1)) + list(range(ncontr, ncontr + b_keep))
+        src = B.pending_source
+        if src is not None:
+            parent, axes_perm, order = src
+            key = ("operand_b", parent.sig, axes_perm, ncontr)
+            plan = self._plan_get(key)
+            if plan is None:
+                shp = B.shapes[:, perm]
+                src_strides = _c_strides(parent.shapes)[order][:, list(axes_perm)][:, perm]
+                jobs = self._make_jobs(parent.offsets[order], B.offsets, shp, src_strides, _c_strides(shp))
+                plan = self._plan_put(key, dict(copy=self._prepare_copy(jobs)))
+            src_buf = parent.buf
+        else:
+            # an operand that is reused (the environments / MPO of a Lanczos loop) keeps its re-laid-out copy
+            if B._relayout is not None and ncontr in B._relayout:
+                return B._relayout[ncontr]
+            key = ("operand_b", B.sig, None, ncontr)
+            plan = self._plan_get(key)
+            if plan is None:
+                shp = B.shapes[:, perm]
+                jobs = self._make_jobs(B.offsets, B.offsets, shp, _c_strides(B.shapes)[:, perm], _c_strides(shp))
+                plan = self._plan_put(key, dict(copy=self._prepare_copy(jobs)))
+            src_buf = B.buf
+        total = int(B.offsets[-1] + B.sizes[-1]) if B.num_blocks else 0
+        out = self._new_buf(B.dtype, total)
+        self._run_copy(src_buf, out, plan["copy"], B.cyb_dtype)
+        if src is None and not self.dry_run:
+            if B._relayout is None:
+                B._relayout = {}
+            B._relayout[ncontr] = out
+        return out
+
+    def _run_gemm(self, a_buf, b_buf, res, plan):
+        if plan["nrun"] == 0 or self.dry_run:
             return
         timed = self.gemm_events is not None and self.device.type == "cuda"
         if timed:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
         with self._ctx():
-            if subset is None:
-                d_sub, n = None, n_out
-            else:
-                d_sub, n = to_device_i64(np.asarray(subset), self.device), len(subset)
-            self._call("cyb_grouped_gemm", ptr(A.buf), ptr(B.buf), ptr(res.buf), res.cyb_dtype,
+            self._call("cyb_grouped_gemm_run", ptr(a_buf), ptr(b_buf), ptr(res.buf), res.cyb_dtype,
                        ptr(plan["d_mn"]), ptr(plan["d_off"]), ptr(plan["d_pp"]), ptr(plan["d_pairs"]),
-                       ptr(d_sub), n, self._stream())
+                       plan["nrun"], ptr(plan["gemm_ws"]), self._stream())
         if timed:
             e1.record()
             self.gemm_events.append((e0, e1))

@@ -260,23 +260,14 @@ int64_t cyb_copy_blocks_workspace(int64_t njobs)
     return (int64_t)(align_up(sizeof(CanonJob) * (size_t)njobs, 256) + sizeof(int64_t) * (2 * (size_t)njobs + 2));
 }
 
-int cyb_copy_blocks(const void* src, void* dst, const cyb_copy_job* jobs, int64_t njobs, int dtype,
-                    int conj, void* workspace, int64_t workspace_bytes, cyb_stream_t stream_)
+int cyb_copy_blocks_prepare(const cyb_copy_job* jobs, int64_t njobs, void* workspace,
+                            int64_t workspace_bytes, cyb_stream_t stream_)
 {
-    CYB_REQUIRE(njobs >= 0, "copy_blocks: njobs < 0");
-    CYB_REQUIRE(dtype == CYB_F64 || dtype == CYB_C128, "copy_blocks: bad dtype %d", dtype);
+    CYB_REQUIRE(njobs >= 0, "copy_blocks_prepare: njobs < 0");
     if (njobs == 0) return CYB_OK;
+    CYB_REQUIRE(workspace && workspace_bytes >= cyb_copy_blocks_workspace(njobs), "copy_blocks_prepare: workspace too small");
     cudaStream_t stream = (cudaStream_t)stream_;
-    const int64_t need = cyb_copy_blocks_workspace(njobs);
-    Scratch own(workspace ? 0 : (size_t)need, stream);
-    char* ws;
-    if (workspace) {
-        CYB_REQUIRE(workspace_bytes >= need, "copy_blocks: workspace too small");
-        ws = static_cast<char*>(workspace);
-    } else {
-        if (!own.ptr) return CYB_ERR_CUDA;
-        ws = own.as<char>();
-    }
+    char* ws = static_cast<char*>(workspace);
     CanonJob* cj = reinterpret_cast<CanonJob*>(ws);
     int64_t* units = reinterpret_cast<int64_t*>(ws + align_up(sizeof(CanonJob) * (size_t)njobs, 256));
     int64_t* unit_start = units + njobs;
@@ -284,6 +275,20 @@ int cyb_copy_blocks(const void* src, void* dst, const cyb_copy_job* jobs, int64_
     CYB_LAUNCH_CHECK();
     scan_units_kernel<<<1, 1024, 0, stream>>>(units, njobs, unit_start);
     CYB_LAUNCH_CHECK();
+    return CYB_OK;
+}
+
+int cyb_copy_blocks_run(const void* src, void* dst, const void* workspace, int64_t njobs, int dtype,
+                        int conj, cyb_stream_t stream_)
+{
+    CYB_REQUIRE(njobs >= 0, "copy_blocks_run: njobs < 0");
+    CYB_REQUIRE(dtype == CYB_F64 || dtype == CYB_C128, "copy_blocks_run: bad dtype %d", dtype);
+    if (njobs == 0) return CYB_OK;
+    CYB_REQUIRE(workspace != nullptr, "copy_blocks_run: no prepared workspace");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const char* ws = static_cast<const char*>(workspace);
+    const CanonJob* cj = reinterpret_cast<const CanonJob*>(ws);
+    const int64_t* unit_start = reinterpret_cast<const int64_t*>(ws + align_up(sizeof(CanonJob) * (size_t)njobs, 256)) + njobs;
     const int grid = sm_count() * 4;
     if (dtype == CYB_F64) {
         copy_blocks_kernel<double, false><<<grid, CP_THREADS, 0, stream>>>(
@@ -297,6 +302,27 @@ int cyb_copy_blocks(const void* src, void* dst, const cyb_copy_job* jobs, int64_
     }
     CYB_LAUNCH_CHECK();
     return CYB_OK;
+}
+
+int cyb_copy_blocks(const void* src, void* dst, const cyb_copy_job* jobs, int64_t njobs, int dtype,
+                    int conj, void* workspace, int64_t workspace_bytes, cyb_stream_t stream_)
+{
+    CYB_REQUIRE(njobs >= 0, "copy_blocks: njobs < 0");
+    CYB_REQUIRE(dtype == CYB_F64 || dtype == CYB_C128, "copy_blocks: bad dtype %d", dtype);
+    if (njobs == 0) return CYB_OK;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int64_t need = cyb_copy_blocks_workspace(njobs);
+    Scratch own(workspace ? 0 : (size_t)need, stream);
+    void* ws = workspace;
+    if (workspace) {
+        CYB_REQUIRE(workspace_bytes >= need, "copy_blocks: workspace too small");
+    } else {
+        if (!own.ptr) return CYB_ERR_CUDA;
+        ws = own.ptr;
+    }
+    const int rc = cyb_copy_blocks_prepare(jobs, njobs, ws, need, stream_);
+    if (rc != CYB_OK) return rc;
+    return cyb_copy_blocks_run(src, dst, ws, njobs, dtype, conj, stream_);
 }
 
 }  // extern "C"

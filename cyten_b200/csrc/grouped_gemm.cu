@@ -56,8 +56,27 @@ struct GemmTables {
     int64_t nblocks;
 };
 
-// single CTA: cost-sorted processing order, tile prefix, ticket reset
-template <int BM, int BN>
+// Output blocks with M <= SK_MAXM rows (an MPO tensor applied to a big operand: M, K of a few units, N
+// up to 10^5) have nothing for an 8x8x4 tensor-core tile to chew on: they are HBM-bound and go to the
+// streaming kernel below (units of SK_COLS columns); everything else goes to the DMMA kernel.
+constexpr int SK_MAXM = 8;
+constexpr int SK_THREADS = 256;
+constexpr int SK_CHUNK = 2 * SK_THREADS;   // columns one CTA covers per pass
+constexpr int SK_PASSES = 8;               // passes per work unit (amortises the unit lookup)
+constexpr int SK_COLS = SK_CHUNK * SK_PASSES;
+
+template <int BM, int BN, bool SKINNY>
+__host__ __device__ __forceinline__ int64_t n_units(int64_t M, int64_t N)
+{
+    if (M <= 0 || N <= 0) return 0;
+    if (SKINNY) return M <= SK_MAXM ? (N + SK_COLS - 1) / SK_COLS : 0;
+    return M > SK_MAXM ? ((M + BM - 1) / BM) * ((N + BN - 1) / BN) : 0;
+}
+
+// single CTA: cost-sorted processing order, tile prefix, ticket reset.
+// SKINNY = false: tiles of the DMMA kernel (blocks with M > SK_MAXM); true: column chunks of the
+// streaming kernel (blocks with M <= SK_MAXM).
+template <int BM, int BN, bool SKINNY>
 __global__ void __launch_bounds__(1024) gemm_schedule_kernel(const int64_t* __restrict__ out_mn,
                                                              const int64_t* __restrict__ out_pair_ptr,
                                                              const int64_t* __restrict__ pairs,
@@ -73,9 +92,9 @@ __global__ void __launch_bounds__(1024) gemm_schedule_kernel(const int64_t* __re
         const int64_t blk = subset ? subset[i] : i;
         double ksum = 0;
         for (int64_t q = out_pair_ptr[blk]; q < out_pair_ptr[blk + 1]; ++q) ksum += (double)pairs[3 * q + 2];
-        const int64_t tm = (out_mn[2 * blk] + BM - 1) / BM, tn = (out_mn[2 * blk + 1] + BN - 1) / BN;
+        const int64_t nt = n_units<BM, BN, SKINNY>(out_mn[2 * blk], out_mn[2 * blk + 1]);
         // per-tile cost decides the order (long k-loops first), ties keep table order
-        cost[i] = (tm * tn > 0) ? ksum : -1.0;
+        cost[i] = (nt > 0) ? ksum : -1.0;
     }
     __syncthreads();
     for (int64_t i = tid; i < nblocks; i += 1024) {
@@ -94,7 +113,7 @@ __global__ void __launch_bounds__(1024) gemm_schedule_kernel(const int64_t* __re
         int64_t v = 0;
         if (i < nblocks) {
             const int64_t blk = order[i];
-            v = ((out_mn[2 * blk] + BM - 1) / BM) * ((out_mn[2 * blk + 1] + BN - 1) / BN);
+            v = n_units<BM, BN, SKINNY>(out_mn[2 * blk], out_mn[2 * blk + 1]);
         }
         int64_t total;
         int64_t pos = block_exclusive_scan<int64_t>(v, s_scan, &total);
@@ -308,6 +327,118 @@ grouped_gemm_kernel(const double* __restrict__ A, const double* __restrict__ B, 
     }
 }
 
+
+// ---- streaming kernel for blocks with M <= SK_MAXM -------------------------------------------------
+// C (M x N) = sum_p A_p (M x K_p) B_p (K_p x N): every thread owns VEC adjacent columns of one chunk and
+// keeps the M partial sums in registers; B is read exactly once (coalesced along N), A_p is a handful of
+// values broadcast through L1.  Algorithmic traffic = |B| + |C|; bound by HBM bandwidth.
+template <bool CPLX, int VEC, int MM>
+__device__ __noinline__ void skinny_unit_mm(const double* __restrict__ A, const double* __restrict__ B,
+                                            double* __restrict__ Cb, const int64_t* __restrict__ pairs,
+                                            int64_t p_begin, int64_t p_end, int M, int64_t N, int64_t n)
+{
+    constexpr int W = (CPLX ? 2 : 1) * VEC;   // doubles per thread per row
+    double acc[MM][W];
+#pragma unroll
+    for (int m = 0; m < MM; ++m)
+#pragma unroll
+        for (int w = 0; w < W; ++w) acc[m][w] = 0.0;
+    for (int64_t p = p_begin; p < p_end; ++p) {
+        const int64_t a_off = pairs[3 * p], b_off = pairs[3 * p + 1];
+        const int K = (int)pairs[3 * p + 2];
+        const double* __restrict__ Ap = A + a_off * (CPLX ? 2 : 1);
+        const double* __restrict__ Bp = B + (b_off + n) * (CPLX ? 2 : 1);
+#pragma unroll 4
+        for (int k = 0; k < K; ++k) {
+            double b[W];
+            if (W == 2) {
+                const double2 t = __ldcs(reinterpret_cast<const double2*>(Bp + (int64_t)k * N * (CPLX ? 2 : 1)));
+                b[0] = t.x; b[W - 1] = t.y;
+            } else if (W == 4) {
+                const double2 t0 = __ldcs(reinterpret_cast<const double2*>(Bp + (int64_t)k * N * 2));
+                const double2 t1 = __ldcs(reinterpret_cast<const double2*>(Bp + (int64_t)k * N * 2 + 2));
+                b[0] = t0.x; b[1] = t0.y; b[W - 2] = t1.x; b[W - 1] = t1.y;
+            } else {
+                b[0] = __ldcs(Bp + (int64_t)k * N);
+            }
+#pragma unroll
+            for (int m = 0; m < MM; ++m) {
+                if (m < M) {
+                    if (!CPLX) {
+                        const double a = __ldg(Ap + m * K + k);
+#pragma unroll
+                        for (int w = 0; w < W; ++w) acc[m][w] = fma(a, b[w], acc[m][w]);
+                    } else {
+                        const double2 a = __ldg(reinterpret_cast<const double2*>(Ap) + m * K + k);
+#pragma unroll
+                        for (int v = 0; v < VEC; ++v) {
+                            acc[m][2 * v] = fma(a.x, b[2 * v], fma(-a.y, b[2 * v + 1], acc[m][2 * v]));
+                            acc[m][2 * v + 1] = fma(a.x, b[2 * v + 1], fma(a.y, b[2 * v], acc[m][2 * v + 1]));
+                        }
+                    }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int m = 0; m < MM; ++m) {
+        if (m < M) {
+            double* c = Cb + ((int64_t)m * N + n) * (CPLX ? 2 : 1);
+            if (W == 1) __stcs(c, acc[m][0]);
+            else {
+#pragma unroll
+                for (int w = 0; w < W; w += 2) __stcs(reinterpret_cast<double2*>(c + w), make_double2(acc[m][w], acc[m][w + 1]));
+            }
+        }
+    }
+}
+
+template <bool CPLX, int VEC>
+__device__ __forceinline__ void skinny_unit(const double* __restrict__ A, const double* __restrict__ B,
+                                            double* __restrict__ Cb, const int64_t* __restrict__ pairs,
+                                            int64_t p_begin, int64_t p_end, int M, int64_t N, int64_t n)
+{
+    if (M <= SK_MAXM / 2) skinny_unit_mm<CPLX, VEC, SK_MAXM / 2>(A, B, Cb, pairs, p_begin, p_end, M, N, n);
+    else skinny_unit_mm<CPLX, VEC, SK_MAXM>(A, B, Cb, pairs, p_begin, p_end, M, N, n);
+}
+
+template <bool CPLX>
+__global__ void __launch_bounds__(SK_THREADS, 3) skinny_gemm_kernel(const double* __restrict__ A,
+                                                                 const double* __restrict__ B,
+                                                                 double* __restrict__ C, GemmTables T)
+{
+    const int64_t total_units = T.tile_start[T.nblocks];
+    for (int64_t unit = blockIdx.x; unit < total_units; unit += gridDim.x) {
+        int64_t lo = 0, hi = T.nblocks;
+        while (hi - lo > 1) {
+            const int64_t mid = (lo + hi) >> 1;
+            if (T.tile_start[mid] <= unit) lo = mid; else hi = mid;
+        }
+        const int64_t blk = T.order[lo];
+        const int M = (int)T.out_mn[2 * blk];
+        const int64_t N = T.out_mn[2 * blk + 1];
+        const int64_t u0 = (unit - T.tile_start[lo]) * SK_COLS;
+        const int64_t p_begin = T.out_pair_ptr[blk], p_end = T.out_pair_ptr[blk + 1];
+        double* Cb = C + T.out_off[blk] * (CPLX ? 2 : 1);
+        const bool vec2 = !CPLX && (N & 1) == 0;   // real with even N: rows stay 16-byte aligned
+#pragma unroll 1
+        for (int pass = 0; pass < SK_PASSES; ++pass) {
+            const int64_t c0 = u0 + (int64_t)pass * SK_CHUNK;
+            if (c0 >= N) break;
+            if (vec2) {
+                const int64_t n = c0 + (int64_t)threadIdx.x * 2;
+                if (n < N) skinny_unit<CPLX, 2>(A, B, Cb, T.pairs, p_begin, p_end, M, N, n);
+            } else {
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int64_t n = c0 + threadIdx.x + h * SK_THREADS;
+                    if (n < N) skinny_unit<CPLX, 1>(A, B, Cb, T.pairs, p_begin, p_end, M, N, n);
+                }
+            }
+        }
+    }
+}
+
 using CfgR = GemmCfg<false, 128, 128, 16, 2, 4, 4>;   // 8 warps, warp tile 64x32, 4-stage pipeline
 using CfgC = GemmCfg<true, 128, 64, 8, 4, 2, 4>;      // 8 warps, warp tile 32x32 complex
 
@@ -331,36 +462,93 @@ using namespace cyb;
 
 extern "C" {
 
+// workspace per pass: cost[n] (double), order[n], tile_start[n+1], ticket  -> 3n + 4 words
+int64_t cyb_grouped_gemm_workspace(int64_t nblocks)
+{
+    return (int64_t)(sizeof(int64_t) * 2 * (3 * (size_t)(nblocks > 0 ? nblocks : 0) + 4));
+}
+
+static void gemm_tables(GemmTables T[2], double* cost[2], const int64_t* out_mn, const int64_t* out_off,
+                        const int64_t* out_pair_ptr, const int64_t* pairs, int64_t nblocks, void* workspace)
+{
+    const size_t n = (size_t)nblocks;
+    const size_t pass_words = 3 * n + 4;
+    char* ws = static_cast<char*>(workspace);
+    for (int pass = 0; pass < 2; ++pass) {
+        char* base = ws + sizeof(int64_t) * pass_words * pass;
+        cost[pass] = reinterpret_cast<double*>(base);
+        T[pass].out_mn = out_mn; T[pass].out_off = out_off; T[pass].out_pair_ptr = out_pair_ptr; T[pass].pairs = pairs;
+        T[pass].order = reinterpret_cast<int64_t*>(base + sizeof(int64_t) * n);
+        T[pass].tile_start = reinterpret_cast<int64_t*>(base + sizeof(int64_t) * 2 * n);
+        T[pass].ticket = reinterpret_cast<unsigned long long*>(base + sizeof(int64_t) * (3 * n + 2));
+        T[pass].nblocks = nblocks;
+    }
+}
+
+int cyb_grouped_gemm_prepare(int dtype, const int64_t* out_mn, const int64_t* out_pair_ptr,
+                             const int64_t* pairs, const int64_t* block_subset, int64_t nblocks,
+                             void* workspace, int64_t workspace_bytes, cyb_stream_t stream_)
+{
+    CYB_REQUIRE(dtype == CYB_F64 || dtype == CYB_C128, "grouped_gemm_prepare: bad dtype %d", dtype);
+    CYB_REQUIRE(nblocks >= 0, "grouped_gemm_prepare: nblocks < 0");
+    if (nblocks == 0) return CYB_OK;
+    CYB_REQUIRE(workspace && workspace_bytes >= cyb_grouped_gemm_workspace(nblocks), "grouped_gemm_prepare: workspace too small");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    GemmTables T[2];
+    double* cost[2];
+    gemm_tables(T, cost, out_mn, nullptr, out_pair_ptr, pairs, nblocks, workspace);
+    if (dtype == CYB_F64) {
+        gemm_schedule_kernel<CfgR::BM, CfgR::BN, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket);
+        gemm_schedule_kernel<CfgR::BM, CfgR::BN, true><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[1], (int64_t*)T[1].order, (int64_t*)T[1].tile_start, T[1].ticket);
+    } else {
+        gemm_schedule_kernel<CfgC::BM, CfgC::BN, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket);
+        gemm_schedule_kernel<CfgC::BM, CfgC::BN, true><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[1], (int64_t*)T[1].order, (int64_t*)T[1].tile_start, T[1].ticket);
+    }
+    CYB_LAUNCH_CHECK();
+    return CYB_OK;
+}
+
+int cyb_grouped_gemm_run(const void* a, const void* b, void* c, int dtype, const int64_t* out_mn,
+                         const int64_t* out_off, const int64_t* out_pair_ptr, const int64_t* pairs,
+                         int64_t nblocks, void* workspace, cyb_stream_t stream_)
+{
+    CYB_REQUIRE(dtype == CYB_F64 || dtype == CYB_C128, "grouped_gemm_run: bad dtype %d", dtype);
+    CYB_REQUIRE(nblocks >= 0, "grouped_gemm_run: nblocks < 0");
+    if (nblocks == 0) return CYB_OK;
+    CYB_REQUIRE(workspace != nullptr, "grouped_gemm_run: no prepared workspace");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    GemmTables T[2];
+    double* cost[2];
+    gemm_tables(T, cost, out_mn, out_off, out_pair_ptr, pairs, nblocks, workspace);
+    // the dynamic tile counter of the persistent DMMA kernel starts at 0 for every run
+    CYB_CHECK_CUDA(cudaMemsetAsync(T[0].ticket, 0, sizeof(unsigned long long), stream));
+    const double* A = static_cast<const double*>(a);
+    const double* B = static_cast<const double*>(b);
+    double* C = static_cast<double*>(c);
+    const int sk_grid = sm_count() * 8;
+    if (dtype == CYB_F64) {
+        skinny_gemm_kernel<false><<<sk_grid, SK_THREADS, 0, stream>>>(A, B, C, T[1]);
+        CYB_LAUNCH_CHECK();
+        return launch_gemm<CfgR>(a, b, c, T[0], stream);
+    }
+    skinny_gemm_kernel<true><<<sk_grid, SK_THREADS, 0, stream>>>(A, B, C, T[1]);
+    CYB_LAUNCH_CHECK();
+    return launch_gemm<CfgC>(a, b, c, T[0], stream);
+}
+
 int cyb_grouped_gemm(const void* a, const void* b, void* c, int dtype, const int64_t* out_mn,
                      const int64_t* out_off, const int64_t* out_pair_ptr, const int64_t* pairs,
-                     const int64_t* block_subset, int64_t nblocks,
-                     cyb_stream_t stream_)
+                     const int64_t* block_subset, int64_t nblocks, cyb_stream_t stream_)
 {
-
     CYB_REQUIRE(dtype == CYB_F64 || dtype == CYB_C128, "grouped_gemm: bad dtype %d", dtype);
     CYB_REQUIRE(nblocks >= 0, "grouped_gemm: nblocks < 0");
     if (nblocks == 0) return CYB_OK;
-    cudaStream_t stream = (cudaStream_t)stream_;
-    // scratch: cost[n] (double), order[n], tile_start[n+1], ticket
-    const size_t n = (size_t)nblocks;
-    Scratch ws(sizeof(int64_t) * (3 * n + 4), stream);
+    const int64_t bytes = cyb_grouped_gemm_workspace(nblocks);
+    Scratch ws((size_t)bytes, (cudaStream_t)stream_);
     if (!ws.ptr) return CYB_ERR_CUDA;
-    double* cost = ws.as<double>();
-    int64_t* order = ws.as<int64_t>(sizeof(int64_t) * n);
-    int64_t* tile_start = ws.as<int64_t>(sizeof(int64_t) * 2 * n);
-    unsigned long long* ticket = ws.as<unsigned long long>(sizeof(int64_t) * (3 * n + 2));
-    GemmTables T;
-    T.out_mn = out_mn; T.out_off = out_off; T.out_pair_ptr = out_pair_ptr; T.pairs = pairs;
-    T.order = order; T.tile_start = tile_start; T.ticket = ticket; T.nblocks = nblocks;
-    if (dtype == CYB_F64) {
-        gemm_schedule_kernel<CfgR::BM, CfgR::BN><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost, order, tile_start, ticket);
-        CYB_LAUNCH_CHECK();
-        return launch_gemm<CfgR>(a, b, c, T, stream);
-    } else {
-        gemm_schedule_kernel<CfgC::BM, CfgC::BN><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost, order, tile_start, ticket);
-        CYB_LAUNCH_CHECK();
-        return launch_gemm<CfgC>(a, b, c, T, stream);
-    }
+    int rc = cyb_grouped_gemm_prepare(dtype, out_mn, out_pair_ptr, pairs, block_subset, nblocks, ws.ptr, bytes, stream_);
+    if (rc != CYB_OK) return rc;
+    return cyb_grouped_gemm_run(a, b, c, dtype, out_mn, out_off, out_pair_ptr, pairs, nblocks, ws.ptr, stream_);
 }
 
 }  // extern "C"

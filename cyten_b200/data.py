@@ -11,6 +11,7 @@ format) and are uploaded where a kernel needs them.
 from __future__ import annotations
 
 import ctypes as C
+import hashlib
 
 import numpy as np
 import torch
@@ -63,16 +64,56 @@ def to_device_i64(a: np.ndarray, device) -> torch.Tensor:
 class AbelianBackendData:
     """All blocks of one tensor in a single device arena + the integer tables describing them."""
 
-    __slots__ = ("dtype", "device", "buf", "block_inds", "offsets", "shapes", "_dev_tables")
+    __slots__ = ("dtype", "device", "_buf", "block_inds", "offsets", "shapes", "_dev_tables", "_sig",
+                 "_pending", "_relayout")
 
-    def __init__(self, dtype, device, buf, block_inds, offsets, shapes):
+    def __init__(self, dtype, device, buf, block_inds, offsets, shapes, sig=None, pending=None):
         self.dtype = dtype_name(dtype)
         self.device = torch.device(device)
-        self.buf = buf
+        self._buf = buf
         self.block_inds = np.ascontiguousarray(block_inds, dtype=np.int64)
         self.offsets = np.ascontiguousarray(offsets, dtype=np.int64)
         self.shapes = np.ascontiguousarray(shapes, dtype=np.int64)
         self._dev_tables = {}
+        self._sig = sig
+        # deferred layout change (permute_legs): a callable producing the arena on first use.  The
+        # reference's numpy blocks are lazy views in the same place (numpy.cpp permute_axes); here the
+        # consumer decides where the one copy happens (compose folds it into its operand re-layout).
+        self._pending = pending
+        self._relayout = None   # cache of re-laid-out copies of this (immutable) arena, see backend.compose
+
+    @property
+    def buf(self) -> torch.Tensor:
+        if self._buf is None:
+            pending, self._pending = self._pending, None
+            self._buf = pending[0]()
+        return self._buf
+
+    @buf.setter
+    def buf(self, value):
+        self._buf, self._pending, self._relayout = value, None, None
+
+    @property
+    def is_pending(self) -> bool:
+        return self._buf is None
+
+    @property
+    def pending_source(self):
+        """(parent data, axes_perm, row order) of an unmaterialised permutation, else None."""
+        return self._pending[1] if self._buf is None else None
+
+    @property
+    def sig(self) -> bytes:
+        """Structure signature (dtype + integer tables, not the contents): the key of cached plans."""
+        if self._sig is None:
+            h = hashlib.blake2b(digest_size=16)
+            h.update(self.dtype.encode())
+            h.update(np.asarray(self.block_inds.shape, dtype=np.int64).tobytes())
+            h.update(self.block_inds.tobytes())
+            h.update(self.shapes.tobytes())
+            h.update(self.offsets.tobytes())
+            self._sig = h.digest()
+        return self._sig
 
     # -- construction ------------------------------------------------------------------------------
     @classmethod

@@ -193,12 +193,30 @@ class ElementarySpace:
     # -- queries -----------------------------------------------------------------------------------
     @property
     def dual(self) -> "ElementarySpace":
-        return ElementarySpace(self.symmetry, self.defining_sectors, self.multiplicities,
-                               not self.is_dual)
+        d = self.__dict__.get("_dual")
+        if d is None:
+            d = ElementarySpace(self.symmetry, self.defining_sectors, self.multiplicities, not self.is_dual)
+            d.__dict__["_dual"] = self
+            self.__dict__["_dual"] = d
+        return d
 
     def as_ElementarySpace(self, is_dual: bool = False) -> "ElementarySpace":
         return ElementarySpace.from_sector_decomposition(self.symmetry, self.sector_decomposition,
                                                          self.multiplicities, is_dual)
+
+    @property
+    def sig(self) -> bytes:
+        """Hashable signature (symmetry, duality, sectors, multiplicities): key material of cached plans."""
+        sg = self.__dict__.get("_sig")
+        if sg is None:
+            import hashlib
+            h = hashlib.blake2b(digest_size=16)
+            h.update(repr(self.symmetry.moduli_array().tolist()).encode())
+            h.update(b"d" if self.is_dual else b"n")
+            h.update(self.defining_sectors.tobytes())
+            h.update(self.multiplicities.tobytes())
+            sg = self.__dict__["_sig"] = h.digest()
+        return sg
 
     def sector_decomposition_where(self, sector) -> int | None:
         sector = np.asarray(sector, dtype=np.int64).reshape(-1)
@@ -269,6 +287,10 @@ class TensorProduct:
     def as_ElementarySpace(self, is_dual: bool = False) -> ElementarySpace:
         return ElementarySpace.from_sector_decomposition(self.symmetry, self.sector_decomposition,
                                                          self.multiplicities, is_dual)
+
+    @property
+    def sig(self) -> tuple:
+        return tuple(f.sig for f in self.factors)
 
     def __getitem__(self, i):
         return self.factors[i]
@@ -350,8 +372,24 @@ class AbelianLegPipe(ElementarySpace):
     def dual(self) -> "AbelianLegPipe":
         """Dual legs in REVERSED order, opposite duality and combine style
         (AbelianLegPipe::dual_pipe, src/symmetries/spaces.cpp:3195-3204)."""
-        return AbelianLegPipe([l.dual for l in reversed(self.legs)], not self.is_dual,
-                              not self.combine_cstyle)
+        d = self.__dict__.get("_dual")
+        if d is None:
+            d = AbelianLegPipe([l.dual for l in reversed(self.legs)], not self.is_dual, not self.combine_cstyle)
+            d.__dict__["_dual"] = self
+            self.__dict__["_dual"] = d
+        return d
+
+    @property
+    def sig(self) -> bytes:
+        sg = self.__dict__.get("_sig")
+        if sg is None:
+            import hashlib
+            h = hashlib.blake2b(digest_size=16)
+            h.update(b"pipe" + (b"d" if self.is_dual else b"n") + (b"c" if self.combine_cstyle else b"f"))
+            for l in self.legs:
+                h.update(l.sig)
+            sg = self.__dict__["_sig"] = h.digest()
+        return sg
 
     def __eq__(self, other):
         if isinstance(other, AbelianLegPipe):

@@ -93,6 +93,16 @@ int64_t cyb_copy_blocks_workspace(int64_t njobs);
 int cyb_copy_blocks(const void* src, void* dst, const cyb_copy_job* jobs, int64_t njobs, int dtype,
                     int conj, void* workspace, int64_t workspace_bytes, cyb_stream_t stream);
 
+/* The two halves of cyb_copy_blocks, for callers that keep a job list (a "plan": the bookkeeping of
+ * permute_legs / combine_legs / split_legs depends only on block_inds and the legs, not on the block
+ * contents) and replay it on new data: prepare canonicalises and schedules the jobs into `workspace`
+ * (>= cyb_copy_blocks_workspace(njobs) bytes, caller-owned, must stay alive), run is the single copy
+ * launch. */
+int cyb_copy_blocks_prepare(const cyb_copy_job* jobs, int64_t njobs, void* workspace,
+                            int64_t workspace_bytes, cyb_stream_t stream);
+int cyb_copy_blocks_run(const void* src, void* dst, const void* workspace, int64_t njobs, int dtype,
+                        int conj, cyb_stream_t stream);
+
 /* ---- (a6) compose: abelian.cpp:1238-1469 ------------------------------------------------ *
  * Device planner for abelian_compose_worker.  Inputs describe A (block_inds a_bi[na][ra],
  * the first `a_keep` columns are kept, the rest contracted) and B (b_bi[nb][rb], the first
@@ -143,6 +153,17 @@ int cyb_fuse_charges(const int64_t* bi, int64_t nrows, int64_t ncols, const int6
 int cyb_grouped_gemm(const void* a, const void* b, void* c, int dtype, const int64_t* out_mn,
                      const int64_t* out_off, const int64_t* out_pair_ptr, const int64_t* pairs,
                      const int64_t* block_subset, int64_t nblocks, cyb_stream_t stream);
+
+/* The two halves of cyb_grouped_gemm for a cached compose plan: prepare builds the tile schedule
+ * (cost-sorted block order, tile prefix sums for the DMMA and the streaming kernel) into `workspace`
+ * (>= cyb_grouped_gemm_workspace(nblocks) bytes, caller-owned); run launches the kernels. */
+int64_t cyb_grouped_gemm_workspace(int64_t nblocks);
+int cyb_grouped_gemm_prepare(int dtype, const int64_t* out_mn, const int64_t* out_pair_ptr,
+                             const int64_t* pairs, const int64_t* block_subset, int64_t nblocks,
+                             void* workspace, int64_t workspace_bytes, cyb_stream_t stream);
+int cyb_grouped_gemm_run(const void* a, const void* b, void* c, int dtype, const int64_t* out_mn,
+                         const int64_t* out_off, const int64_t* out_pair_ptr, const int64_t* pairs,
+                         int64_t nblocks, void* workspace, cyb_stream_t stream);
 
 /* ---- (a7,a9,a10) per-sector factorisations ----------------------------------------------- *
  * Batched over `nmat` independent row-major matrices inside arenas (device pointers a,u,s,...).

@@ -149,7 +149,18 @@ def cyb_fuse_charges(bi, nrows, ncols, cols, nlegs, sectors, sector_ptr, modulus
 
 # ---- (a3-a5) strided block copies ---------------------------------------------------------------------
 def cyb_copy_blocks_workspace(njobs):
+    return 8 * JOB_WORDS * int(njobs) + 8
+
+
+def cyb_copy_blocks_prepare(jobs, njobs, workspace, workspace_bytes, stream=None):
+    """Plan half of cyb_copy_blocks: here the 'schedule' is the job list itself."""
+    if njobs:
+        _i64(workspace, njobs * JOB_WORDS)[:] = _i64(jobs, njobs * JOB_WORDS)
     return 0
+
+
+def cyb_copy_blocks_run(src, dst, workspace, njobs, dtype, conj, stream=None):
+    return cyb_copy_blocks(src, dst, workspace, njobs, dtype, conj, None, 0)
 
 
 def cyb_copy_blocks(src, dst, jobs, njobs, dtype, conj, workspace, workspace_bytes, stream=None):
@@ -281,6 +292,24 @@ def cyb_grouped_gemm(a, b, c, dtype, out_mn, out_off, out_pair_ptr, pairs, block
             acc = np.zeros((M, N), dtype=dt)
         _arr(_addr(c) + isz * int(off[t]), M * N, dt).reshape(M, N)[:] = acc
     return 0
+
+
+def cyb_grouped_gemm_workspace(nblocks):
+    return 8 * int(nblocks) + 8
+
+
+def cyb_grouped_gemm_prepare(dtype, out_mn, out_pair_ptr, pairs, block_subset, nblocks, workspace,
+                             workspace_bytes, stream=None):
+    """Plan half of cyb_grouped_gemm: the schedule of the oracle is just the list of blocks to do."""
+    sub = _i64(block_subset, nblocks) if _addr(block_subset) else np.arange(nblocks)
+    if nblocks:
+        _i64(workspace, nblocks)[:] = sub
+    return 0
+
+
+def cyb_grouped_gemm_run(a, b, c, dtype, out_mn, out_off, out_pair_ptr, pairs, nblocks, workspace,
+                         stream=None):
+    return cyb_grouped_gemm(a, b, c, dtype, out_mn, out_off, out_pair_ptr, pairs, workspace, nblocks)
 
 
 # ---- (a7, a9, a10) factorisations --------------------------------------------------------------------------

@@ -1,0 +1,89 @@
+"""Worker of tests/test_sharding.py: one process per (virtual) GPU, gloo backend, the host logic of
+cyten_b200 over the numpy oracle of the C-ABI."""
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parents[1]
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+
+def _dense_of(T):
+    return T.to_dense()
+
+
+def worker(rank, world, port, out_dir):
+    import torch
+    import torch.distributed as dist
+    from cyten_b200 import sharding as sh
+    from cyten_b200 import tensors as ct
+    from cyten_b200.backend import B200AbelianBackend
+    from cyten_b200.workloads import build_heff, mps_tensor, u1_bond_leg, u1_phys_leg
+    from oracle import cabi_numpy
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        be = B200AbelianBackend("cpu", _library=cabi_numpy)
+        pg = sh.attach_process_group(be, dist.group.WORLD)
+        assert (pg.rank, pg.world) == (rank, world)
+        res = {}
+
+        # ---- H_eff matvec: sharded chain + one all_reduce == unsharded ----
+        H, theta, _, _ = build_heff(64, be, Q=3, sigma=1.2)
+        want = H.matvec(theta)
+        SH = sh.ShardedHEffective(H, pg)
+        th_loc = SH.shard(theta)
+        nblk = torch.tensor([th_loc.data.num_blocks])
+        dist.all_reduce(nblk)
+        assert int(nblk.item()) == theta.data.num_blocks          # disjoint cover
+        be.plan_mkn = []
+        got = SH.matvec(th_loc)
+        fl = torch.tensor([float(sum(be.plan_mkn))], dtype=torch.float64)
+        be.plan_mkn = []
+        H.matvec(theta)
+        fl_full = float(sum(be.plan_mkn))
+        be.plan_mkn = None
+        dist.all_reduce(fl)
+        assert float(fl.item()) == fl_full, "sharding must not duplicate flops"
+        full_want = sh.expand_to_full(want)
+        assert np.array_equal(got.data.block_inds, full_want.data.block_inds)
+        d_got, d_want = _dense_of(got), _dense_of(want)
+        assert np.allclose(d_got, d_want, rtol=0, atol=1e-12 * np.abs(d_want).max())
+        res["matvec_max"] = float(np.abs(d_want).max())
+
+        # ---- tdot with the output blocks partitioned over the ranks ----
+        v, p = u1_bond_leg(48, 3, 1.2), u1_phys_leg()
+        A, B = mps_tensor(v, p, v, be, seed=1), mps_tensor(v, p, v, be, seed=2)
+        th = ct.tdot(A, B, [2], [0])
+        th_loc = sh.tdot_sharded(A, B, [2], [0], pg)
+        nb = torch.tensor([th_loc.data.num_blocks])
+        dist.all_reduce(nb)
+        assert int(nb.item()) == th.data.num_blocks               # every output block computed exactly once
+        th_rep = sh.all_gather_blocks(th_loc, pg)
+        assert np.array_equal(_dense_of(th_rep), _dense_of(th))   # same kernels, same order: bit-exact
+
+        # ---- truncated SVD with the sectors LPT-partitioned, global cut via all_gather of S ----
+        for chi_max in (30, 48):
+            U1, S1, V1, err1, ren1 = ct.truncated_svd(th, chi_max=chi_max, svd_min=1e-12)
+            U, S, Vh, err, ren, owner = sh.truncated_svd_sharded(th, pg, chi_max=chi_max, svd_min=1e-12)
+            assert abs(err - err1) <= 1e-14 and ren == ren1
+            assert S.leg == S1.leg                                # identical kept-sector dimensions
+            # my blocks are exactly the sectors I own, and equal the unsharded ones
+            s_un = {int(r[0]): b for r, b in zip(S1.data.block_inds, S1.data.to_numpy_blocks())}
+            for r, b in zip(S.data.block_inds, S.data.to_numpy_blocks()):
+                assert np.array_equal(b, s_un[int(r[0])])
+            kept = torch.tensor([int(S.data.shapes.sum())])
+            dist.all_reduce(kept)
+            assert int(kept.item()) == int(S1.data.shapes.sum())
+            Ur, Vr = sh.all_gather_blocks(U, pg), sh.all_gather_blocks(Vh, pg)
+            assert np.array_equal(_dense_of(Ur), _dense_of(sh.expand_to_full(U1)))
+            assert np.array_equal(_dense_of(Vr), _dense_of(sh.expand_to_full(V1)))
+        res["ok"] = True
+        np.save(os.path.join(out_dir, f"rank{rank}.npy"), np.asarray([1.0]))
+    finally:
+        dist.destroy_process_group()

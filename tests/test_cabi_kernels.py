@@ -231,7 +231,9 @@ def _gemm_case(rng, dtype, problems):
 def test_grouped_gemm(lib, dtype):
     rng = np.random.default_rng(11)
     problems = [(1, 1, [1]), (5, 7, [3]), (17, 33, [9, 4, 1]), (128, 128, [64]), (130, 129, [31, 17]), (64, 300, [50]),
-                (257, 66, [128, 3]), (3, 500, [7, 7, 7, 7]), (200, 1, [33]), (96, 96, [5, 6, 7, 8, 9])]
+                (257, 66, [128, 3]), (3, 500, [7, 7, 7, 7]), (200, 1, [33]), (96, 96, [5, 6, 7, 8, 9]),
+                # M <= 8: the streaming (HBM-bound) path, even / odd N, chunk edges, several pairs
+                (8, 1025, [2, 3]), (4, 2048, [6]), (2, 513, [1]), (7, 512, [5, 1]), (1, 1300, [2]), (9, 1024, [3])]
     Aar, Bar, csize, pairs, mn, pp, coff, a_parts, b_parts = _gemm_case(rng, dtype, problems)
     d_c = lib.up(np.full(csize, np.nan, dtype=dtype))
     lib.call("cyb_grouped_gemm", lib.p(lib.up(Aar)), lib.p(lib.up(Bar)), lib.p(d_c), int(dtype == np.complex128),
@@ -248,15 +250,15 @@ def test_grouped_gemm(lib, dtype):
         got = out[coff[t]:coff[t] + M * N].reshape(M, N)
         # float64 dot products: |err| <= (sum K) * eps * sum|a||b|; stated tolerance 1e-13 relative to that bound
         assert np.all(np.abs(got - want) <= 1e-13 * bound + 1e-300), (t, M, N, Ks)
-    # subset launch: only blocks 3 and 5 are written
+    # subset launch: only blocks 3, 5 and 7 are written
     d_c2 = lib.up(np.full(csize, 7.0, dtype=dtype))
-    sub = np.asarray([5, 3], dtype=np.int64)
+    sub = np.asarray([5, 3, 7], dtype=np.int64)
     lib.call("cyb_grouped_gemm", lib.p(lib.up(Aar)), lib.p(lib.up(Bar)), lib.p(d_c2), int(dtype == np.complex128),
-             lib.p(lib.up(mn)), lib.p(lib.up(coff)), lib.p(lib.up(pp)), lib.p(lib.up(pairs)), lib.p(lib.up(sub)), 2, lib.stream())
+             lib.p(lib.up(mn)), lib.p(lib.up(coff)), lib.p(lib.up(pp)), lib.p(lib.up(pairs)), lib.p(lib.up(sub)), 3, lib.stream())
     out2 = d_c2.cpu().numpy()
     for t, (M, N, Ks) in enumerate(problems):
         got = out2[coff[t]:coff[t] + M * N]
-        if t in (3, 5):
+        if t in (3, 5, 7):
             assert np.allclose(got, out[coff[t]:coff[t] + M * N], rtol=0, atol=0)
         else:
             assert np.all(got == 7.0)
