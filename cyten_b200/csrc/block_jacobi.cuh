@@ -1,0 +1,451 @@
+// One-sided BLOCK Jacobi for the large real sectors of svd / eigh (included by factorize.cu).
+//
+// The scalar kernel in factorize.cu streams two rows of W and Z through L2 for every plane rotation;
+// for a 1000 x 1000 sector that is ~30 GB of traffic per sweep and no tensor-core work.  Here the rows
+// are grouped in blocks of BJ_B = 32.  A work item is a pair of row blocks (I, J) of one matrix (or a
+// single block, for the rotations inside a block); one CTA
+//   1. forms the 64 x 64 Gram matrix G = R R^T of the item's rows R = [W_I; W_J] on the FP64 tensor
+//      pipe (DMMA m8n8k4, operands staged global -> shared with cp.async, double buffered),
+//   2. checks the item's pairs against the Jacobi criterion |g_pq| <= tol sqrt(g_pp g_qq) on this FRESH
+//      Gram matrix; if some pair fails, runs one cyclic pass of plane rotations over the item's pairs
+//      entirely in shared memory (32 disjoint rotations per step; G is updated two-sidedly, the product of
+//      the rotations is accumulated in Q),
+//   3. applies Q to the rows of W and of the accumulated transformation Z with DMMA GEMMs
+//      ([W_I; W_J] <- Q [W_I; W_J]), in place, 64 columns at a time.
+// The items of one round-robin round touch disjoint rows, so a round is one kernel launch over all
+// large sectors of the batch; a sweep = 1 launch for the within-block pairs + (#blocks - 1) launches
+// for the block pairs = every pair of rows exactly once (cyclic Jacobi ordering).  Convergence is decided
+// only on fresh Gram matrices, never on the two-sidedly updated ones.
+#pragma once
+
+namespace cyb {
+
+constexpr int BJ_B = 32;                 // rows per block
+constexpr int BJ_R = 2 * BJ_B;           // rows per work item
+constexpr int BJ_THREADS = 256;
+constexpr int BJ_BK = 32;                // k-chunk of the Gram product
+constexpr int BJ_LDT = BJ_BK + 4;        // 36: conflict-free fragment loads (ld = 4 mod 16)
+constexpr int BJ_LDQ = BJ_R + 4;         // 68
+constexpr int BJ_LDG = BJ_R + 1;         // 65
+constexpr int BJ_BN = 64;                // column chunk of the update
+constexpr int BJ_LDB = BJ_BN + 4;        // 68
+constexpr int BJ_SQ = BJ_R * BJ_LDQ;                       // doubles
+constexpr int BJ_SBUF_A = BJ_R * BJ_LDG + 2 * BJ_R * BJ_LDT;   // phases 1-2: G + two Gram tiles
+constexpr int BJ_SBUF_B = 2 * BJ_R * BJ_LDB;                   // phase 3: two update tiles (aliases the above)
+constexpr int BJ_SBUF = BJ_SBUF_A > BJ_SBUF_B ? BJ_SBUF_A : BJ_SBUF_B;
+constexpr size_t BJ_SMEM = sizeof(double) * (size_t)(BJ_SQ + BJ_SBUF);
+constexpr int BJ_KS = 256;               // columns per partial Gram matrix
+constexpr int BJ_AC = 128;               // columns per apply work unit
+constexpr size_t BJ_SMEM_GRAM = sizeof(double) * (size_t)(2 * BJ_R * BJ_LDT);
+constexpr size_t BJ_SMEM_ROT = sizeof(double) * (size_t)(2 * BJ_R * BJ_LDG);
+constexpr size_t BJ_SMEM_APPLY = sizeof(double) * (size_t)(BJ_SQ + BJ_SBUF_B);
+
+struct BjItem {
+    int32_t mat;     // index into the FzDesc table
+    int32_t i0, ni;  // rows [i0, i0 + ni) of block I  -> slots 0 .. 31
+    int32_t j0, nj;  // rows [j0, j0 + nj) of block J  -> slots 32 .. 63 (nj == 0: within-block item)
+    int32_t rowbase; // start of this matrix in the rowmap / norm2 arrays
+    int32_t w0, nw;  // this item's partial Gram matrices: work units [w0, w0 + nw) of its round
+};
+// A round runs as three launches so that the whole GPU works on it (an item alone on one SM would be a
+// ~150 us critical path per round, 31 rounds per sweep):
+//   bj_gram_kernel   one CTA per (item, slice of BJ_KS columns): partial 64 x 64 Gram matrix -> Gpart
+//   bj_rotate_kernel one CTA per item: sums the partials in a fixed order (deterministic), convergence
+//                    test, one cyclic pass of rotations in shared memory -> Q (or skip flag)
+//   bj_apply_kernel  one CTA per (item, W or Z, chunk of BJ_AC columns): rows <- Q rows, in place
+struct BjWork {
+    int32_t item;    // index into the round's item list
+    int32_t arg;     // gram: slice index; apply: (which << 24) | chunk, which = 0 (W) / 1 (Z)
+};
+// i0 / j0 are POSITIONS in the norm-sorted order of the rows (de Rijk): position -> physical row through
+// rowmap.  Sorting the rows by decreasing norm before every sweep gathers the (numerical) null space of a
+// rank-deficient sector in the trailing blocks, which restores fast convergence (numpy experiment:
+// 34 -> 12 sweeps for a rank-n/2 matrix); pairs of rows that are BOTH below the noise floor
+// (eps * r * ||A||_F) are left alone until the significant part has converged and are orthogonalised in
+// a second, much smaller, pass over the trailing blocks only.
+
+__device__ __forceinline__ void bj_cp8(void* smem, const void* g, bool pred)
+{
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    const int sz = pred ? 8 : 0;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" ::"r"(s), "l"(g), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void bj_cp16(void* smem, const void* g, bool pred)
+{
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    const int sz = pred ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(s), "l"(g), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void bj_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N> __device__ __forceinline__ void bj_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+__device__ __forceinline__ void bj_dmma(double& c0, double& c1, double a, double b)
+{
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
+// position of slot t in the sorted order (or -1)
+__device__ __forceinline__ int bj_pos(const BjItem& it, int t)
+{
+    if (t < BJ_B) return t < it.ni ? it.i0 + t : -1;
+    const int u = t - BJ_B;
+    return u < it.nj ? it.j0 + u : -1;
+}
+
+// stage rows x [col0, col0 + NC) of a row-major matrix (leading dimension ld, ncols valid columns) into
+// a shared tile [BJ_R][LDS]; missing rows / columns are zero-filled
+template <int NC, int LDS>
+__device__ __forceinline__ void bj_load_tile(double* tile, const double* __restrict__ base, int64_t ld,
+                                             int64_t ncols, int64_t col0, const int* s_rows, bool vec)
+{
+    const int tid = threadIdx.x;
+    if (vec) {
+        constexpr int CH = NC / 2;
+        for (int c = tid; c < BJ_R * CH; c += BJ_THREADS) {
+            const int t = c / CH, k = (c % CH) * 2;
+            const int row = s_rows[t];
+            const bool ok = row >= 0 && col0 + k < ncols;    // ld even and ncols == ld or ncols even: pairs never straddle
+            bj_cp16(tile + t * LDS + k, ok ? base + (int64_t)row * ld + col0 + k : base, ok);
+        }
+    } else {
+        for (int c = tid; c < BJ_R * NC; c += BJ_THREADS) {
+            const int t = c / NC, k = c % NC;
+            const int row = s_rows[t];
+            const bool ok = row >= 0 && col0 + k < ncols;
+            bj_cp8(tile + t * LDS + k, ok ? base + (int64_t)row * ld + col0 + k : base, ok);
+        }
+    }
+}
+
+// [rows of the item] <- Q [rows of the item] for columns [cbeg, cend) of one row-major matrix, 64 columns
+// per step, in place
+__device__ __forceinline__ void bj_apply(const double* sQ, double* sBuf, double* __restrict__ base, int64_t ld,
+                                         int64_t ncols, const int* s_rows, int64_t cbeg, int64_t cend)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int lr = lane >> 2, lc = lane & 3;
+    const int wm0 = (warp >> 1) * 16, wn0 = (warp & 1) * 32;
+    const bool vec = (ld & 1) == 0 && (ncols & 1) == 0;
+    if (cend > ncols) cend = ncols;
+    const int64_t nchunks = (cend - cbeg + BJ_BN - 1) / BJ_BN;
+    bj_load_tile<BJ_BN, BJ_LDB>(sBuf, base, ld, cend, cbeg, s_rows, vec);
+    bj_commit();
+    for (int64_t ch = 0; ch < nchunks; ++ch) {
+        double* cur = sBuf + (ch & 1) * (BJ_R * BJ_LDB);
+        if (ch + 1 < nchunks) bj_load_tile<BJ_BN, BJ_LDB>(sBuf + ((ch + 1) & 1) * (BJ_R * BJ_LDB), base, ld, cend, cbeg + (ch + 1) * BJ_BN, s_rows, vec);
+        bj_commit();
+        bj_wait<1>();
+        __syncthreads();
+        double acc[2][4][2];
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
+#pragma unroll 4
+        for (int kk = 0; kk < BJ_R; kk += 4) {
+            double a[2], b[4];
+#pragma unroll
+            for (int i = 0; i < 2; ++i) a[i] = sQ[(wm0 + i * 8 + lr) * BJ_LDQ + kk + lc];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = cur[(kk + lc) * BJ_LDB + wn0 + j * 8 + lr];
+#pragma unroll
+            for (int i = 0; i < 2; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) bj_dmma(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+        }
+        const int64_t n0 = cbeg + ch * BJ_BN;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const int row = s_rows[wm0 + i * 8 + lr];
+            if (row < 0) continue;
+            double* out = base + (int64_t)row * ld + n0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int col = wn0 + j * 8 + lc * 2;
+                if (vec) {
+                    if (n0 + col < cend) __stcg(reinterpret_cast<double2*>(out + col), make_double2(acc[i][j][0], acc[i][j][1]));
+                } else {
+                    if (n0 + col < cend) __stcg(out + col, acc[i][j][0]);
+                    if (n0 + col + 1 < cend) __stcg(out + col + 1, acc[i][j][1]);
+                }
+            }
+        }
+        __syncthreads();   // everybody is done with `cur` before it is refilled two chunks later
+    }
+    bj_wait<0>();
+}
+
+struct BjRot { int p, q; double cs, sn; };
+
+__device__ __forceinline__ void bj_fill_rows(int* s_rows, const BjItem& it, const int* __restrict__ rowmap)
+{
+    if (threadIdx.x < BJ_R) {
+        const int pos = bj_pos(it, threadIdx.x);
+        s_rows[threadIdx.x] = pos >= 0 ? rowmap[it.rowbase + pos] : -1;
+    }
+}
+
+// ---- 1. partial Gram matrices -----------------------------------------------------------------
+__global__ void __launch_bounds__(BJ_THREADS, 3)
+bj_gram_kernel(const double* __restrict__ ws, const FzDesc* __restrict__ descs, const BjItem* __restrict__ items,
+               const BjWork* __restrict__ works, const int* __restrict__ active, const int* __restrict__ rowmap,
+               double* __restrict__ gpart)
+{
+    extern __shared__ __align__(16) double bj_smem[];
+    double* sT = bj_smem;                    // two tiles [64][36]
+    __shared__ int s_rows[BJ_R];
+    const BjWork wk = works[blockIdx.x];
+    const BjItem it = items[wk.item];
+    if (!active[it.mat]) return;
+    bj_fill_rows(s_rows, it, rowmap);
+    const FzDesc D = descs[it.mat];
+    const int64_t c = D.c;
+    const double* W = ws + D.w_off;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int lr = lane >> 2, lc = lane & 3;
+    const bool vec = (c & 1) == 0;
+    const int wm0 = (warp >> 2) * 32, wn0 = (warp & 3) * 16;
+    const int64_t k_beg = (int64_t)wk.arg * BJ_KS;
+    const int64_t k_end = k_beg + BJ_KS < c ? k_beg + BJ_KS : c;
+    __syncthreads();
+    double acc[4][2][2];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
+    const int64_t nk = (k_end - k_beg + BJ_BK - 1) / BJ_BK;
+    bj_load_tile<BJ_BK, BJ_LDT>(sT, W, c, k_end, k_beg, s_rows, vec);
+    bj_commit();
+    for (int64_t kc = 0; kc < nk; ++kc) {
+        const double* cur = sT + (kc & 1) * (BJ_R * BJ_LDT);
+        if (kc + 1 < nk) bj_load_tile<BJ_BK, BJ_LDT>(sT + ((kc + 1) & 1) * (BJ_R * BJ_LDT), W, c, k_end, k_beg + (kc + 1) * BJ_BK, s_rows, vec);
+        bj_commit();
+        bj_wait<1>();
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < BJ_BK; kk += 4) {
+            double a[4], b[2];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) a[i] = cur[(wm0 + i * 8 + lr) * BJ_LDT + kk + lc];
+#pragma unroll
+            for (int j = 0; j < 2; ++j) b[j] = cur[(wn0 + j * 8 + lr) * BJ_LDT + kk + lc];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 2; ++j) bj_dmma(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+        }
+        __syncthreads();
+    }
+    bj_wait<0>();
+    double* out = gpart + (size_t)blockIdx.x * (BJ_R * BJ_R);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int row = wm0 + i * 8 + lr, col = wn0 + j * 8 + lc * 2;
+            __stcg(reinterpret_cast<double2*>(out + row * BJ_R + col), make_double2(acc[i][j][0], acc[i][j][1]));
+        }
+}
+
+// ---- 2. convergence test + one cyclic pass of rotations ----------------------------------------------
+__global__ void __launch_bounds__(BJ_THREADS)
+bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ items, const int* __restrict__ active,
+                 int* __restrict__ flags, const double* __restrict__ floor2, int use_floor,
+                 const double* __restrict__ gpart, double* __restrict__ qbuf, int* __restrict__ skip)
+{
+    extern __shared__ __align__(16) double bj_smem[];
+    double* sG = bj_smem;                    // [64][65]
+    double* sQ = bj_smem + BJ_R * BJ_LDG;    // [64][65]
+    __shared__ BjRot s_rot[BJ_B];
+    __shared__ int s_any;
+    const BjItem it = items[blockIdx.x];
+    const int tid = threadIdx.x;
+    if (!active[it.mat]) { if (tid == 0) skip[blockIdx.x] = 1; return; }
+    const double fl = use_floor ? floor2[it.mat] : 0.0;
+    const double tol = FZ_EPS * sqrt((double)descs[it.mat].c);
+    const double tol2 = tol * tol;
+    const bool cross = it.nj > 0;
+    // G = sum of the partials, in slice order
+    for (int e = tid; e < BJ_R * BJ_R; e += BJ_THREADS) {
+        double g = 0.0;
+        for (int w = 0; w < it.nw; ++w) g += __ldcg(gpart + (size_t)(it.w0 + w) * (BJ_R * BJ_R) + e);
+        sG[(e / BJ_R) * BJ_LDG + e % BJ_R] = g;
+    }
+    if (tid == 0) s_any = 0;
+    __syncthreads();
+    {
+        int bad = 0;
+        for (int e = tid; e < BJ_B * BJ_B; e += BJ_THREADS) {
+            int p, q;
+            bool valid;
+            if (cross) { p = e / BJ_B; q = BJ_B + e % BJ_B; valid = p < it.ni && q - BJ_B < it.nj; }
+            else { p = e / BJ_B; q = e % BJ_B; valid = p < q && q < it.ni; }
+            if (valid) {
+                const double al = sG[p * BJ_LDG + p], be = sG[q * BJ_LDG + q], ga = sG[p * BJ_LDG + q];
+                bad |= (al >= FZ_TINY && be >= FZ_TINY && !(al <= fl && be <= fl) && ga * ga > tol2 * al * be);
+            }
+        }
+        if (bad) s_any = 1;
+        __syncthreads();
+        if (!s_any) { if (tid == 0) skip[blockIdx.x] = 1; return; }   // every pair of this item is orthogonal
+        if (tid == 0) { flags[it.mat] = 1; skip[blockIdx.x] = 0; }
+    }
+    for (int e = tid; e < BJ_R * BJ_R; e += BJ_THREADS) sQ[(e / BJ_R) * BJ_LDG + e % BJ_R] = (e / BJ_R == e % BJ_R) ? 1.0 : 0.0;
+    const int nsteps = cross ? BJ_B : BJ_B - 1;
+    const int nrot = cross ? BJ_B : BJ_B / 2;
+    __syncthreads();
+    for (int step = 0; step < nsteps; ++step) {
+        if (tid < nrot) {
+            int p, q;
+            bool valid;
+            if (cross) {
+                p = tid; q = BJ_B + (tid + step) % BJ_B;
+                valid = p < it.ni && q - BJ_B < it.nj;
+            } else {
+                if (tid == 0) { p = BJ_B - 1; q = step; }
+                else { p = (step + tid) % (BJ_B - 1); q = (step - tid + (BJ_B - 1)) % (BJ_B - 1); }
+                if (p > q) { const int t = p; p = q; q = t; }
+                valid = q < it.ni;
+            }
+            double cs = 1.0, sn = 0.0;
+            if (valid) {
+                const double al = sG[p * BJ_LDG + p], be = sG[q * BJ_LDG + q], ga = sG[p * BJ_LDG + q];
+                if (al >= FZ_TINY && be >= FZ_TINY && !(al <= fl && be <= fl) && ga * ga > tol2 * al * be) {
+                    const double zeta = (be - al) / (2.0 * ga);
+                    const double t = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+                    cs = 1.0 / sqrt(1.0 + t * t);
+                    sn = cs * t;
+                }
+            }
+            s_rot[tid].p = p; s_rot[tid].q = q; s_rot[tid].cs = cs; s_rot[tid].sn = sn;
+        }
+        __syncthreads();
+        // rows p, q of G and Q:  x <- cs x - sn y,  y <- sn x + cs y
+        for (int e = tid; e < nrot * BJ_R; e += BJ_THREADS) {
+            const BjRot R = s_rot[e / BJ_R];
+            if (R.sn == 0.0) continue;
+            const int col = e % BJ_R;
+            double x = sG[R.p * BJ_LDG + col], y = sG[R.q * BJ_LDG + col];
+            sG[R.p * BJ_LDG + col] = R.cs * x - R.sn * y;
+            sG[R.q * BJ_LDG + col] = R.sn * x + R.cs * y;
+            x = sQ[R.p * BJ_LDG + col]; y = sQ[R.q * BJ_LDG + col];
+            sQ[R.p * BJ_LDG + col] = R.cs * x - R.sn * y;
+            sQ[R.q * BJ_LDG + col] = R.sn * x + R.cs * y;
+        }
+        __syncthreads();
+        // columns p, q of G
+        for (int e = tid; e < nrot * BJ_R; e += BJ_THREADS) {
+            const BjRot R = s_rot[e / BJ_R];
+            if (R.sn == 0.0) continue;
+            const int row = e % BJ_R;
+            const double x = sG[row * BJ_LDG + R.p], y = sG[row * BJ_LDG + R.q];
+            sG[row * BJ_LDG + R.p] = R.cs * x - R.sn * y;
+            sG[row * BJ_LDG + R.q] = R.sn * x + R.cs * y;
+        }
+        __syncthreads();
+    }
+    double* out = qbuf + (size_t)blockIdx.x * (BJ_R * BJ_R);
+    for (int e = tid; e < BJ_R * BJ_R; e += BJ_THREADS) __stcg(out + e, sQ[(e / BJ_R) * BJ_LDG + e % BJ_R]);
+}
+
+// ---- 3. rows <- Q rows -------------------------------------------------------------------------------
+__global__ void __launch_bounds__(BJ_THREADS, 2)
+bj_apply_kernel(double* __restrict__ ws, const FzDesc* __restrict__ descs, const BjItem* __restrict__ items,
+                const BjWork* __restrict__ works, const int* __restrict__ rowmap, const double* __restrict__ qbuf,
+                const int* __restrict__ skip)
+{
+    extern __shared__ __align__(16) double bj_smem[];
+    double* sQ = bj_smem;                    // [64][68]
+    double* sBuf = bj_smem + BJ_SQ;          // two tiles [64][68]
+    __shared__ int s_rows[BJ_R];
+    const BjWork wk = works[blockIdx.x];
+    if (skip[wk.item]) return;
+    const BjItem it = items[wk.item];
+    bj_fill_rows(s_rows, it, rowmap);
+    const double* q = qbuf + (size_t)wk.item * (BJ_R * BJ_R);
+    for (int e = threadIdx.x; e < BJ_R * BJ_R / 2; e += BJ_THREADS) {
+        const double2 v = __ldcg(reinterpret_cast<const double2*>(q) + e);
+        const int row = (2 * e) / BJ_R, col = (2 * e) % BJ_R;
+        sQ[row * BJ_LDQ + col] = v.x;
+        sQ[row * BJ_LDQ + col + 1] = v.y;
+    }
+    __syncthreads();
+    const FzDesc D = descs[it.mat];
+    const int which = wk.arg >> 24;
+    const int64_t cbeg = (int64_t)(wk.arg & 0xffffff) * BJ_AC;
+    if (which == 0) bj_apply(sQ, sBuf, ws + D.w_off, D.c, D.c, s_rows, cbeg, cbeg + BJ_AC);
+    else bj_apply(sQ, sBuf, ws + D.z_off, D.r, D.r, s_rows, cbeg, cbeg + BJ_AC);
+}
+
+// squared row norms of the working copies: one warp per row, grid-stride over (matrix, row)
+__global__ void __launch_bounds__(256)
+bj_norms_kernel(const double* __restrict__ ws, const FzDesc* __restrict__ descs, const int64_t* __restrict__ mats,
+                const int* __restrict__ rowbase, int nmats, double* __restrict__ norm2)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t gwarp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int64_t total = rowbase[nmats];
+    for (int64_t g = gwarp; g < total; g += nwarps) {
+        int lo = 0, hi = nmats;
+        while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (rowbase[mid] <= g) lo = mid; else hi = mid; }
+        const FzDesc D = descs[mats[lo]];
+        const double* x = ws + D.w_off + (g - rowbase[lo]) * D.c;
+        double acc = 0.0;
+        for (int64_t q = lane; q < D.c; q += 32) { const double v = __ldcg(x + q); acc = fma(v, v, acc); }
+        acc = warp_sum(acc);
+        if (lane == 0) norm2[g] = acc;
+    }
+}
+
+// one CTA per matrix: rows ranked by decreasing norm (ties: lower row first) -> rowmap; with `init`
+// also the noise floor (eps r)^2 ||A||_F^2; nnoise = number of rows at or below the floor
+__global__ void __launch_bounds__(1024)
+bj_sort_kernel(const FzDesc* __restrict__ descs, const int64_t* __restrict__ mats, const int* __restrict__ rowbase,
+               const double* __restrict__ norm2, int* __restrict__ rowmap, double* __restrict__ floor2,
+               int* __restrict__ nnoise, const int* __restrict__ active, int init)
+{
+    const int64_t mat = mats[blockIdx.x];
+    if (!init && !active[mat]) return;
+    const int r = (int)descs[mat].r;
+    const int base = rowbase[blockIdx.x];
+    const double* key = norm2 + base;
+    __shared__ double s_red[32];
+    __shared__ int s_cnt;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (init) {
+        double acc = 0.0;
+        for (int i = tid; i < r; i += 1024) acc += key[i];
+        acc = warp_sum(acc);
+        if (lane == 0) s_red[warp] = acc;
+        __syncthreads();
+        if (tid == 0) {
+            double t = 0.0;
+            for (int w = 0; w < 32; ++w) t += s_red[w];
+            const double er = FZ_EPS * (double)r;
+            floor2[mat] = er * er * t;
+        }
+        __syncthreads();
+    }
+    const double fl = floor2[mat];
+    if (tid == 0) s_cnt = 0;
+    __syncthreads();
+    int cnt = 0;
+    for (int i = tid; i < r; i += 1024) {
+        const double ki = key[i];
+        int rank = 0;
+        for (int j = 0; j < r; ++j) {
+            const double kj = key[j];
+            rank += (kj > ki) || (kj == ki && j < i);
+        }
+        rowmap[base + rank] = i;
+        cnt += (ki <= fl);
+    }
+    if (cnt) atomicAdd(&s_cnt, cnt);
+    __syncthreads();
+    if (tid == 0) nnoise[mat] = s_cnt;
+}
+
+}  // namespace cyb

@@ -20,6 +20,7 @@
 #include "common.cuh"
 #include <vector>
 #include <cmath>
+#include <algorithm>
 
 namespace cyb {
 
@@ -106,7 +107,12 @@ struct FzDesc {
 //                                   rot_count[FZ_MAX_SWEEPS+1] (uint64) | pdiag[c] | misc[8]
 __host__ __device__ inline int64_t svd_aux_doubles(int64_t r, int64_t c) { return 2 * r + 2 * r + (FZ_MAX_SWEEPS + 1) + c + 8; }
 
-template <bool CX, int G, bool EIGH>
+// PH selects the phases a launch runs: 1 = load the working copy, 2 = scalar Jacobi sweeps,
+// 4 = ordering / normalisation / outputs.  Small sectors run all three in one launch (PH = 7); large
+// real sectors run 1, then the block-Jacobi rounds (bj_pair_kernel below), then 4.
+constexpr int PH_INIT = 1, PH_SWEEPS = 2, PH_FINISH = 4, PH_ALL = 7;
+
+template <bool CX, int G, bool EIGH, int PH>
 __global__ void __launch_bounds__(FZ_THREADS, 1)
 jacobi_svd_kernel(const void* __restrict__ a_, void* __restrict__ o0_, double* __restrict__ s_out,
                   void* __restrict__ o2_, void* __restrict__ ws_, double* __restrict__ aux_,
@@ -135,8 +141,10 @@ jacobi_svd_kernel(const void* __restrict__ a_, void* __restrict__ o0_, double* _
     __shared__ double s_red[FZ_WARPS];
     __shared__ unsigned long long s_cnt;
 
+    if (!(PH & PH_INIT)) sigma = __ldcg(&misc[2]);
     // ---- load working copy, Z = I ----
-    if (EIGH) {
+    if (!(PH & PH_INIT)) {
+    } else if (EIGH) {
         // sigma = 1.5 * ||H||_F  (every CTA of the team computes it redundantly, deterministic)
         double acc = 0.0;
         for (int64_t e = tid; e < r * c; e += FZ_THREADS) acc += E::abs2(A[e]);
@@ -165,9 +173,13 @@ jacobi_svd_kernel(const void* __restrict__ a_, void* __restrict__ o0_, double* _
     } else {
         for (int64_t e = gtid; e < r * c; e += gthreads) E::stcg(&W[e], A[e]);
     }
-    for (int64_t e = gtid; e < r * r; e += gthreads) E::stcg(&Z[e], (e / r == e % r) ? E::one() : E::zero());
-    for (int64_t e = gtid; e < FZ_MAX_SWEEPS + 1; e += gthreads) rot_count[e] = 0ull;
+    if (PH & PH_INIT) {
+        for (int64_t e = gtid; e < r * r; e += gthreads) E::stcg(&Z[e], (e / r == e % r) ? E::one() : E::zero());
+        for (int64_t e = gtid; e < FZ_MAX_SWEEPS + 1; e += gthreads) rot_count[e] = 0ull;
+        if (gtid == 0) __stcg(&misc[2], sigma);
+    }
     Team<G>::sync();
+    if (!(PH & (PH_SWEEPS | PH_FINISH))) return;
 
     // ---- Jacobi sweeps ----
     const double tol = FZ_EPS * sqrt((double)c);
@@ -175,7 +187,7 @@ jacobi_svd_kernel(const void* __restrict__ a_, void* __restrict__ o0_, double* _
     const int64_t rounds = rp - 1, npairs = rp / 2;
     int sweeps_done = 0;
     bool converged = (r < 2);
-    for (int sweep = 0; sweep < FZ_MAX_SWEEPS && !converged; ++sweep) {
+    for (int sweep = 0; (PH & PH_SWEEPS) && sweep < FZ_MAX_SWEEPS && !converged; ++sweep) {
         unsigned long long my_rot = 0ull;
         for (int64_t round = 0; round < rounds; ++round) {
             for (int64_t k = gwarp; k < npairs; k += gwarps) {
@@ -234,6 +246,7 @@ jacobi_svd_kernel(const void* __restrict__ a_, void* __restrict__ o0_, double* _
         converged = (total == 0ull);
     }
 
+    if (!(PH & PH_FINISH)) return;
     // ---- singular values, ordering ----
     for (int64_t i = gwarp; i < r; i += gwarps) {
         double acc = 0.0;
@@ -369,9 +382,13 @@ jacobi_svd_kernel(const void* __restrict__ a_, void* __restrict__ o0_, double* _
             }
         }
     }
-    if (gtid == 0) info[mat] = converged ? (sweeps_done > 0 ? sweeps_done : 1) : -(sweeps_done > 0 ? sweeps_done : 1);
+    if ((PH & PH_SWEEPS) && gtid == 0) info[mat] = converged ? (sweeps_done > 0 ? sweeps_done : 1) : -(sweeps_done > 0 ? sweeps_done : 1);
     (void)m;
 }
+
+}  // namespace cyb
+#include "block_jacobi.cuh"
+namespace cyb {
 
 // ---- QR ---------------------------------------------------------------------------------------
 // Working copy Wt = A^T (n x m): row i of Wt is column i of A.  Hermitian Householder reflectors
@@ -509,6 +526,217 @@ static cudaError_t launch_team(K kernel, int G, int nteams, cudaStream_t stream,
 constexpr int FZ_BIG_G = 8;          // CTAs per team for large sectors (portable cluster size)
 constexpr int64_t FZ_BIG_MIN = 96;   // working rows from which a team is used
 
+// Host driver of the block Jacobi: load phase, sweeps of (sort + 1 + #block-pair rounds) launches, a
+// second pass over the noise rows, output phase.
+struct BjRounds {
+    std::vector<std::vector<BjItem>> rounds;   // rounds[0]: within-block items; rounds[1 + t]: block pairs of round t
+    std::vector<BjItem> flat;                  // all rounds back to back
+    std::vector<BjWork> gworks, aworks;        // Gram / apply work units of all rounds back to back
+    std::vector<size_t> start, gstart, astart; // per round offsets (+ one past the end)
+    size_t max_items = 0, max_gworks = 0;
+};
+
+// items over the blocks [kb[mat], nb) of every listed matrix
+static void bj_build_rounds(BjRounds& R, const std::vector<FzDesc>& descs, const std::vector<int64_t>& mats,
+                            const std::vector<int>& rowbase, const std::vector<int>& first_block)
+{
+    R.rounds.assign(1, {});
+    for (size_t q = 0; q < mats.size(); ++q) {
+        const int64_t mat = mats[q];
+        const int64_t r = descs[(size_t)mat].r;
+        const int nb_all = (int)((r + BJ_B - 1) / BJ_B);
+        const int kb = first_block[q];
+        const int nb = nb_all - kb;
+        if (nb <= 0) continue;
+        auto rows_of = [&](int k, int32_t& r0, int32_t& n) { r0 = (kb + k) * BJ_B; n = (int32_t)std::min<int64_t>(BJ_B, r - (int64_t)(kb + k) * BJ_B); };
+        for (int k = 0; k < nb; ++k) {
+            BjItem it{(int32_t)mat, 0, 0, 0, 0, rowbase[q], 0, 0};
+            rows_of(k, it.i0, it.ni);
+            if (it.ni > 1) R.rounds[0].push_back(it);
+        }
+        const int np = nb + (nb & 1);
+        if (np < 2) continue;
+        if ((int)R.rounds.size() < np) R.rounds.resize((size_t)np);
+        for (int t = 0; t < np - 1; ++t)
+            for (int k = 0; k < np / 2; ++k) {
+                int i = (k == 0) ? np - 1 : (t + k) % (np - 1);
+                int j = (k == 0) ? t : (t - k + (np - 1)) % (np - 1);
+                if (i > j) std::swap(i, j);
+                if (j >= nb) continue;
+                BjItem it{(int32_t)mat, 0, 0, 0, 0, rowbase[q], 0, 0};
+                rows_of(i, it.i0, it.ni);
+                rows_of(j, it.j0, it.nj);
+                R.rounds[(size_t)(1 + t)].push_back(it);
+            }
+    }
+    // the most expensive items (longest rows) first within every round; work units of the three kernels
+    R.flat.clear(); R.gworks.clear(); R.aworks.clear();
+    R.start.clear(); R.gstart.clear(); R.astart.clear();
+    R.max_items = R.max_gworks = 0;
+    for (auto& rd : R.rounds) {
+        std::stable_sort(rd.begin(), rd.end(), [&](const BjItem& x, const BjItem& y) {
+            return descs[(size_t)x.mat].c + descs[(size_t)x.mat].r > descs[(size_t)y.mat].c + descs[(size_t)y.mat].r; });
+        R.start.push_back(R.flat.size());
+        R.gstart.push_back(R.gworks.size());
+        R.astart.push_back(R.aworks.size());
+        int32_t w = 0;
+        for (size_t idx = 0; idx < rd.size(); ++idx) {
+            const FzDesc& D = descs[(size_t)rd[idx].mat];
+            const int32_t nsl = (int32_t)((D.c + BJ_KS - 1) / BJ_KS);
+            rd[idx].w0 = w; rd[idx].nw = nsl;
+            for (int32_t sl = 0; sl < nsl; ++sl) R.gworks.push_back(BjWork{(int32_t)idx, sl});
+            w += nsl;
+            for (int32_t ch = 0; ch < (int32_t)((D.c + BJ_AC - 1) / BJ_AC); ++ch) R.aworks.push_back(BjWork{(int32_t)idx, ch});
+            for (int32_t ch = 0; ch < (int32_t)((D.r + BJ_AC - 1) / BJ_AC); ++ch) R.aworks.push_back(BjWork{(int32_t)idx, (1 << 24) | ch});
+        }
+        R.max_items = std::max(R.max_items, rd.size());
+        R.max_gworks = std::max(R.max_gworks, (size_t)w);
+        R.flat.insert(R.flat.end(), rd.begin(), rd.end());
+    }
+    R.start.push_back(R.flat.size());
+    R.gstart.push_back(R.gworks.size());
+    R.astart.push_back(R.aworks.size());
+}
+
+template <bool EIGH>
+static int run_block_jacobi(const void* a, void* o0, double* s_out, void* o2, void* d_ws, double* d_aux,
+                            FzDesc* d_desc, const std::vector<FzDesc>& descs, const std::vector<int64_t>& big,
+                            const int64_t* sel_big, int64_t* info, cudaStream_t stream)
+{
+    static bool configured = false;
+    if (!configured) {
+        CYB_CHECK_CUDA(cudaFuncSetAttribute(bj_gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BJ_SMEM_GRAM));
+        CYB_CHECK_CUDA(cudaFuncSetAttribute(bj_rotate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BJ_SMEM_ROT));
+        CYB_CHECK_CUDA(cudaFuncSetAttribute(bj_apply_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BJ_SMEM_APPLY));
+        configured = true;
+    }
+    const int nbig = (int)big.size();
+    const size_t nmat = descs.size();
+    cudaError_t err = launch_team(jacobi_svd_kernel<false, FZ_BIG_G, EIGH, PH_INIT>, FZ_BIG_G, nbig, stream,
+                                  a, o0, s_out, o2, d_ws, d_aux, d_desc, sel_big, info);
+    if (err != cudaSuccess) { set_error("block jacobi: load launch failed: %s", cudaGetErrorString(err)); return CYB_ERR_CUDA; }
+    std::vector<int> rowbase((size_t)nbig + 1, 0);
+    for (int q = 0; q < nbig; ++q) rowbase[(size_t)q + 1] = rowbase[(size_t)q] + (int)descs[(size_t)big[(size_t)q]].r;
+    const size_t nrows = (size_t)rowbase[(size_t)nbig];
+    BjRounds R1, R2;
+    bj_build_rounds(R1, descs, big, rowbase, std::vector<int>((size_t)nbig, 0));
+    // device scratch: items | Gram works | apply works (pass-2 lists are never longer than pass-1 ones) |
+    //                 active | flags | nnoise | rowbase | rowmap | norm2 | floor2 | skip | Gpart | Q
+    const size_t items_bytes = align_up(sizeof(BjItem) * std::max<size_t>(R1.flat.size(), 1), 256);
+    const size_t gw_bytes = align_up(sizeof(BjWork) * std::max<size_t>(R1.gworks.size(), 1), 256);
+    const size_t aw_bytes = align_up(sizeof(BjWork) * std::max<size_t>(R1.aworks.size(), 1), 256);
+    const size_t skip_bytes = align_up(sizeof(int) * std::max<size_t>(R1.max_items, 1), 256);
+    const size_t gpart_bytes = align_up(sizeof(double) * BJ_R * BJ_R * std::max<size_t>(R1.max_gworks, 1), 256);
+    const size_t q_bytes = align_up(sizeof(double) * BJ_R * BJ_R * std::max<size_t>(R1.max_items, 1), 256);
+    const size_t ints_bytes = align_up(sizeof(int) * nmat, 256);
+    const size_t rb_bytes = align_up(sizeof(int) * ((size_t)nbig + 1), 256);
+    const size_t map_bytes = align_up(sizeof(int) * std::max<size_t>(nrows, 1), 256);
+    const size_t nrm_bytes = align_up(sizeof(double) * std::max<size_t>(nrows, 1), 256);
+    const size_t fl_bytes = align_up(sizeof(double) * nmat, 256);
+    Scratch scr(items_bytes + gw_bytes + aw_bytes + 3 * ints_bytes + rb_bytes + map_bytes + nrm_bytes + fl_bytes +
+                skip_bytes + gpart_bytes + q_bytes, stream);
+    if (!scr.ptr) return CYB_ERR_CUDA;
+    size_t o = 0;
+    BjItem* d_items = scr.as<BjItem>(o); o += items_bytes;
+    BjWork* d_gworks = scr.as<BjWork>(o); o += gw_bytes;
+    BjWork* d_aworks = scr.as<BjWork>(o); o += aw_bytes;
+    int* d_active = scr.as<int>(o); o += ints_bytes;
+    int* d_flags = scr.as<int>(o); o += ints_bytes;
+    int* d_nnoise = scr.as<int>(o); o += ints_bytes;
+    int* d_rowbase = scr.as<int>(o); o += rb_bytes;
+    int* d_rowmap = scr.as<int>(o); o += map_bytes;
+    double* d_norm2 = scr.as<double>(o); o += nrm_bytes;
+    double* d_floor2 = scr.as<double>(o); o += fl_bytes;
+    int* d_skip = scr.as<int>(o); o += skip_bytes;
+    double* d_gpart = scr.as<double>(o); o += gpart_bytes;
+    double* d_qbuf = scr.as<double>(o);
+    std::vector<int> active(nmat, 0), flags(nmat, 0), nnoise(nmat, 0);
+    std::vector<int64_t> sweeps(nmat, 0);
+    for (int64_t mat : big) active[(size_t)mat] = 1;
+    CYB_CHECK_CUDA(cudaMemcpyAsync(d_rowbase, rowbase.data(), sizeof(int) * rowbase.size(), cudaMemcpyHostToDevice, stream));
+    CYB_CHECK_CUDA(cudaMemsetAsync(d_floor2, 0, sizeof(double) * nmat, stream));
+    const int norm_grid = sm_count() * 4;
+    auto sort_rows = [&](int init) {
+        bj_norms_kernel<<<norm_grid, 256, 0, stream>>>(static_cast<const double*>(d_ws), d_desc, sel_big, d_rowbase, nbig, d_norm2);
+        bj_sort_kernel<<<nbig, 1024, 0, stream>>>(d_desc, sel_big, d_rowbase, d_norm2, d_rowmap, d_floor2, d_nnoise, d_active, init);
+    };
+    // runs sweeps over the item lists of R until no item rotates; returns false on a CUDA error
+    auto run_sweeps = [&](const BjRounds& R, bool phase1) -> int {
+        if (R.flat.empty()) return CYB_OK;
+        CYB_CHECK_CUDA(cudaMemcpyAsync(d_items, R.flat.data(), sizeof(BjItem) * R.flat.size(), cudaMemcpyHostToDevice, stream));
+        CYB_CHECK_CUDA(cudaMemcpyAsync(d_gworks, R.gworks.data(), sizeof(BjWork) * R.gworks.size(), cudaMemcpyHostToDevice, stream));
+        CYB_CHECK_CUDA(cudaMemcpyAsync(d_aworks, R.aworks.data(), sizeof(BjWork) * R.aworks.size(), cudaMemcpyHostToDevice, stream));
+        bool any = false;
+        for (size_t m = 0; m < nmat; ++m) any = any || active[m];
+        for (int sweep = 0; sweep < FZ_MAX_SWEEPS && any; ++sweep) {
+            CYB_CHECK_CUDA(cudaMemcpyAsync(d_active, active.data(), sizeof(int) * nmat, cudaMemcpyHostToDevice, stream));
+            CYB_CHECK_CUDA(cudaMemsetAsync(d_flags, 0, sizeof(int) * nmat, stream));
+            if (phase1) sort_rows(sweep == 0);
+            for (size_t rd = 0; rd < R.rounds.size(); ++rd) {
+                bool live = false;   // skip rounds whose items all belong to converged matrices
+                for (const BjItem& it : R.rounds[rd]) if (active[(size_t)it.mat]) { live = true; break; }
+                if (!live) continue;
+                const unsigned ni = (unsigned)R.rounds[rd].size();
+                const unsigned ng = (unsigned)(R.gstart[rd + 1] - R.gstart[rd]), na = (unsigned)(R.astart[rd + 1] - R.astart[rd]);
+                bj_gram_kernel<<<ng, BJ_THREADS, BJ_SMEM_GRAM, stream>>>(
+                    static_cast<const double*>(d_ws), d_desc, d_items + R.start[rd], d_gworks + R.gstart[rd], d_active, d_rowmap, d_gpart);
+                bj_rotate_kernel<<<ni, BJ_THREADS, BJ_SMEM_ROT, stream>>>(
+                    d_desc, d_items + R.start[rd], d_active, d_flags, d_floor2, phase1 ? 1 : 0, d_gpart, d_qbuf, d_skip);
+                bj_apply_kernel<<<na, BJ_THREADS, BJ_SMEM_APPLY, stream>>>(
+                    static_cast<double*>(d_ws), d_desc, d_items + R.start[rd], d_aworks + R.astart[rd], d_rowmap, d_qbuf, d_skip);
+            }
+            CYB_LAUNCH_CHECK();
+            CYB_CHECK_CUDA(cudaMemcpyAsync(flags.data(), d_flags, sizeof(int) * nmat, cudaMemcpyDeviceToHost, stream));
+            CYB_CHECK_CUDA(cudaStreamSynchronize(stream));
+            any = false;
+            for (size_t m = 0; m < nmat; ++m) {
+                if (!active[m]) continue;
+                sweeps[m] += 1;
+                active[m] = flags[m];
+                any = any || flags[m];
+            }
+        }
+        return CYB_OK;
+    };
+    // ---- pass 1: all rows, pairs of two noise rows left alone ----
+    int rc = run_sweeps(R1, true);
+    if (rc != CYB_OK) return rc;
+    bool failed = false;
+    for (size_t m = 0; m < nmat; ++m) failed = failed || active[m];
+    // ---- pass 2: orthogonalise the noise rows among themselves (trailing blocks of the sorted order) ----
+    if (!failed) {
+        for (int64_t mat : big) active[(size_t)mat] = 1;
+        CYB_CHECK_CUDA(cudaMemcpyAsync(d_active, active.data(), sizeof(int) * nmat, cudaMemcpyHostToDevice, stream));
+        sort_rows(0);
+        CYB_LAUNCH_CHECK();
+        CYB_CHECK_CUDA(cudaMemcpyAsync(nnoise.data(), d_nnoise, sizeof(int) * nmat, cudaMemcpyDeviceToHost, stream));
+        CYB_CHECK_CUDA(cudaStreamSynchronize(stream));
+        std::vector<int> first_block((size_t)nbig, 0);
+        for (int q = 0; q < nbig; ++q) {
+            const int64_t mat = big[(size_t)q];
+            const int64_t r = descs[(size_t)mat].r;
+            const int nn = nnoise[(size_t)mat];
+            active[(size_t)mat] = nn > 1;
+            first_block[(size_t)q] = nn > 1 ? (int)((r - nn) / BJ_B) : (int)((r + BJ_B - 1) / BJ_B);
+        }
+        bj_build_rounds(R2, descs, big, rowbase, first_block);
+        rc = run_sweeps(R2, false);
+        if (rc != CYB_OK) return rc;
+    }
+    err = launch_team(jacobi_svd_kernel<false, FZ_BIG_G, EIGH, PH_FINISH>, FZ_BIG_G, nbig, stream,
+                      a, o0, s_out, o2, d_ws, d_aux, d_desc, sel_big, info);
+    if (err != cudaSuccess) { set_error("block jacobi: output launch failed: %s", cudaGetErrorString(err)); return CYB_ERR_CUDA; }
+    // info: sweeps used (negative: not converged within FZ_MAX_SWEEPS)
+    std::vector<int64_t> vals((size_t)nbig);
+    for (int q = 0; q < nbig; ++q) {
+        const size_t mat = (size_t)big[(size_t)q];
+        vals[(size_t)q] = std::max<int64_t>(sweeps[mat], 1) * (active[mat] ? -1 : 1);
+        CYB_CHECK_CUDA(cudaMemcpyAsync(info + mat, &vals[(size_t)q], sizeof(int64_t), cudaMemcpyHostToDevice, stream));
+    }
+    CYB_CHECK_CUDA(cudaStreamSynchronize(stream));   // the host vectors must outlive the copies
+    return CYB_OK;
+}
+
 static int run_factorize(FzKind kind, const void* a, void* o0, double* o1d, void* o1, void* o2,
                          const int64_t* desc_host, int64_t nmat, int dtype, int64_t* info,
                          cudaStream_t stream)
@@ -565,21 +793,29 @@ static int run_factorize(FzKind kind, const void* a, void* o0, double* o1d, void
     cudaError_t err = cudaSuccess;
 #define FZ_LAUNCH(KERN, G, NT, ...) \
     do { if ((NT) > 0) { err = launch_team(KERN, G, (int)(NT), stream, __VA_ARGS__); if (err != cudaSuccess) { set_error("factorize launch failed: %s", cudaGetErrorString(err)); return CYB_ERR_CUDA; } } } while (0)
+    if (!cx && kind != FZ_QR && !big.empty()) {
+        // large real sectors: block Jacobi (block_jacobi.cuh) between the load and the output phases
+        const int rc = (kind == FZ_EIGH)
+            ? run_block_jacobi<true>(a, o0, o1d, o2, d_ws, d_aux, d_desc, descs, big, sel_big, info, stream)
+            : run_block_jacobi<false>(a, o0, o1d, o2, d_ws, d_aux, d_desc, descs, big, sel_big, info, stream);
+        if (rc != CYB_OK) return rc;
+        big.clear();
+    }
     if (kind == FZ_SVD) {
         if (cx) {
-            FZ_LAUNCH((jacobi_svd_kernel<true, 1, false>), 1, small.size(), a, o0, o1d, o2, d_ws, d_aux, d_desc, sel_small, info);
-            FZ_LAUNCH((jacobi_svd_kernel<true, FZ_BIG_G, false>), FZ_BIG_G, big.size(), a, o0, o1d, o2, d_ws, d_aux, d_desc, sel_big, info);
+            FZ_LAUNCH((jacobi_svd_kernel<true, 1, false, PH_ALL>), 1, small.size(), a, o0, o1d, o2, d_ws, d_aux, d_desc, sel_small, info);
+            FZ_LAUNCH((jacobi_svd_kernel<true, FZ_BIG_G, false, PH_ALL>), FZ_BIG_G, big.size(), a, o0, o1d, o2, d_ws, d_aux, d_desc, sel_big, info);
         } else {
-            FZ_LAUNCH((jacobi_svd_kernel<false, 1, false>), 1, small.size(), a, o0, o1d, o2, d_ws, d_aux, d_desc, sel_small, info);
-            FZ_LAUNCH((jacobi_svd_kernel<false, FZ_BIG_G, false>), FZ_BIG_G, big.size(), a, o0, o1d, o2, d_ws, d_aux, d_desc, sel_big, info);
+            FZ_LAUNCH((jacobi_svd_kernel<false, 1, false, PH_ALL>), 1, small.size(), a, o0, o1d, o2, d_ws, d_aux, d_desc, sel_small, info);
+            FZ_LAUNCH((jacobi_svd_kernel<false, FZ_BIG_G, false, PH_ALL>), FZ_BIG_G, big.size(), a, o0, o1d, o2, d_ws, d_aux, d_desc, sel_big, info);
         }
     } else if (kind == FZ_EIGH) {
         if (cx) {
-            FZ_LAUNCH((jacobi_svd_kernel<true, 1, true>), 1, small.size(), a, o0, o1d, o2, d_ws, d_aux, d_desc, sel_small, info);
-            FZ_LAUNCH((jacobi_svd_kernel<true, FZ_BIG_G, true>), FZ_BIG_G, big.size(), a, o0, o1d, o2, d_ws, d_aux, d_desc, sel_big, info);
+            FZ_LAUNCH((jacobi_svd_kernel<true, 1, true, PH_ALL>), 1, small.size(), a, o0, o1d, o2, d_ws, d_aux, d_desc, sel_small, info);
+            FZ_LAUNCH((jacobi_svd_kernel<true, FZ_BIG_G, true, PH_ALL>), FZ_BIG_G, big.size(), a, o0, o1d, o2, d_ws, d_aux, d_desc, sel_big, info);
         } else {
-            FZ_LAUNCH((jacobi_svd_kernel<false, 1, true>), 1, small.size(), a, o0, o1d, o2, d_ws, d_aux, d_desc, sel_small, info);
-            FZ_LAUNCH((jacobi_svd_kernel<false, FZ_BIG_G, true>), FZ_BIG_G, big.size(), a, o0, o1d, o2, d_ws, d_aux, d_desc, sel_big, info);
+            FZ_LAUNCH((jacobi_svd_kernel<false, 1, true, PH_ALL>), 1, small.size(), a, o0, o1d, o2, d_ws, d_aux, d_desc, sel_small, info);
+            FZ_LAUNCH((jacobi_svd_kernel<false, FZ_BIG_G, true, PH_ALL>), FZ_BIG_G, big.size(), a, o0, o1d, o2, d_ws, d_aux, d_desc, sel_big, info);
         }
     } else {
         if (cx) {

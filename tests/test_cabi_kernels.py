@@ -290,7 +290,9 @@ def _pack(mats, dtype):
     return ar, np.asarray(offs, np.int64)
 
 
-SVD_DIMS = [(1, 1), (2, 3), (5, 5), (17, 9), (9, 17), (40, 40), (64, 33), (100, 130), (150, 97), (1, 20), (20, 1)]
+SVD_DIMS = [(1, 1), (2, 3), (5, 5), (17, 9), (9, 17), (40, 40), (64, 33), (100, 130), (150, 97), (1, 20), (20, 1),
+            # >= 96 working rows: the block-Jacobi path (odd / even leading dimensions, ragged last block)
+            (300, 300), (200, 331), (257, 131), (129, 640)]
 
 
 @pytest.mark.parametrize("dtype", [np.float64, np.complex128])
@@ -350,7 +352,7 @@ def test_batched_qr(lib, dtype, kind):
 @pytest.mark.parametrize("dtype", [np.float64, np.complex128])
 def test_batched_eigh(lib, dtype):
     rng = np.random.default_rng(23)
-    ns = [1, 2, 7, 33, 64, 100, 129]
+    ns = [1, 2, 7, 33, 64, 100, 129, 300, 193]
     mats = []
     for n in ns:
         A = _mats(rng, dtype, [(n, n)])[0]
