@@ -250,7 +250,9 @@ bj_gram_kernel(const double* __restrict__ ws, const FzDesc* __restrict__ descs, 
 }
 
 // ---- 2. convergence test + one cyclic pass of rotations ----------------------------------------------
-__global__ void __launch_bounds__(BJ_THREADS)
+constexpr int BJ_RT = 1024;              // threads of the rotation kernel
+
+__global__ void __launch_bounds__(BJ_RT)
 bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ items, const int* __restrict__ active,
                  int* __restrict__ flags, const double* __restrict__ floor2, int use_floor,
                  const double* __restrict__ gpart, double* __restrict__ qbuf, int* __restrict__ skip)
@@ -268,7 +270,7 @@ bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ it
     const double tol2 = tol * tol;
     const bool cross = it.nj > 0;
     // G = sum of the partials, in slice order
-    for (int e = tid; e < BJ_R * BJ_R; e += BJ_THREADS) {
+    for (int e = tid; e < BJ_R * BJ_R; e += BJ_RT) {
         double g = 0.0;
         for (int w = 0; w < it.nw; ++w) g += __ldcg(gpart + (size_t)(it.w0 + w) * (BJ_R * BJ_R) + e);
         sG[(e / BJ_R) * BJ_LDG + e % BJ_R] = g;
@@ -277,7 +279,7 @@ bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ it
     __syncthreads();
     {
         int bad = 0;
-        for (int e = tid; e < BJ_B * BJ_B; e += BJ_THREADS) {
+        for (int e = tid; e < BJ_B * BJ_B; e += BJ_RT) {
             int p, q;
             bool valid;
             if (cross) { p = e / BJ_B; q = BJ_B + e % BJ_B; valid = p < it.ni && q - BJ_B < it.nj; }
@@ -292,7 +294,7 @@ bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ it
         if (!s_any) { if (tid == 0) skip[blockIdx.x] = 1; return; }   // every pair of this item is orthogonal
         if (tid == 0) { flags[it.mat] = 1; skip[blockIdx.x] = 0; }
     }
-    for (int e = tid; e < BJ_R * BJ_R; e += BJ_THREADS) sQ[(e / BJ_R) * BJ_LDG + e % BJ_R] = (e / BJ_R == e % BJ_R) ? 1.0 : 0.0;
+    for (int e = tid; e < BJ_R * BJ_R; e += BJ_RT) sQ[(e / BJ_R) * BJ_LDG + e % BJ_R] = (e / BJ_R == e % BJ_R) ? 1.0 : 0.0;
     const int nsteps = cross ? BJ_B : BJ_B - 1;
     const int nrot = cross ? BJ_B : BJ_B / 2;
     __syncthreads();
@@ -322,32 +324,34 @@ bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ it
             s_rot[tid].p = p; s_rot[tid].q = q; s_rot[tid].cs = cs; s_rot[tid].sn = sn;
         }
         __syncthreads();
-        // rows p, q of G and Q:  x <- cs x - sn y,  y <- sn x + cs y
-        for (int e = tid; e < nrot * BJ_R; e += BJ_THREADS) {
+        // G <- J G J^T, one 2x2 block G[{p,q}][{p',q'}] per (rotation a, rotation b): the blocks are disjoint,
+        // so rows and columns are updated in ONE phase;  Q <- J Q (rows p, q) in the same phase
+        for (int e = tid; e < nrot * nrot; e += BJ_RT) {
+            const BjRot Ra = s_rot[e / nrot], Rb = s_rot[e % nrot];
+            if (Ra.sn == 0.0 && Rb.sn == 0.0) continue;
+            const double g00 = sG[Ra.p * BJ_LDG + Rb.p], g01 = sG[Ra.p * BJ_LDG + Rb.q];
+            const double g10 = sG[Ra.q * BJ_LDG + Rb.p], g11 = sG[Ra.q * BJ_LDG + Rb.q];
+            // rows:  [x; y] <- [cs x - sn y; sn x + cs y]
+            const double h00 = Ra.cs * g00 - Ra.sn * g10, h01 = Ra.cs * g01 - Ra.sn * g11;
+            const double h10 = Ra.sn * g00 + Ra.cs * g10, h11 = Ra.sn * g01 + Ra.cs * g11;
+            // columns with rotation b
+            sG[Ra.p * BJ_LDG + Rb.p] = Rb.cs * h00 - Rb.sn * h01;
+            sG[Ra.p * BJ_LDG + Rb.q] = Rb.sn * h00 + Rb.cs * h01;
+            sG[Ra.q * BJ_LDG + Rb.p] = Rb.cs * h10 - Rb.sn * h11;
+            sG[Ra.q * BJ_LDG + Rb.q] = Rb.sn * h10 + Rb.cs * h11;
+        }
+        for (int e = tid; e < nrot * BJ_R; e += BJ_RT) {
             const BjRot R = s_rot[e / BJ_R];
             if (R.sn == 0.0) continue;
             const int col = e % BJ_R;
-            double x = sG[R.p * BJ_LDG + col], y = sG[R.q * BJ_LDG + col];
-            sG[R.p * BJ_LDG + col] = R.cs * x - R.sn * y;
-            sG[R.q * BJ_LDG + col] = R.sn * x + R.cs * y;
-            x = sQ[R.p * BJ_LDG + col]; y = sQ[R.q * BJ_LDG + col];
+            const double x = sQ[R.p * BJ_LDG + col], y = sQ[R.q * BJ_LDG + col];
             sQ[R.p * BJ_LDG + col] = R.cs * x - R.sn * y;
             sQ[R.q * BJ_LDG + col] = R.sn * x + R.cs * y;
         }
         __syncthreads();
-        // columns p, q of G
-        for (int e = tid; e < nrot * BJ_R; e += BJ_THREADS) {
-            const BjRot R = s_rot[e / BJ_R];
-            if (R.sn == 0.0) continue;
-            const int row = e % BJ_R;
-            const double x = sG[row * BJ_LDG + R.p], y = sG[row * BJ_LDG + R.q];
-            sG[row * BJ_LDG + R.p] = R.cs * x - R.sn * y;
-            sG[row * BJ_LDG + R.q] = R.sn * x + R.cs * y;
-        }
-        __syncthreads();
     }
     double* out = qbuf + (size_t)blockIdx.x * (BJ_R * BJ_R);
-    for (int e = tid; e < BJ_R * BJ_R; e += BJ_THREADS) __stcg(out + e, sQ[(e / BJ_R) * BJ_LDG + e % BJ_R]);
+    for (int e = tid; e < BJ_R * BJ_R; e += BJ_RT) __stcg(out + e, sQ[(e / BJ_R) * BJ_LDG + e % BJ_R]);
 }
 
 // ---- 3. rows <- Q rows -------------------------------------------------------------------------------

@@ -680,7 +680,7 @@ static int run_block_jacobi(const void* a, void* o0, double* s_out, void* o2, vo
                 const unsigned ng = (unsigned)(R.gstart[rd + 1] - R.gstart[rd]), na = (unsigned)(R.astart[rd + 1] - R.astart[rd]);
                 bj_gram_kernel<<<ng, BJ_THREADS, BJ_SMEM_GRAM, stream>>>(
                     static_cast<const double*>(d_ws), d_desc, d_items + R.start[rd], d_gworks + R.gstart[rd], d_active, d_rowmap, d_gpart);
-                bj_rotate_kernel<<<ni, BJ_THREADS, BJ_SMEM_ROT, stream>>>(
+                bj_rotate_kernel<<<ni, BJ_RT, BJ_SMEM_ROT, stream>>>(
                     d_desc, d_items + R.start[rd], d_active, d_flags, d_floor2, phase1 ? 1 : 0, d_gpart, d_qbuf, d_skip);
                 bj_apply_kernel<<<na, BJ_THREADS, BJ_SMEM_APPLY, stream>>>(
                     static_cast<double*>(d_ws), d_desc, d_items + R.start[rd], d_aworks + R.astart[rd], d_rowmap, d_qbuf, d_skip);
