@@ -26,8 +26,8 @@ SIGNATURES = {
     "cyb_row_differences": (_int, [_vp, _i64, _i64, _vp, _vp, _vp]),
     "cyb_pack_rows": (_int, [_vp, _i64, _i64, _vp, _vp, _vp]),
     "cyb_common_sorted": (_int, [_vp, _i64, _vp, _i64, _vp, _vp, _vp]),
-    "cyb_copy_blocks_workspace": (_i64, [_i64]),
-    "cyb_copy_blocks": (_int, [_vp, _vp, _vp, _i64, _int, _int, _vp, _i64, _vp]),
+    "cyb_copy_blocks_workspace": (_i64, [_vp, _i64]),
+    "cyb_copy_blocks": (_int, [_vp, _vp, _vp, _vp, _i64, _int, _int, _vp]),
     "cyb_copy_blocks_prepare": (_int, [_vp, _i64, _vp, _i64, _vp]),
     "cyb_copy_blocks_run": (_int, [_vp, _vp, _vp, _i64, _int, _int, _vp]),
     "cyb_grouped_gemm_workspace": (_i64, [_i64]),

@@ -55,12 +55,12 @@ class B200AbelianBackend:
             _lib.load()
             self._lib_call = _lib.call
             self._plan_ws = lambda na, nb: _lib.load().cyb_compose_plan_workspace(na, nb)
-            self._copy_ws = lambda n: _lib.load().cyb_copy_blocks_workspace(n)
+            self._copy_ws = lambda jobs, n: _lib.load().cyb_copy_blocks_workspace(jobs.ctypes.data_as(C.c_void_p), n)
             self._gemm_ws = lambda n: _lib.load().cyb_grouped_gemm_workspace(n)
         else:
             self._lib_call = _library.call
             self._plan_ws = _library.cyb_compose_plan_workspace
-            self._copy_ws = _library.cyb_copy_blocks_workspace
+            self._copy_ws = lambda jobs, n: _library.cyb_copy_blocks_workspace(jobs.ctypes.data_as(C.c_void_p), n)
             self._gemm_ws = _library.cyb_grouped_gemm_workspace
         # Plans: the integer bookkeeping of an operation (sorted block_inds, copy job lists, GEMM work
         # lists and tile schedules) depends only on the structure of its operands (block_inds + legs),
@@ -131,9 +131,10 @@ class B200AbelianBackend:
         if njobs == 0 or self.dry_run:
             return
         with self._ctx():
+            jobs = np.ascontiguousarray(jobs, dtype=np.int64)
             d_jobs = to_device_i64(jobs, self.device)
-            self._call("cyb_copy_blocks", ptr(src_buf), ptr(dst_buf), ptr(d_jobs), njobs, cyb_dtype,
-                       int(conj), C.c_void_p(0), 0, self._stream())
+            self._call("cyb_copy_blocks", ptr(src_buf), ptr(dst_buf), ptr(d_jobs), jobs.ctypes.data_as(C.c_void_p),
+                       njobs, cyb_dtype, int(conj), self._stream())
 
     def _prepare_copy(self, jobs: np.ndarray):
         """Uploads a job list and builds its device schedule once; returns (njobs, workspace)."""
@@ -141,8 +142,9 @@ class B200AbelianBackend:
         if njobs == 0 or self.dry_run:
             return (0, None)
         with self._ctx():
+            jobs = np.ascontiguousarray(jobs, dtype=np.int64)
             d_jobs = to_device_i64(jobs, self.device)
-            nbytes = int(self._copy_ws(njobs))
+            nbytes = int(self._copy_ws(jobs, njobs))
             d_ws = torch.empty(nbytes // 8 + 1, dtype=torch.int64, device=self.device)
             self._call("cyb_copy_blocks_prepare", ptr(d_jobs), njobs, ptr(d_ws), nbytes, self._stream())
         return (njobs, d_ws)

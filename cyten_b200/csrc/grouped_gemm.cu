@@ -16,6 +16,7 @@
 // not apply), shared-memory rows are padded so every fragment load is bank-conflict free.
 // complex128 = 4 real DMMAs per fragment pair on split re/im accumulators.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace cyb {
 
@@ -61,8 +62,8 @@ struct GemmTables {
 // streaming kernel below (units of SK_COLS columns); everything else goes to the DMMA kernel.
 constexpr int SK_MAXM = 8;
 constexpr int SK_THREADS = 256;
-constexpr int SK_CHUNK = 2 * SK_THREADS;   // columns one CTA covers per pass
-constexpr int SK_PASSES = 8;               // passes per work unit (amortises the unit lookup)
+constexpr int SK_CHUNK = 4 * SK_THREADS;   // columns one CTA covers per pass
+constexpr int SK_PASSES = 4;               // passes per work unit (amortises the unit lookup)
 constexpr int SK_COLS = SK_CHUNK * SK_PASSES;
 
 template <int BM, int BN, bool SKINNY>
@@ -123,9 +124,14 @@ __global__ void __launch_bounds__(1024) gemm_schedule_kernel(const int64_t* __re
     if (tid == 0) { tile_start[nblocks] = carry; *ticket = 0ull; }
 }
 
-template <bool CPLX, int BM_, int BN_, int BK_, int WARPS_M_, int WARPS_N_, int STAGES_>
+// IL: a warp's 8x8 groups are interleaved over the tile (group = w + i * WARPS) instead of contiguous;
+// WMFAST: wm = warp % WARPS_M (else warp / WARPS_N);  SKIP: groups beyond the block edge issue no DMMA
+template <bool CPLX, int BM_, int BN_, int BK_, int WARPS_M_, int WARPS_N_, int STAGES_, bool IL_ = true,
+          bool WMFAST_ = true, bool SKIP_ = true, int MINB_ = 1>
 struct GemmCfg {
+    static constexpr int MINB = MINB_;      // resident CTAs per SM (persistent grid = MINB x #SMs)
     static constexpr bool cplx = CPLX;
+    static constexpr bool IL = IL_, WMFAST = WMFAST_, SKIP = SKIP_;
     static constexpr int BM = BM_, BN = BN_, BK = BK_, WARPS_M = WARPS_M_, WARPS_N = WARPS_N_, STAGES = STAGES_;
     static constexpr int THREADS = WARPS_M * WARPS_N * 32;
     static constexpr int WM = BM / WARPS_M, WN = BN / WARPS_N;
@@ -134,7 +140,7 @@ struct GemmCfg {
     // row strides in ELEMENTS; bank-conflict-free fragment loads need
     //   real:    lda = 4 (mod 16) doubles,  ldb = 4 (mod 16)
     //   complex: lda = 4 (mod 8) elements,  ldb = 2 (mod 8)
-    static constexpr int LDA = BK + 4;
+    static constexpr int LDA = (BK + 15) / 16 * 16 + 4;
     static constexpr int LDB = CPLX ? BN + 2 : BN + 4;
     static constexpr int A_STAGE = BM * LDA * ES;           // doubles
     static constexpr int B_STAGE = BK * LDB * ES;           // doubles
@@ -143,8 +149,60 @@ struct GemmCfg {
     static_assert(CPLX ? (LDA % 8 == 4 && LDB % 8 == 2) : (LDA % 16 == 4 && LDB % 16 == 4), "padding");
 };
 
+// all k-steps of one pipeline stage; FULL: every group of the warp is inside the block
+template <class Cfg, bool FULL>
+__device__ __forceinline__ void compute_stage(const double* __restrict__ tA, const double* __restrict__ tB,
+                                              double (&acc)[Cfg::cplx ? 2 : 1][Cfg::MI][Cfg::NI][2], int wm, int wn,
+                                              int lr, int lc, int mi_cnt, int nj_cnt)
+{
+    constexpr int BK = Cfg::BK, LDA = Cfg::LDA, LDB = Cfg::LDB, MI = Cfg::MI, NI = Cfg::NI;
+    constexpr bool CPLX = Cfg::cplx;
+#define CYB_GM(i) (Cfg::IL ? (wm + (i) * Cfg::WARPS_M) : (wm * MI + (i)))
+#define CYB_GN(j) (Cfg::IL ? (wn + (j) * Cfg::WARPS_N) : (wn * NI + (j)))
+#pragma unroll
+    for (int kk = 0; kk < BK; kk += 4) {
+        if (!CPLX) {
+            double a[MI], b[NI];
+#pragma unroll
+            for (int i = 0; i < MI; ++i) a[i] = tA[(size_t)(CYB_GM(i) * 8 + lr) * LDA + kk + lc];
+#pragma unroll
+            for (int j = 0; j < NI; ++j) b[j] = tB[(size_t)(kk + lc) * LDB + CYB_GN(j) * 8 + lr];
+#pragma unroll
+            for (int i = 0; i < MI; ++i) {
+                if (!FULL && i >= mi_cnt) continue;
+#pragma unroll
+                for (int j = 0; j < NI; ++j) {
+                    if (!FULL && j >= nj_cnt) continue;
+                    dmma884(acc[0][i][j][0], acc[0][i][j][1], a[i], b[j]);
+                }
+            }
+        } else {
+            double2 a[MI], b[NI];
+#pragma unroll
+            for (int i = 0; i < MI; ++i)
+                a[i] = *reinterpret_cast<const double2*>(tA + ((size_t)(CYB_GM(i) * 8 + lr) * LDA + kk + lc) * 2);
+#pragma unroll
+            for (int j = 0; j < NI; ++j)
+                b[j] = *reinterpret_cast<const double2*>(tB + ((size_t)(kk + lc) * LDB + CYB_GN(j) * 8 + lr) * 2);
+#pragma unroll
+            for (int i = 0; i < MI; ++i) {
+                if (!FULL && i >= mi_cnt) continue;
+                const double nai = neg_bits(a[i].y);
+#pragma unroll
+                for (int j = 0; j < NI; ++j) {
+                    if (!FULL && j >= nj_cnt) continue;
+                    dmma884(acc[0][i][j][0], acc[0][i][j][1], a[i].x, b[j].x);
+                    dmma884(acc[0][i][j][0], acc[0][i][j][1], nai, b[j].y);
+                    dmma884(acc[CPLX ? 1 : 0][i][j][0], acc[CPLX ? 1 : 0][i][j][1], a[i].x, b[j].y);
+                    dmma884(acc[CPLX ? 1 : 0][i][j][0], acc[CPLX ? 1 : 0][i][j][1], a[i].y, b[j].x);
+                }
+            }
+        }
+    }
+}
+
 template <class Cfg>
-__global__ void __launch_bounds__(Cfg::THREADS, 1)
+__global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB)
 grouped_gemm_kernel(const double* __restrict__ A, const double* __restrict__ B, double* __restrict__ C,
                     GemmTables T)
 {
@@ -158,7 +216,13 @@ grouped_gemm_kernel(const double* __restrict__ A, const double* __restrict__ B, 
     __shared__ long long s_tile;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int wm0 = (warp / Cfg::WARPS_N) * Cfg::WM, wn0 = (warp % Cfg::WARPS_N) * Cfg::WN;
+    // Warp (wm, wn) owns the 8-row groups wm, wm + WARPS_M, ... and the 8-column groups wn, wn + WARPS_N, ...
+    // of the tile (interleaved), and skips the groups that lie beyond the block edge.  With wm = warp % 4
+    // the two warps of every SM sub-partition (warp % 4) have the same wm and different wn, so the DMMA
+    // work of a ragged tile stays balanced over the four tensor pipes.
+    const int wm = Cfg::WMFAST ? warp % Cfg::WARPS_M : warp / Cfg::WARPS_N;
+    const int wn = Cfg::WMFAST ? warp / Cfg::WARPS_M : warp % Cfg::WARPS_N;
+    // 8x8 groups CYB_GM(i) / CYB_GN(j) of this warp inside the tile: see compute_stage
     const int lr = lane >> 2, lc = lane & 3;
     const int64_t total_tiles = T.tile_start[T.nblocks];
 
@@ -180,6 +244,13 @@ grouped_gemm_kernel(const double* __restrict__ A, const double* __restrict__ B, 
         const int64_t local = tile - T.tile_start[lo];
         const int64_t m0 = (local / tiles_n) * BM, n0 = (local % tiles_n) * BN;
         const int64_t p_begin = T.out_pair_ptr[blk], p_end = T.out_pair_ptr[blk + 1];
+        // number of this warp's row / column groups inside the block (a prefix of its interleaved list)
+        const int64_t mg = (min((int64_t)BM, M - m0) + 7) / 8, ng = (min((int64_t)BN, N - n0) + 7) / 8;
+        const int mi_cnt = !Cfg::SKIP ? MI : Cfg::IL ? (int)max((int64_t)0, (mg - wm + Cfg::WARPS_M - 1) / Cfg::WARPS_M)
+                                                     : (int)min((int64_t)MI, max((int64_t)0, mg - wm * MI));
+        const int nj_cnt = !Cfg::SKIP ? NI : Cfg::IL ? (int)max((int64_t)0, (ng - wn + Cfg::WARPS_N - 1) / Cfg::WARPS_N)
+                                                     : (int)min((int64_t)NI, max((int64_t)0, ng - wn * NI));
+        const bool full_tile = (mi_cnt == MI) && (nj_cnt == NI);
         int64_t n_iters = 0;
         for (int64_t p = p_begin; p < p_end; ++p) n_iters += (T.pairs[3 * p + 2] + BK - 1) / BK;
 
@@ -264,39 +335,10 @@ grouped_gemm_kernel(const double* __restrict__ A, const double* __restrict__ B, 
             const int stage = (int)(it % STAGES);
             const double* tA = sA + (size_t)stage * Cfg::A_STAGE;
             const double* tB = sB + (size_t)stage * Cfg::B_STAGE;
-#pragma unroll
-            for (int kk = 0; kk < BK; kk += 4) {
-                if (!CPLX) {
-                    double a[MI], b[NI];
-#pragma unroll
-                    for (int i = 0; i < MI; ++i) a[i] = tA[(size_t)(wm0 + i * 8 + lr) * LDA + kk + lc];
-#pragma unroll
-                    for (int j = 0; j < NI; ++j) b[j] = tB[(size_t)(kk + lc) * LDB + wn0 + j * 8 + lr];
-#pragma unroll
-                    for (int i = 0; i < MI; ++i)
-#pragma unroll
-                        for (int j = 0; j < NI; ++j) dmma884(acc[0][i][j][0], acc[0][i][j][1], a[i], b[j]);
-                } else {
-                    double2 a[MI], b[NI];
-#pragma unroll
-                    for (int i = 0; i < MI; ++i)
-                        a[i] = *reinterpret_cast<const double2*>(tA + ((size_t)(wm0 + i * 8 + lr) * LDA + kk + lc) * 2);
-#pragma unroll
-                    for (int j = 0; j < NI; ++j)
-                        b[j] = *reinterpret_cast<const double2*>(tB + ((size_t)(kk + lc) * LDB + wn0 + j * 8 + lr) * 2);
-#pragma unroll
-                    for (int i = 0; i < MI; ++i) {
-                        const double nai = neg_bits(a[i].y);
-#pragma unroll
-                        for (int j = 0; j < NI; ++j) {
-                            dmma884(acc[0][i][j][0], acc[0][i][j][1], a[i].x, b[j].x);
-                            dmma884(acc[0][i][j][0], acc[0][i][j][1], nai, b[j].y);
-                            dmma884(acc[CPLX ? 1 : 0][i][j][0], acc[CPLX ? 1 : 0][i][j][1], a[i].x, b[j].y);
-                            dmma884(acc[CPLX ? 1 : 0][i][j][0], acc[CPLX ? 1 : 0][i][j][1], a[i].y, b[j].x);
-                        }
-                    }
-                }
-            }
+            // the full / ragged decision is hoisted out of the unrolled k-steps: one basic block per stage,
+            // so the fragment loads of the next k-step are scheduled between the DMMAs of the current one
+            if (full_tile) compute_stage<Cfg, true>(tA, tB, acc, wm, wn, lr, lc, mi_cnt, nj_cnt);
+            else compute_stage<Cfg, false>(tA, tB, acc, wm, wn, lr, lc, mi_cnt, nj_cnt);
         }
         cp_async_wait<0>();
 
@@ -304,11 +346,11 @@ grouped_gemm_kernel(const double* __restrict__ A, const double* __restrict__ B, 
         double* Cb = C + T.out_off[blk] * ES;
 #pragma unroll
         for (int i = 0; i < MI; ++i) {
-            const int64_t r = m0 + wm0 + i * 8 + lr;
+            const int64_t r = m0 + CYB_GM(i) * 8 + lr;
             if (r >= M) continue;
 #pragma unroll
             for (int j = 0; j < NI; ++j) {
-                const int64_t c = n0 + wn0 + j * 8 + lc * 2;
+                const int64_t c = n0 + CYB_GN(j) * 8 + lc * 2;
                 if (!CPLX) {
                     double* p = Cb + r * N + c;
                     if (c + 1 < N && ((N & 1) == 0)) {
@@ -348,32 +390,43 @@ __device__ __noinline__ void skinny_unit_mm(const double* __restrict__ A, const 
         const int K = (int)pairs[3 * p + 2];
         const double* __restrict__ Ap = A + a_off * (CPLX ? 2 : 1);
         const double* __restrict__ Bp = B + (b_off + n) * (CPLX ? 2 : 1);
-#pragma unroll 4
-        for (int k = 0; k < K; ++k) {
-            double b[W];
-            if (W == 2) {
-                const double2 t = __ldcs(reinterpret_cast<const double2*>(Bp + (int64_t)k * N * (CPLX ? 2 : 1)));
-                b[0] = t.x; b[W - 1] = t.y;
-            } else if (W == 4) {
-                const double2 t0 = __ldcs(reinterpret_cast<const double2*>(Bp + (int64_t)k * N * 2));
-                const double2 t1 = __ldcs(reinterpret_cast<const double2*>(Bp + (int64_t)k * N * 2 + 2));
-                b[0] = t0.x; b[1] = t0.y; b[W - 2] = t1.x; b[W - 1] = t1.y;
-            } else {
-                b[0] = __ldcs(Bp + (int64_t)k * N);
+        // batches of 4 k-rows: all loads of a batch are issued before the first FMA, so every thread keeps
+        // up to 4 * W * 8 bytes in flight (an in-order warp would otherwise stall on each load in turn)
+        for (int k0 = 0; k0 < K; k0 += 4) {
+            double b[4][W];
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+                if (k0 + kk < K) {
+                    const double* row = Bp + (int64_t)(k0 + kk) * N * (CPLX ? 2 : 1);
+                    if (W == 1) b[kk][0] = __ldcs(row);
+                    else {
+#pragma unroll
+                        for (int w = 0; w < W; w += 2) {
+                            const double2 t = __ldcs(reinterpret_cast<const double2*>(row + w));
+                            b[kk][w] = t.x; b[kk][w + 1 < W ? w + 1 : w] = t.y;
+                        }
+                    }
+                }
             }
 #pragma unroll
-            for (int m = 0; m < MM; ++m) {
-                if (m < M) {
-                    if (!CPLX) {
-                        const double a = __ldg(Ap + m * K + k);
+            for (int kk = 0; kk < 4; ++kk) {
+                if (k0 + kk < K) {
+                    const int k = k0 + kk;
 #pragma unroll
-                        for (int w = 0; w < W; ++w) acc[m][w] = fma(a, b[w], acc[m][w]);
-                    } else {
-                        const double2 a = __ldg(reinterpret_cast<const double2*>(Ap) + m * K + k);
+                    for (int m = 0; m < MM; ++m) {
+                        if (m < M) {
+                            if (!CPLX) {
+                                const double a = __ldg(Ap + m * K + k);
 #pragma unroll
-                        for (int v = 0; v < VEC; ++v) {
-                            acc[m][2 * v] = fma(a.x, b[2 * v], fma(-a.y, b[2 * v + 1], acc[m][2 * v]));
-                            acc[m][2 * v + 1] = fma(a.x, b[2 * v + 1], fma(a.y, b[2 * v], acc[m][2 * v + 1]));
+                                for (int w = 0; w < W; ++w) acc[m][w] = fma(a, b[kk][w], acc[m][w]);
+                            } else {
+                                const double2 a = __ldg(reinterpret_cast<const double2*>(Ap) + m * K + k);
+#pragma unroll
+                                for (int v = 0; v < VEC; ++v) {
+                                    acc[m][2 * v] = fma(a.x, b[kk][2 * v], fma(-a.y, b[kk][2 * v + 1], acc[m][2 * v]));
+                                    acc[m][2 * v + 1] = fma(a.x, b[kk][2 * v + 1], fma(a.y, b[kk][2 * v], acc[m][2 * v + 1]));
+                                }
+                            }
                         }
                     }
                 }
@@ -399,7 +452,10 @@ __device__ __forceinline__ void skinny_unit(const double* __restrict__ A, const 
                                             int64_t p_begin, int64_t p_end, int M, int64_t N, int64_t n)
 {
     if (M <= SK_MAXM / 2) skinny_unit_mm<CPLX, VEC, SK_MAXM / 2>(A, B, Cb, pairs, p_begin, p_end, M, N, n);
-    else skinny_unit_mm<CPLX, VEC, SK_MAXM>(A, B, Cb, pairs, p_begin, p_end, M, N, n);
+    else if (VEC == 4) {   // 8 rows x 4 columns of accumulators would spill: two passes of 2 columns
+        skinny_unit_mm<CPLX, 2, SK_MAXM>(A, B, Cb, pairs, p_begin, p_end, M, N, n);
+        skinny_unit_mm<CPLX, 2, SK_MAXM>(A, B, Cb, pairs, p_begin, p_end, M, N, n + 2);
+    } else skinny_unit_mm<CPLX, VEC, SK_MAXM>(A, B, Cb, pairs, p_begin, p_end, M, N, n);
 }
 
 template <bool CPLX>
@@ -407,17 +463,25 @@ __global__ void __launch_bounds__(SK_THREADS, 3) skinny_gemm_kernel(const double
                                                                  const double* __restrict__ B,
                                                                  double* __restrict__ C, GemmTables T)
 {
-    const int64_t total_units = T.tile_start[T.nblocks];
+    // the unit -> block lookup runs on a shared-memory copy of the prefix table (a dependent chain of
+    // global loads per unit would cost as much as streaming the unit)
+    constexpr int SK_CACHE = 1024;
+    __shared__ int64_t s_start[SK_CACHE + 1];
+    const bool cached = T.nblocks <= SK_CACHE;
+    if (cached) for (int64_t i = threadIdx.x; i <= T.nblocks; i += SK_THREADS) s_start[i] = T.tile_start[i];
+    __syncthreads();
+    const int64_t* start = cached ? s_start : T.tile_start;
+    const int64_t total_units = start[T.nblocks];
     for (int64_t unit = blockIdx.x; unit < total_units; unit += gridDim.x) {
         int64_t lo = 0, hi = T.nblocks;
         while (hi - lo > 1) {
             const int64_t mid = (lo + hi) >> 1;
-            if (T.tile_start[mid] <= unit) lo = mid; else hi = mid;
+            if (start[mid] <= unit) lo = mid; else hi = mid;
         }
         const int64_t blk = T.order[lo];
         const int M = (int)T.out_mn[2 * blk];
         const int64_t N = T.out_mn[2 * blk + 1];
-        const int64_t u0 = (unit - T.tile_start[lo]) * SK_COLS;
+        const int64_t u0 = (unit - start[lo]) * SK_COLS;
         const int64_t p_begin = T.out_pair_ptr[blk], p_end = T.out_pair_ptr[blk + 1];
         double* Cb = C + T.out_off[blk] * (CPLX ? 2 : 1);
         const bool vec2 = !CPLX && (N & 1) == 0;   // real with even N: rows stay 16-byte aligned
@@ -426,11 +490,12 @@ __global__ void __launch_bounds__(SK_THREADS, 3) skinny_gemm_kernel(const double
             const int64_t c0 = u0 + (int64_t)pass * SK_CHUNK;
             if (c0 >= N) break;
             if (vec2) {
-                const int64_t n = c0 + (int64_t)threadIdx.x * 2;
-                if (n < N) skinny_unit<CPLX, 2>(A, B, Cb, T.pairs, p_begin, p_end, M, N, n);
+                const int64_t n = c0 + (int64_t)threadIdx.x * 4;
+                if (n + 2 < N) skinny_unit<CPLX, CPLX ? 1 : 4>(A, B, Cb, T.pairs, p_begin, p_end, M, N, n);
+                else if (n < N) skinny_unit<CPLX, CPLX ? 1 : 2>(A, B, Cb, T.pairs, p_begin, p_end, M, N, n);
             } else {
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
+#pragma unroll 1
+                for (int h = 0; h < 4; ++h) {
                     const int64_t n = c0 + threadIdx.x + h * SK_THREADS;
                     if (n < N) skinny_unit<CPLX, 1>(A, B, Cb, T.pairs, p_begin, p_end, M, N, n);
                 }
@@ -439,8 +504,29 @@ __global__ void __launch_bounds__(SK_THREADS, 3) skinny_gemm_kernel(const double
     }
 }
 
-using CfgR = GemmCfg<false, 128, 128, 16, 2, 4, 4>;   // 8 warps, warp tile 64x32, 4-stage pipeline
-using CfgC = GemmCfg<true, 128, 64, 8, 4, 2, 4>;      // 8 warps, warp tile 32x32 complex
+using CfgR = GemmCfg<false, 128, 128, 16, 4, 2, 4>;   // 8 warps, 4 x 8 interleaved 8x8 groups per warp, 4-stage pipeline
+// tuning variants (same 128 x 128 tile grid, so one schedule serves all); selected with CYB_GEMM_VARIANT
+using CfgR0 = GemmCfg<false, 128, 128, 16, 2, 4, 4, false, false, false>;  // round-1 baseline layout
+using CfgR2 = GemmCfg<false, 128, 128, 16, 2, 4, 4, false, false, true>;   // baseline layout + edge skipping
+using CfgR3 = GemmCfg<false, 128, 128, 32, 2, 4, 3, false, false, true>;   // BK = 32, 3 stages
+using CfgR4 = GemmCfg<false, 128, 128, 8, 2, 4, 6, false, false, true>;    // BK = 8, 6 stages
+using CfgR5 = GemmCfg<false, 128, 128, 16, 2, 4, 4, true, false, true>;    // interleaved, wm slow
+using CfgR6 = GemmCfg<false, 128, 128, 32, 4, 2, 3>;                       // current layout, BK = 32
+using CfgR7 = GemmCfg<false, 128, 64, 16, 4, 2, 3, true, true, true, 2>;   // 128 x 64 tiles, two CTAs per SM
+using CfgR8 = GemmCfg<false, 128, 64, 16, 4, 2, 3, false, false, false, 2>;
+using CfgR9 = GemmCfg<false, 64, 128, 16, 2, 4, 3, false, false, false, 2>;
+using CfgR10 = GemmCfg<false, 64, 64, 16, 2, 2, 3, false, false, false, 4>;   // 4 warps, 4 CTAs per SM
+using CfgR11 = GemmCfg<false, 128, 64, 8, 4, 2, 4, false, false, false, 2>;   // BK = 8, 4 stages
+using CfgR12 = GemmCfg<false, 64, 64, 32, 2, 2, 3, false, false, false, 3>;   // 64 x 64, BK = 32
+
+static int gemm_variant()
+{
+    // default: 64 x 64 tiles, 4 warps, four CTAs per SM (22.8 TFLOP/s on the chi = 4096 H_eff GEMMs; the
+    // 128 x 128 / one-CTA-per-SM layout of the first version reached 18.5) -- profiles/r1b
+    static const int v = [] { const char* e = getenv("CYB_GEMM_VARIANT"); return e ? atoi(e) : 10; }();
+    return v;
+}
+using CfgC = GemmCfg<true, 128, 64, 8, 4, 2, 4>;      // 8 warps, 4 x 4 interleaved groups per warp, complex
 
 template <class Cfg>
 static int launch_gemm(const void* a, const void* b, void* c, GemmTables T, cudaStream_t stream)
@@ -450,7 +536,7 @@ static int launch_gemm(const void* a, const void* b, void* c, GemmTables T, cuda
         CYB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
         configured = true;
     }
-    grouped_gemm_kernel<Cfg><<<sm_count(), Cfg::THREADS, Cfg::SMEM, stream>>>(
+    grouped_gemm_kernel<Cfg><<<sm_count() * Cfg::MINB, Cfg::THREADS, Cfg::SMEM, stream>>>(
         static_cast<const double*>(a), static_cast<const double*>(b), static_cast<double*>(c), T);
     CYB_LAUNCH_CHECK();
     return CYB_OK;
@@ -498,6 +584,14 @@ int cyb_grouped_gemm_prepare(int dtype, const int64_t* out_mn, const int64_t* ou
     double* cost[2];
     gemm_tables(T, cost, out_mn, nullptr, out_pair_ptr, pairs, nblocks, workspace);
     if (dtype == CYB_F64) {
+        const int v = gemm_variant();
+        if (v == 10 || v == 12)
+            gemm_schedule_kernel<64, 64, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket);
+        else if (v == 7 || v == 8 || v == 11)
+            gemm_schedule_kernel<128, 64, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket);
+        else if (v == 9)
+            gemm_schedule_kernel<64, 128, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket);
+        else
         gemm_schedule_kernel<CfgR::BM, CfgR::BN, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket);
         gemm_schedule_kernel<CfgR::BM, CfgR::BN, true><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[1], (int64_t*)T[1].order, (int64_t*)T[1].tile_start, T[1].ticket);
     } else {
@@ -529,7 +623,21 @@ int cyb_grouped_gemm_run(const void* a, const void* b, void* c, int dtype, const
     if (dtype == CYB_F64) {
         skinny_gemm_kernel<false><<<sk_grid, SK_THREADS, 0, stream>>>(A, B, C, T[1]);
         CYB_LAUNCH_CHECK();
-        return launch_gemm<CfgR>(a, b, c, T[0], stream);
+        switch (gemm_variant()) {
+            case 0: return launch_gemm<CfgR0>(a, b, c, T[0], stream);
+            case 2: return launch_gemm<CfgR2>(a, b, c, T[0], stream);
+            case 3: return launch_gemm<CfgR3>(a, b, c, T[0], stream);
+            case 4: return launch_gemm<CfgR4>(a, b, c, T[0], stream);
+            case 5: return launch_gemm<CfgR5>(a, b, c, T[0], stream);
+            case 6: return launch_gemm<CfgR6>(a, b, c, T[0], stream);
+            case 7: return launch_gemm<CfgR7>(a, b, c, T[0], stream);
+            case 8: return launch_gemm<CfgR8>(a, b, c, T[0], stream);
+            case 9: return launch_gemm<CfgR9>(a, b, c, T[0], stream);
+            case 10: return launch_gemm<CfgR10>(a, b, c, T[0], stream);
+            case 11: return launch_gemm<CfgR11>(a, b, c, T[0], stream);
+            case 12: return launch_gemm<CfgR12>(a, b, c, T[0], stream);
+            default: return launch_gemm<CfgR>(a, b, c, T[0], stream);
+        }
     }
     skinny_gemm_kernel<true><<<sk_grid, SK_THREADS, 0, stream>>>(A, B, C, T[1]);
     CYB_LAUNCH_CHECK();

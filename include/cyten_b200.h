@@ -87,17 +87,17 @@ typedef struct cyb_copy_job {
     int64_t dst_stride[CYB_MAX_RANK];
 } cyb_copy_job;
 
-/* Bytes of device scratch cyb_copy_blocks needs for `njobs` jobs. */
-int64_t cyb_copy_blocks_workspace(int64_t njobs);
-/* Executes all jobs (device array `jobs[njobs]`) src -> dst. `conj` != 0 conjugates complex data. */
-int cyb_copy_blocks(const void* src, void* dst, const cyb_copy_job* jobs, int64_t njobs, int dtype,
-                    int conj, void* workspace, int64_t workspace_bytes, cyb_stream_t stream);
+/* Executes all jobs src -> dst in one launch.  `jobs` is a DEVICE array, `jobs_host` its HOST copy (the
+ * library sizes its schedule from it).  `conj` != 0 conjugates complex data. */
+int cyb_copy_blocks(const void* src, void* dst, const cyb_copy_job* jobs, const cyb_copy_job* jobs_host,
+                    int64_t njobs, int dtype, int conj, cyb_stream_t stream);
 
 /* The two halves of cyb_copy_blocks, for callers that keep a job list (a "plan": the bookkeeping of
  * permute_legs / combine_legs / split_legs depends only on block_inds and the legs, not on the block
- * contents) and replay it on new data: prepare canonicalises and schedules the jobs into `workspace`
- * (>= cyb_copy_blocks_workspace(njobs) bytes, caller-owned, must stay alive), run is the single copy
- * launch. */
+ * contents) and replay it on new data.  prepare canonicalises the jobs and resolves them into work
+ * units inside `workspace` (device memory, >= cyb_copy_blocks_workspace(jobs_host, njobs) bytes,
+ * caller-owned, must stay alive); run is the single copy launch. */
+int64_t cyb_copy_blocks_workspace(const cyb_copy_job* jobs_host, int64_t njobs);
 int cyb_copy_blocks_prepare(const cyb_copy_job* jobs, int64_t njobs, void* workspace,
                             int64_t workspace_bytes, cyb_stream_t stream);
 int cyb_copy_blocks_run(const void* src, void* dst, const void* workspace, int64_t njobs, int dtype,

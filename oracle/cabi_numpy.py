@@ -148,7 +148,7 @@ def cyb_fuse_charges(bi, nrows, ncols, cols, nlegs, sectors, sector_ptr, modulus
 
 
 # ---- (a3-a5) strided block copies ---------------------------------------------------------------------
-def cyb_copy_blocks_workspace(njobs):
+def cyb_copy_blocks_workspace(jobs_host, njobs):
     return 8 * JOB_WORDS * int(njobs) + 8
 
 
@@ -160,10 +160,10 @@ def cyb_copy_blocks_prepare(jobs, njobs, workspace, workspace_bytes, stream=None
 
 
 def cyb_copy_blocks_run(src, dst, workspace, njobs, dtype, conj, stream=None):
-    return cyb_copy_blocks(src, dst, workspace, njobs, dtype, conj, None, 0)
+    return cyb_copy_blocks(src, dst, workspace, None, njobs, dtype, conj)
 
 
-def cyb_copy_blocks(src, dst, jobs, njobs, dtype, conj, workspace, workspace_bytes, stream=None):
+def cyb_copy_blocks(src, dst, jobs, jobs_host, njobs, dtype, conj, stream=None):
     """permute_axes / combine_legs set_item / split_legs get_item as strided box copies
     (abelian.cpp:988-1006, 1196-1217, 3418-3433)."""
     dt = _dt(dtype)

@@ -135,6 +135,11 @@ def _jobs(src_off, dst_off, shapes, ss, ds):
     return J
 
 
+def hp(a):
+    """host pointer of a contiguous numpy array"""
+    return a.ctypes.data_as(C.c_void_p)
+
+
 def _cstr(shape):
     st = np.ones(len(shape), dtype=np.int64)
     for a in range(len(shape) - 2, -1, -1):
@@ -146,7 +151,8 @@ def _cstr(shape):
 @pytest.mark.parametrize("shape,perm", [
     ((5,), (0,)), ((7, 9), (1, 0)), ((70, 45), (1, 0)), ((33, 1, 64), (2, 1, 0)), ((3, 40, 2, 50), (1, 3, 0, 2)),
     ((6, 5, 4, 3, 2), (4, 2, 0, 3, 1)), ((130, 3, 100), (0, 2, 1)), ((2, 300), (0, 1)), ((1, 1, 1), (2, 0, 1)),
-    ((64, 64), (1, 0)), ((257, 129), (1, 0)), ((4, 1000), (1, 0)), ((2, 3, 4, 2, 3, 2, 3, 2), (7, 0, 6, 1, 5, 2, 4, 3)),
+    ((64, 64), (1, 0)), ((257, 129), (1, 0)), ((4, 1000), (1, 0)), ((3, 5000), (0, 1)), ((5, 3, 700), (1, 0, 2)),
+    ((2, 40, 3, 70), (2, 1, 0, 3)), ((300, 310), (1, 0)), ((2, 3, 4, 2, 3, 2, 3, 2), (7, 0, 6, 1, 5, 2, 4, 3)),
 ])
 def test_copy_blocks_permute(lib, dtype, shape, perm):
     """Batched permutes: three blocks of the same rank but different extents in one launch."""
@@ -163,15 +169,15 @@ def test_copy_blocks_permute(lib, dtype, shape, perm):
     ds = np.asarray([_cstr(ns) for ns in new_shapes], dtype=np.int64)
     J = _jobs(offs[:-1], offs[:-1], new_shapes, ss, ds)
     d_src, d_dst = lib.up(src), lib.up(np.zeros_like(src))
-    lib.call("cyb_copy_blocks", lib.p(d_src), lib.p(d_dst), lib.p(lib.up(J)), len(J), int(dtype == np.complex128), 0,
-             lib.p(None), 0, lib.stream())
+    lib.call("cyb_copy_blocks", lib.p(d_src), lib.p(d_dst), lib.p(lib.up(J)), hp(J), len(J), int(dtype == np.complex128), 0,
+             lib.stream())
     out = d_dst.cpu().numpy()
     for b, o in zip(blocks, offs):
         assert np.array_equal(out[o:o + b.size].reshape([b.shape[p] for p in perm]), b.transpose(perm))   # bit-exact
     # conjugating copy
     if dtype == np.complex128:
         d_dst2 = lib.up(np.zeros_like(src))
-        lib.call("cyb_copy_blocks", lib.p(d_src), lib.p(d_dst2), lib.p(lib.up(J)), len(J), 1, 1, lib.p(None), 0, lib.stream())
+        lib.call("cyb_copy_blocks", lib.p(d_src), lib.p(d_dst2), lib.p(lib.up(J)), hp(J), len(J), 1, 1, lib.stream())
         out = d_dst2.cpu().numpy()
         for b, o in zip(blocks, offs):
             assert np.array_equal(out[o:o + b.size].reshape([b.shape[p] for p in perm]), b.transpose(perm).conj())
@@ -186,7 +192,7 @@ def test_copy_blocks_box_into_slice(lib):
     b0, c0 = 9, 60
     J = _jobs([0], [b0 * 300 + c0], np.asarray([[37, 5, 41]]), np.asarray([_cstr((37, 5, 41))]), np.asarray([[300, 1, 5]]))
     d_small, d_big = lib.up(small.reshape(-1)), lib.up(big.reshape(-1))
-    lib.call("cyb_copy_blocks", lib.p(d_small), lib.p(d_big), lib.p(lib.up(J)), 1, 0, 0, lib.p(None), 0, lib.stream())
+    lib.call("cyb_copy_blocks", lib.p(d_small), lib.p(d_big), lib.p(lib.up(J)), hp(J), 1, 0, 0, lib.stream())
     want = big.copy()
     want[b0:b0 + 37, c0:c0 + 205] = small.transpose(0, 2, 1).reshape(37, 205)
     got = d_big.cpu().numpy().reshape(50, 300)
@@ -194,7 +200,7 @@ def test_copy_blocks_box_into_slice(lib):
     # split_legs-style: slice of the big block -> contiguous small block
     J2 = _jobs([b0 * 300 + c0], [0], np.asarray([[37, 5, 41]]), np.asarray([[300, 1, 5]]), np.asarray([_cstr((37, 5, 41))]))
     d_back = lib.up(np.zeros(small.size))
-    lib.call("cyb_copy_blocks", lib.p(d_big), lib.p(d_back), lib.p(lib.up(J2)), 1, 0, 0, lib.p(None), 0, lib.stream())
+    lib.call("cyb_copy_blocks", lib.p(d_big), lib.p(d_back), lib.p(lib.up(J2)), hp(J2), 1, 0, 0, lib.stream())
     assert np.array_equal(d_back.cpu().numpy().reshape(small.shape), small)
 
 
