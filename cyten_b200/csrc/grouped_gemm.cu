@@ -62,7 +62,7 @@ struct GemmTables {
 // streaming kernel below (units of SK_COLS columns); everything else goes to the DMMA kernel.
 constexpr int SK_MAXM = 8;
 constexpr int SK_THREADS = 256;
-constexpr int SK_CHUNK = 4 * SK_THREADS;   // columns one CTA covers per pass
+constexpr int SK_CHUNK = 2 * SK_THREADS;   // columns one CTA covers per pass
 constexpr int SK_PASSES = 4;               // passes per work unit (amortises the unit lookup)
 constexpr int SK_COLS = SK_CHUNK * SK_PASSES;
 
@@ -72,6 +72,11 @@ __host__ __device__ __forceinline__ int64_t n_units(int64_t M, int64_t N)
     if (M <= 0 || N <= 0) return 0;
     if (SKINNY) return M <= SK_MAXM ? (N + SK_COLS - 1) / SK_COLS : 0;
     return M > SK_MAXM ? ((M + BM - 1) / BM) * ((N + BN - 1) / BN) : 0;
+}
+
+__host__ __device__ __forceinline__ int64_t sk_units(int64_t M, int64_t N, int64_t ucols)
+{
+    return (M > 0 && M <= SK_MAXM && N > 0) ? (N + ucols - 1) / ucols : 0;
 }
 
 // single CTA: cost-sorted processing order, tile prefix, ticket reset.
@@ -85,15 +90,40 @@ __global__ void __launch_bounds__(1024) gemm_schedule_kernel(const int64_t* __re
                                                              int64_t nblocks, double* __restrict__ cost,
                                                              int64_t* __restrict__ order,
                                                              int64_t* __restrict__ tile_start,
-                                                             unsigned long long* __restrict__ ticket)
+                                                             unsigned long long* __restrict__ ticket,
+                                                             int64_t target_units)
 {
     __shared__ int64_t s_scan[33];
+    __shared__ int64_t s_target;
     const int tid = threadIdx.x;
+    if (SKINNY) {
+        // unit width of the streaming kernel: all skinny columns / target_units, rounded up to whole
+        // SK_CHUNKs: long enough to amortise the per-unit table lookups, short enough to balance the grid
+        int64_t carry = 0;
+        for (int64_t base = 0; base < nblocks; base += 1024) {
+            const int64_t i = base + tid;
+            int64_t v = 0;
+            if (i < nblocks) {
+                const int64_t blk = subset ? subset[i] : i;
+                const int64_t M = out_mn[2 * blk], N = out_mn[2 * blk + 1];
+                v = (M > 0 && M <= SK_MAXM && N > 0) ? N : 0;
+            }
+            int64_t total;
+            block_exclusive_scan<int64_t>(v, s_scan, &total);
+            carry += total;
+        }
+        if (tid == 0) {
+            const int64_t t = (carry + target_units - 1) / (target_units > 0 ? target_units : 1);
+            s_target = ((t > SK_CHUNK ? t : SK_CHUNK) + SK_CHUNK - 1) / SK_CHUNK * SK_CHUNK;
+        }
+        __syncthreads();
+    }
     for (int64_t i = tid; i < nblocks; i += 1024) {
         const int64_t blk = subset ? subset[i] : i;
         double ksum = 0;
         for (int64_t q = out_pair_ptr[blk]; q < out_pair_ptr[blk + 1]; ++q) ksum += (double)pairs[3 * q + 2];
-        const int64_t nt = n_units<BM, BN, SKINNY>(out_mn[2 * blk], out_mn[2 * blk + 1]);
+        const int64_t nt = SKINNY ? sk_units(out_mn[2 * blk], out_mn[2 * blk + 1], s_target)
+                                  : n_units<BM, BN, SKINNY>(out_mn[2 * blk], out_mn[2 * blk + 1]);
         // per-tile cost decides the order (long k-loops first), ties keep table order
         cost[i] = (nt > 0) ? ksum : -1.0;
     }
@@ -114,14 +144,18 @@ __global__ void __launch_bounds__(1024) gemm_schedule_kernel(const int64_t* __re
         int64_t v = 0;
         if (i < nblocks) {
             const int64_t blk = order[i];
-            v = n_units<BM, BN, SKINNY>(out_mn[2 * blk], out_mn[2 * blk + 1]);
+            v = SKINNY ? sk_units(out_mn[2 * blk], out_mn[2 * blk + 1], s_target)
+                       : n_units<BM, BN, SKINNY>(out_mn[2 * blk], out_mn[2 * blk + 1]);
         }
         int64_t total;
         int64_t pos = block_exclusive_scan<int64_t>(v, s_scan, &total);
         if (i < nblocks) tile_start[i] = carry + pos;
         carry += total;
     }
-    if (tid == 0) { tile_start[nblocks] = carry; *ticket = 0ull; }
+    if (tid == 0) {
+        tile_start[nblocks] = carry;
+        *ticket = SKINNY ? (unsigned long long)s_target : 0ull;   // the streaming kernel reads its unit width here
+    }
 }
 
 // IL: a warp's 8x8 groups are interleaved over the tile (group = w + i * WARPS) instead of contiguous;
@@ -458,20 +492,111 @@ __device__ __forceinline__ void skinny_unit(const double* __restrict__ A, const 
     } else skinny_unit_mm<CPLX, VEC, SK_MAXM>(A, B, Cb, pairs, p_begin, p_end, M, N, n);
 }
 
+// Fast path of the streaming kernel.  All (pair, k) rows of the output block are flattened once per work
+// unit into a shared-memory row table (element offset of B_p[k, 0]) and a coefficient table
+// (A_p[m, k]); the streaming loop is then free of pointer chasing: per batch of RB rows every thread issues
+// its RB * W / 2 16-byte loads back to back, then does the FMAs with coefficients broadcast from shared memory.
+constexpr int SK_J = 64;     // rows the tables hold; blocks with more rows take the generic path
+
+template <bool CPLX, int W, int MM>
+__device__ __noinline__ void skinny_rows(const double* __restrict__ B, double* __restrict__ Cb,
+                                            const int64_t* s_row, const double* s_coef, int J, int M,
+                                            int64_t N, int64_t n)
+{
+    constexpr int ES = CPLX ? 2 : 1;
+    constexpr int RB = 8;   // rows in flight per thread: 8 x 16 bytes
+    double acc[MM][W];
+#pragma unroll
+    for (int m = 0; m < MM; ++m)
+#pragma unroll
+        for (int w = 0; w < W; ++w) acc[m][w] = 0.0;
+    for (int j0 = 0; j0 < J; j0 += RB) {
+        double b[RB][W];
+#pragma unroll
+        for (int r = 0; r < RB; ++r) {
+            if (j0 + r < J) {
+                const double* row = B + (s_row[j0 + r] + n) * ES;
+                if (W == 1) b[r][0] = __ldcs(row);
+                else {
+#pragma unroll
+                    for (int w = 0; w < W; w += 2) {
+                        const double2 t = __ldcs(reinterpret_cast<const double2*>(row + w));
+                        b[r][w] = t.x; b[r][w + 1 < W ? w + 1 : w] = t.y;
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int w = 0; w < W; ++w) b[r][w] = 0.0;
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < RB; ++r) {
+            const int jj = (j0 + r < J) ? j0 + r : J - 1;   // b is zero beyond J
+#pragma unroll
+            for (int m = 0; m < MM; ++m) {
+                if (m < M) {
+                    if (!CPLX) {
+                        const double a = s_coef[m * SK_J + jj];
+#pragma unroll
+                        for (int w = 0; w < W; ++w) acc[m][w] = fma(a, b[r][w], acc[m][w]);
+                    } else {
+                        const double ax = s_coef[(m * SK_J + jj) * 2], ay = s_coef[(m * SK_J + jj) * 2 + 1];
+#pragma unroll
+                        for (int w = 0; w < W; w += 2) {
+                            acc[m][w] = fma(ax, b[r][w], fma(-ay, b[r][w + 1], acc[m][w]));
+                            acc[m][w + 1] = fma(ax, b[r][w + 1], fma(ay, b[r][w], acc[m][w + 1]));
+                        }
+                    }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int m = 0; m < MM; ++m) {
+        if (m < M) {
+            double* c = Cb + ((int64_t)m * N + n) * ES;
+            if (W == 1) __stcs(c, acc[m][0]);
+            else {
+#pragma unroll
+                for (int w = 0; w < W; w += 2) __stcs(reinterpret_cast<double2*>(c + w), make_double2(acc[m][w], acc[m][w + 1]));
+            }
+        }
+    }
+}
+
+template <bool CPLX, int W>
+__device__ __forceinline__ void skinny_rows_m(const double* __restrict__ B, double* __restrict__ Cb,
+                                              const int64_t* s_row, const double* s_coef, int J, int M,
+                                              int64_t N, int64_t n)
+{
+    if (M <= SK_MAXM / 2) skinny_rows<CPLX, W, SK_MAXM / 2>(B, Cb, s_row, s_coef, J, M, N, n);
+    else if (W == 4) {      // 8 rows x 4 columns of accumulators would spill
+        skinny_rows<CPLX, 2, SK_MAXM>(B, Cb, s_row, s_coef, J, M, N, n);
+        skinny_rows<CPLX, 2, SK_MAXM>(B, Cb, s_row, s_coef, J, M, N, n + 2);
+    } else skinny_rows<CPLX, W, SK_MAXM>(B, Cb, s_row, s_coef, J, M, N, n);
+}
+
 template <bool CPLX>
-__global__ void __launch_bounds__(SK_THREADS, 3) skinny_gemm_kernel(const double* __restrict__ A,
+__global__ void __launch_bounds__(SK_THREADS, 4) skinny_gemm_kernel(const double* __restrict__ A,
                                                                  const double* __restrict__ B,
                                                                  double* __restrict__ C, GemmTables T)
 {
     // the unit -> block lookup runs on a shared-memory copy of the prefix table (a dependent chain of
     // global loads per unit would cost as much as streaming the unit)
     constexpr int SK_CACHE = 1024;
+    constexpr int ES = CPLX ? 2 : 1;
     __shared__ int64_t s_start[SK_CACHE + 1];
+    __shared__ int64_t s_row[SK_J];
+    __shared__ double s_coef[SK_MAXM * SK_J * ES];
+    __shared__ int s_J;
     const bool cached = T.nblocks <= SK_CACHE;
     if (cached) for (int64_t i = threadIdx.x; i <= T.nblocks; i += SK_THREADS) s_start[i] = T.tile_start[i];
     __syncthreads();
     const int64_t* start = cached ? s_start : T.tile_start;
     const int64_t total_units = start[T.nblocks];
+    const int64_t ucols = (int64_t)*T.ticket;   // unit width chosen by the schedule kernel
+    const int npass = (int)(ucols / SK_CHUNK);
+    const int lane = threadIdx.x & 31;
     for (int64_t unit = blockIdx.x; unit < total_units; unit += gridDim.x) {
         int64_t lo = 0, hi = T.nblocks;
         while (hi - lo > 1) {
@@ -481,23 +606,67 @@ __global__ void __launch_bounds__(SK_THREADS, 3) skinny_gemm_kernel(const double
         const int64_t blk = T.order[lo];
         const int M = (int)T.out_mn[2 * blk];
         const int64_t N = T.out_mn[2 * blk + 1];
-        const int64_t u0 = (unit - start[lo]) * SK_COLS;
+        const int64_t u0 = (unit - start[lo]) * ucols;
         const int64_t p_begin = T.out_pair_ptr[blk], p_end = T.out_pair_ptr[blk + 1];
-        double* Cb = C + T.out_off[blk] * (CPLX ? 2 : 1);
+        double* Cb = C + T.out_off[blk] * ES;
         const bool vec2 = !CPLX && (N & 1) == 0;   // real with even N: rows stay 16-byte aligned
+        // ---- row / coefficient tables of this block (warp 0) ----
+        __syncthreads();                            // the previous unit is done with the tables
+        if (threadIdx.x < 32) {
+            const int np = (int)(p_end - p_begin);
+            int J = SK_J + 1;
+            if (np <= 32) {
+                int64_t a_off = 0, b_off = 0;
+                int K = 0;
+                if (lane < np) {
+                    const int64_t* pr = T.pairs + 3 * (p_begin + lane);
+                    a_off = pr[0]; b_off = pr[1]; K = (int)min(pr[2], (int64_t)(SK_J + 1));
+                }
+                int incl = K;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const int o = __shfl_up_sync(0xffffffffu, incl, d);
+                    if (lane >= d) incl += o;
+                }
+                J = __shfl_sync(0xffffffffu, incl, 31);
+                if (J <= SK_J) {
+                    const int j0 = incl - K;
+                    for (int k = 0; k < K; ++k) {
+                        s_row[j0 + k] = b_off + (int64_t)k * N;
+                        for (int m = 0; m < M; ++m) {
+                            if (!CPLX) s_coef[m * SK_J + j0 + k] = __ldg(A + a_off + m * K + k);
+                            else {
+                                const double2 v = __ldg(reinterpret_cast<const double2*>(A) + a_off + m * K + k);
+                                s_coef[(m * SK_J + j0 + k) * 2] = v.x;
+                                s_coef[(m * SK_J + j0 + k) * 2 + 1] = v.y;
+                            }
+                        }
+                    }
+                }
+            }
+            if (lane == 0) s_J = J;
+        }
+        __syncthreads();
+        const int J = s_J;
+        const bool fast = J <= SK_J;
 #pragma unroll 1
-        for (int pass = 0; pass < SK_PASSES; ++pass) {
+        for (int pass = 0; pass < npass; ++pass) {
             const int64_t c0 = u0 + (int64_t)pass * SK_CHUNK;
             if (c0 >= N) break;
             if (vec2) {
-                const int64_t n = c0 + (int64_t)threadIdx.x * 4;
-                if (n + 2 < N) skinny_unit<CPLX, CPLX ? 1 : 4>(A, B, Cb, T.pairs, p_begin, p_end, M, N, n);
-                else if (n < N) skinny_unit<CPLX, CPLX ? 1 : 2>(A, B, Cb, T.pairs, p_begin, p_end, M, N, n);
+                const int64_t n = c0 + (int64_t)threadIdx.x * 2;
+                if (n < N) {
+                    if (fast) skinny_rows_m<CPLX, 2>(B, Cb, s_row, s_coef, J, M, N, n);
+                    else skinny_unit<CPLX, CPLX ? 1 : 2>(A, B, Cb, T.pairs, p_begin, p_end, M, N, n);
+                }
             } else {
 #pragma unroll 1
-                for (int h = 0; h < 4; ++h) {
+                for (int h = 0; h < 2; ++h) {
                     const int64_t n = c0 + threadIdx.x + h * SK_THREADS;
-                    if (n < N) skinny_unit<CPLX, 1>(A, B, Cb, T.pairs, p_begin, p_end, M, N, n);
+                    if (n < N) {
+                        if (fast) skinny_rows_m<CPLX, CPLX ? 2 : 1>(B, Cb, s_row, s_coef, J, M, N, n);
+                        else skinny_unit<CPLX, 1>(A, B, Cb, T.pairs, p_begin, p_end, M, N, n);
+                    }
                 }
             }
         }
@@ -583,20 +752,23 @@ int cyb_grouped_gemm_prepare(int dtype, const int64_t* out_mn, const int64_t* ou
     GemmTables T[2];
     double* cost[2];
     gemm_tables(T, cost, out_mn, nullptr, out_pair_ptr, pairs, nblocks, workspace);
+    // streaming kernel: aim at SK_UNITS_PER_SLOT work units per resident CTA (3 per SM)
+    static const int ups = [] { const char* e = getenv("CYB_SK_UNITS_PER_SLOT"); return e ? atoi(e) : 4; }();
+    const int64_t sk_target = (int64_t)sm_count() * 4 * ups;
     if (dtype == CYB_F64) {
         const int v = gemm_variant();
         if (v == 10 || v == 12)
-            gemm_schedule_kernel<64, 64, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket);
+            gemm_schedule_kernel<64, 64, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket, 0);
         else if (v == 7 || v == 8 || v == 11)
-            gemm_schedule_kernel<128, 64, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket);
+            gemm_schedule_kernel<128, 64, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket, 0);
         else if (v == 9)
-            gemm_schedule_kernel<64, 128, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket);
+            gemm_schedule_kernel<64, 128, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket, 0);
         else
-        gemm_schedule_kernel<CfgR::BM, CfgR::BN, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket);
-        gemm_schedule_kernel<CfgR::BM, CfgR::BN, true><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[1], (int64_t*)T[1].order, (int64_t*)T[1].tile_start, T[1].ticket);
+        gemm_schedule_kernel<CfgR::BM, CfgR::BN, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket, 0);
+        gemm_schedule_kernel<CfgR::BM, CfgR::BN, true><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[1], (int64_t*)T[1].order, (int64_t*)T[1].tile_start, T[1].ticket, sk_target);
     } else {
-        gemm_schedule_kernel<CfgC::BM, CfgC::BN, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket);
-        gemm_schedule_kernel<CfgC::BM, CfgC::BN, true><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[1], (int64_t*)T[1].order, (int64_t*)T[1].tile_start, T[1].ticket);
+        gemm_schedule_kernel<CfgC::BM, CfgC::BN, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket, 0);
+        gemm_schedule_kernel<CfgC::BM, CfgC::BN, true><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[1], (int64_t*)T[1].order, (int64_t*)T[1].tile_start, T[1].ticket, sk_target);
     }
     CYB_LAUNCH_CHECK();
     return CYB_OK;
