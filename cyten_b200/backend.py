@@ -258,6 +258,15 @@ class B200AbelianBackend:
             if not isinstance(p, AbelianLegPipe):
                 raise ValueError("abelian backend requires AbelianLegPipe")
         num_result_legs = num_legs - sum(len(g) - 1 for g in groups)
+        # the integer part below depends on the structure only: cached plan (tables + prepared copy schedule)
+        key = ("combine", data.sig, num_codomain, tuple(tuple(g) for g in groups), tuple(p.sig for p in pipes),
+               new_codomain.sig, new_domain.sig)
+        plan = self._plan_get(key)
+        if plan is not None:
+            res = self._empty(data.dtype, self.device, plan["bi"], plan["shapes"], zero=True)
+            res._sig = plan["sig"]
+            self._run_copy(data.buf, res.buf, plan["copy"], data.cyb_dtype)
+            return res
         t_bi = data.block_inds
         n_old = data.num_blocks
         res_bi = np.zeros((n_old, num_result_legs), dtype=np.int64)
@@ -327,7 +336,9 @@ class B200AbelianBackend:
             if not in_group[k]:
                 dst_strides[:, k] = new_strides[:, old_to_new_axis[k]]
         jobs = self._make_jobs(data.offsets[sort], dst_off, old_shapes, _c_strides(old_shapes), dst_strides)
-        self._copy_blocks(data.buf, res.buf, jobs, data.cyb_dtype)
+        prepared = self._prepare_copy(jobs)
+        self._plan_put(key, dict(bi=new_bi, shapes=new_shapes, copy=prepared, sig=res.sig))
+        self._run_copy(data.buf, res.buf, prepared, data.cyb_dtype)
         return res
 
     # ------------------------------------------------------------------------------------------
@@ -352,6 +363,14 @@ class B200AbelianBackend:
         if n_old == 0:
             return self._empty(data.dtype, self.device, np.zeros((0, res_num_legs), np.int64),
                                             np.zeros((0, res_num_legs), np.int64))
+        key = ("split", data.sig, num_codomain, tuple(leg_idcs), tuple(p.sig for p in pipes),
+               new_codomain.sig, new_domain.sig)
+        plan = self._plan_get(key)
+        if plan is not None:
+            res = self._empty(data.dtype, self.device, plan["bi"], plan["shapes"])
+            res._sig = plan["sig"]
+            self._run_copy(data.buf, res.buf, plan["copy"], data.cyb_dtype)
+            return res
         old_bi = data.block_inds
         n_split = len(leg_idcs)
         beg = np.stack([p.block_ind_map_slices[old_bi[:, i]] for p, i in zip(pipes, leg_idcs)], axis=1)
@@ -409,7 +428,9 @@ class B200AbelianBackend:
             src_strides[:, k:k2] *= inner
         src_off = data.offsets[old_rows] + np.sum(src_beg * old_strides, axis=1)
         jobs = self._make_jobs(src_off, res.offsets, new_shapes, src_strides, _c_strides(new_shapes))
-        self._copy_blocks(data.buf, res.buf, jobs, data.cyb_dtype)
+        prepared = self._prepare_copy(jobs)
+        self._plan_put(key, dict(bi=new_bi, shapes=new_shapes, copy=prepared, sig=res.sig))
+        self._run_copy(data.buf, res.buf, prepared, data.cyb_dtype)
         return res
 
     # ------------------------------------------------------------------------------------------

@@ -154,7 +154,19 @@ def permute_legs(T: SymmetricTensor, codomain: Sequence | None = None, domain: S
 
 def make_pipe(legs, is_dual: bool, in_domain: bool) -> AbelianLegPipe:
     """TensorBackend::make_pipe (tensor_backend.cpp:118-136): ``combine_cstyle = not is_dual``."""
-    return AbelianLegPipe(list(legs), is_dual=is_dual, combine_cstyle=not is_dual)
+    legs = list(legs)
+    key = (tuple(l.sig for l in legs), bool(is_dual))
+    pipe = _PIPE_CACHE.get(key)
+    if pipe is None:
+        if len(_PIPE_CACHE) > 4096:
+            _PIPE_CACHE.clear()
+        pipe = _PIPE_CACHE[key] = AbelianLegPipe(legs, is_dual=is_dual, combine_cstyle=not is_dual)
+    return pipe
+
+
+# AbelianLegPipe.prepare is pure integer work on the legs' sector tables: pipes are immutable, so one
+# instance per (legs, duality) serves every combine_legs of a sweep
+_PIPE_CACHE: dict = {}
 
 
 def combine_legs(T: SymmetricTensor, *groups, pipe_dualities=None):

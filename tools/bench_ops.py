@@ -1,0 +1,257 @@
+#!/usr/bin/env python3
+"""Per-row measurement of the SURVEY section 8(a) hot-path operations on one B200.
+
+  python tools/bench_ops.py [--chi 4096] [--dtype float64] [--no-ref] [--out gpurun_out/ops.json]
+
+For every row (permute_legs, combine_legs, split_legs, tdot, svd, truncated_svd, qr, eigh) it reports
+device time (CUDA events, best of ``--reps`` after warm-up, plan cache warm), the ALGORITHMIC work of
+SURVEY section 8(d) (bytes for the copies, LAPACK-formula flops for the factorisations, sum 2MKN for
+tdot), the resulting GB/s or TFLOP/s, and the time of the UNMODIFIED reference
+(AbelianBackend+NumpyBlockBackend from oracle/_ref) on the host cores for the same inputs.
+One JSON line per row, and a markdown table on stderr.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--chi", type=int, default=4096)
+    ap.add_argument("--dtype", default="float64", choices=["float64", "complex128"])
+    ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--no-ref", action="store_true")
+    ap.add_argument("--rows", default="permute,combine,split,tdot,svd,tsvd,qr,eigh")
+    ap.add_argument("--out", default=None)
+    return ap.parse_args()
+
+
+def legs_for(chi):
+    from cyten_b200.workloads import CONFIG_LEGS, u1_bond_leg, u1_phys_leg
+    if chi in CONFIG_LEGS:
+        Q, sigma = CONFIG_LEGS[chi]
+    else:   # interpolate the Gaussian width with log2(chi) like the named configs
+        Q = max(2, int(round(3 + 1.5 * (np.log2(chi) - 7))))
+        sigma = 1.2 + 0.5 * (np.log2(chi) - 7)
+    return u1_bond_leg(chi, Q, sigma), u1_phys_leg()
+
+
+def gpu_time(fn, reps, sync_result):
+    """Best-of-reps device time in ms; ``sync_result(res)`` forces deferred work (lazy permutes)."""
+    import torch
+    for _ in range(2):
+        sync_result(fn())
+    torch.cuda.synchronize()
+    best = float("inf")
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        sync_result(fn())
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    return best
+
+
+def touch(res):
+    """Materialises every arena of a result (tuple of tensors / scalars)."""
+    items = res if isinstance(res, (tuple, list)) else (res,)
+    for x in items:
+        d = getattr(x, "data", None)
+        if d is not None and hasattr(d, "buf"):
+            d.buf
+
+
+def svd_flops(shapes, cx):
+    f = 0.0
+    for m, n in shapes:
+        lo, hi = min(m, n), max(m, n)
+        f += 4.0 * hi * lo * lo + 8.0 * lo ** 3
+    return f * (4.0 if cx else 1.0)
+
+
+def qr_flops(shapes, cx):
+    f = 0.0
+    for m, n in shapes:
+        k = min(m, n)
+        f += 2.0 * (2.0 * m * n * k - 2.0 * k ** 3 / 3.0)
+    return f * (4.0 if cx else 1.0)
+
+
+def eigh_flops(shapes, cx):
+    return sum((4.0 / 3.0 + 8.0) * float(n) ** 3 for n, _ in shapes) * (4.0 if cx else 1.0)
+
+
+def main():
+    args = parse()
+    import torch
+    from cyten_b200 import tensors as ct
+    from cyten_b200.backend import B200AbelianBackend
+    from cyten_b200.tensors import SymmetricTensor
+    from cyten_b200.workloads import random_blocks
+
+    dev = torch.device("cuda:0")
+    be = B200AbelianBackend(dev)
+    chi, dt = args.chi, args.dtype
+    cx = dt == "complex128"
+    esz = 16 if cx else 8
+    v, p = legs_for(chi)
+    rows = args.rows.split(",")
+
+    hostA = random_blocks([v, p], [v], 7, dt)
+    hostB = random_blocks([v, p], [v], 8, dt)
+    hostT = random_blocks([v, p], [p.dual, v], 9, dt)     # full-rank two-site theta
+    A = SymmetricTensor.from_numpy_blocks(hostA[1], hostA[0], [v, p], [v], be, labels=["vL", "p", "vR"], dtype=dt)
+    B = SymmetricTensor.from_numpy_blocks(hostB[1], hostB[0], [v, p], [v], be, labels=["vL", "p", "vR"], dtype=dt)
+    TH = SymmetricTensor.from_numpy_blocks(hostT[1], hostT[0], [v, p], [p.dual, v], be,
+                                           labels=["vL", "p0", "p1", "vR"], dtype=dt)
+    # Hermitian two-leg tensor on the bond leg for eigh
+    rng = np.random.default_rng(11)
+    hb, hbi = [], []
+    for i, m in enumerate(v.multiplicities):
+        x = rng.standard_normal((m, m)) + (1j * rng.standard_normal((m, m)) if cx else 0)
+        hb.append(x + x.conj().T)
+        hbi.append([i, i])
+    HM = SymmetricTensor.from_numpy_blocks(hb, np.asarray(hbi), [v], [v], be, labels=["a", "b"], dtype=dt)
+
+    peak_hbm = json.loads((ROOT / "MEASURED_PEAKS.json").read_text()).get("hbm_gbs", 6650.0) \
+        if (ROOT / "MEASURED_PEAKS.json").exists() else 6650.0
+    n = 8192
+    a = torch.randn(n, n, dtype=torch.float64, device=dev)
+    torch.matmul(a, a)
+    best = float("inf")
+    for _ in range(3):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); torch.matmul(a, a); e1.record(); torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    peak_f64 = 2.0 * n ** 3 / (best * 1e-3) / 1e12
+    del a
+
+    THc = ct.combine_legs(TH, [0, 1], [2, 3])
+    touch(THc)
+    sect = [(int(s[0]), int(s[1])) for s in THc.data.shapes]
+    Ac = ct.combine_legs(A, [0, 1])
+    qsect = [(int(s[0]), int(s[1])) for s in Ac.data.shapes]
+    hsect = [(int(s[0]), int(s[1])) for s in HM.data.shapes]
+
+    out = []
+
+    def emit(row, ms, work, unit, peak, note=""):
+        rate = work / (ms * 1e-3) / (1e9 if unit == "GB/s" else 1e12)
+        out.append({"row": row, "chi": chi, "dtype": dt, "gpu_ms": ms, "work": work, "rate": rate, "unit": unit,
+                    "peak": peak, "frac": rate / peak, "note": note})
+
+    be.plan_mkn = None
+    if "permute" in rows:
+        ms = gpu_time(lambda: ct.permute_legs(TH, ["vR", "p1"], ["vL", "p0"]), args.reps, touch)
+        emit("a3 permute_legs(theta -> [vR,p1 | vL,p0])", ms, 2.0 * TH.data.nbytes(), "GB/s", peak_hbm)
+    if "combine" in rows:
+        ms = gpu_time(lambda: ct.combine_legs(TH, [0, 1], [2, 3]), args.reps, touch)
+        emit("a4 combine_legs(theta, [vL,p0], [p1,vR])", ms, 2.0 * TH.data.nbytes(), "GB/s", peak_hbm)
+    if "split" in rows:
+        ms = gpu_time(lambda: ct.split_legs(THc), args.reps, touch)
+        emit("a5 split_legs", ms, 2.0 * TH.data.nbytes(), "GB/s", peak_hbm)
+    if "tdot" in rows:
+        be.plan_mkn = []
+        touch(ct.tdot(A, B, [2], [0]))
+        fl = (8.0 if cx else 2.0) * float(sum(be.plan_mkn))
+        be.plan_mkn = None
+        ms = gpu_time(lambda: ct.tdot(A, B, [2], [0]), args.reps, touch)
+        emit("a6 tdot(A, B, vR, vL)", ms, fl, "TFLOP/s", peak_f64)
+    if "svd" in rows:
+        ms = gpu_time(lambda: ct.svd(TH), max(2, args.reps // 2), touch)
+        emit("a7 svd(theta) full rank", ms, svd_flops(sect, cx), "TFLOP/s", peak_f64,
+             f"{len(sect)} sectors, largest {max(sect)}; sweeps_max={int(be.last_info.abs().max().item())}")
+    if "tsvd" in rows:
+        ms = gpu_time(lambda: ct.truncated_svd(TH, chi_max=chi, svd_min=1e-14), max(2, args.reps // 2), touch)
+        emit("a7+a8 truncated_svd(theta, chi_max=chi)", ms, svd_flops(sect, cx), "TFLOP/s", peak_f64)
+    if "qr" in rows:
+        ms = gpu_time(lambda: ct.qr(A), max(2, args.reps // 2), touch)
+        emit("a9 qr(A[vL,p | vR])", ms, qr_flops(qsect, cx), "TFLOP/s", peak_f64,
+             f"{len(qsect)} sectors, largest {max(qsect)}")
+    if "eigh" in rows:
+        ms = gpu_time(lambda: ct.eigh(HM), max(2, args.reps // 2), touch)
+        emit("a10 eigh(H[v | v])", ms, eigh_flops(hsect, cx), "TFLOP/s", peak_f64,
+             f"{len(hsect)} sectors, largest {max(hsect)}")
+
+    # ---- the reference on the host cores, same inputs ----
+    ref = {}
+    if not args.no_ref and list((ROOT / "oracle" / "_ref" / "cyten").glob("_core*.so")):
+        sys.path.insert(0, str(ROOT / "oracle" / "_ref"))
+        import cyten as rc
+        rbe = rc.get_backend("abelian", "numpy")
+        sym = rc.u1_symmetry
+        rdt = rc.Dtype.complex128 if cx else rc.Dtype.float64
+
+        def conv(leg):
+            return rc.ElementarySpace.from_defining_sectors(sym, leg.defining_sectors, leg.multiplicities, is_dual=leg.is_dual)
+
+        def mk(host, cod, dom, labels):
+            bi, blocks = host
+            data = rc.backends.AbelianBackendData(dtype=rdt, device="cpu",
+                                                  blocks=[rbe.block_backend.as_block(b) for b in blocks],
+                                                  block_inds=rc.backends.BlockInds(bi), is_sorted=True)
+            return rc.SymmetricTensor(data, [conv(l) for l in cod], [conv(l) for l in dom], backend=rbe, labels=labels)
+        rA = mk(hostA, [v, p], [v], ["vL", "p", "vR"])
+        rB = mk(hostB, [v, p], [v], ["vL", "p", "vR"])
+        rT = mk(hostT, [v, p], [p.dual, v], ["vL", "p0", "p1", "vR"])
+        rH = mk((np.asarray(hbi), hb), [v], [v], ["a", "b"])
+        rTc = rc.combine_legs(rT, [0, 1], [2, 3])
+
+        def cpu_time(fn, reps=2):
+            fn()
+            best = float("inf")
+            for _ in range(reps):
+                t0 = time.perf_counter()
+                fn()
+                best = min(best, time.perf_counter() - t0)
+            return best * 1e3
+
+        def force(t):   # numpy permutes are lazy views: force like the next consumer would
+            for b in t.data.blocks:
+                np.ascontiguousarray(rbe.block_backend.to_numpy(b))
+        calls = {
+            "a3": lambda: force(rc.permute_legs(rT, ["vR", "p1"], ["vL", "p0"], bend_right=None)),
+            "a4": lambda: rc.combine_legs(rT, [0, 1], [2, 3]),
+            "a5": lambda: rc.split_legs(rTc),
+            "a6": lambda: rc.tdot(rA, rB, ["vR"], ["vL"]),
+            "a7": lambda: rc.svd(rT),
+            "a7+a8": lambda: rc.truncated_svd(rT, chi_max=chi, svd_min=1e-14),
+            "a9": lambda: rc.qr(rA),
+            "a10": lambda: rc.eigh(rH, ["a", "b", "c"], False),
+        }
+        for o in out:
+            key = o["row"].split()[0]
+            try:
+                ref[key] = cpu_time(calls[key], 1 if key in ("a7", "a7+a8", "a9", "a10") else 2)
+            except Exception as e:   # noqa: BLE001
+                ref[key] = f"failed: {e!r}"
+    for o in out:
+        key = o["row"].split()[0]
+        o["ref_cpu_ms"] = ref.get(key)
+        o["cores"] = os.cpu_count()
+        if isinstance(o["ref_cpu_ms"], float):
+            o["speedup"] = o["ref_cpu_ms"] / o["gpu_ms"]
+        print(json.dumps(o))
+    print(f"\n| row | GPU ms | rate | frac of peak | reference CPU ms ({os.cpu_count()} cores) | note |", file=sys.stderr)
+    print("|---|---|---|---|---|---|", file=sys.stderr)
+    for o in out:
+        r = o["ref_cpu_ms"]
+        print(f"| {o['row']} | {o['gpu_ms']:.3f} | {o['rate']:.1f} {o['unit']} | {o['frac']:.3f} | "
+              f"{r if not isinstance(r, float) else round(r, 1)} | {o['note']} |", file=sys.stderr)
+    if args.out:
+        Path(args.out).write_text("\n".join(json.dumps(o) for o in out) + "\n")
+
+
+if __name__ == "__main__":
+    main()
