@@ -1,4 +1,9 @@
-// One-sided BLOCK Jacobi for the large real sectors of svd / eigh (included by factorize.cu).
+// One-sided BLOCK Jacobi for the large sectors of svd / eigh (included by factorize.cu); real and complex.
+// complex128 sectors run on the SAME real DMMA machinery over the interleaved (re, im) view of the rows:
+//   Re(R R^H) is the plain Gram matrix of the 2c-long real rows, Im(R R^H) the Gram product with the
+//   B fragment taken from the neighbouring column with a sign (b'[2k] = -b[2k+1], b'[2k+1] = b[2k]);
+//   Q R = Qr R + Qi R' with the same swizzle on the column index.  So a complex sector costs 2 DMMAs
+//   per fragment pair on twice as many columns (the 4 real products of a complex product).
 //
 // The scalar kernel in factorize.cu streams two rows of W and Z through L2 for every plane rotation;
 // for a 1000 x 1000 sector that is ~30 GB of traffic per sweep and no tensor-core work.  Here the rows
@@ -39,6 +44,8 @@ constexpr int BJ_AC = 128;               // columns per apply work unit
 constexpr size_t BJ_SMEM_GRAM = sizeof(double) * (size_t)(2 * BJ_R * BJ_LDT);
 constexpr size_t BJ_SMEM_ROT = sizeof(double) * (size_t)(2 * BJ_R * BJ_LDG);
 constexpr size_t BJ_SMEM_APPLY = sizeof(double) * (size_t)(BJ_SQ + BJ_SBUF_B);
+constexpr size_t BJ_SMEM_ROT_CX = 2 * BJ_SMEM_ROT;                                            // + Im G, Im Q
+constexpr size_t BJ_SMEM_APPLY_CX = sizeof(double) * (size_t)(2 * BJ_SQ + BJ_SBUF_B);        // + Im Q
 
 struct BjItem {
     int32_t mat;     // index into the FzDesc table
@@ -121,7 +128,8 @@ __device__ __forceinline__ void bj_load_tile(double* tile, const double* __restr
 
 // [rows of the item] <- Q [rows of the item] for columns [cbeg, cend) of one row-major matrix, 64 columns
 // per step, in place
-__device__ __forceinline__ void bj_apply(const double* sQ, double* sBuf, double* __restrict__ base, int64_t ld,
+template <bool CX>
+__device__ __forceinline__ void bj_apply(const double* sQ, const double* sQi, double* sBuf, double* __restrict__ base, int64_t ld,
                                          int64_t ncols, const int* s_rows, int64_t cbeg, int64_t cend)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -154,6 +162,21 @@ __device__ __forceinline__ void bj_apply(const double* sQ, double* sBuf, double*
             for (int i = 0; i < 2; ++i)
 #pragma unroll
                 for (int j = 0; j < 4; ++j) bj_dmma(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+            if (CX) {
+                // + Qi R': R'[k][2n] = -R[k][2n+1], R'[k][2n+1] = R[k][2n]  (column parity = parity of lr)
+                double ai[2], bs[4];
+#pragma unroll
+                for (int i = 0; i < 2; ++i) ai[i] = sQi[(wm0 + i * 8 + lr) * BJ_LDQ + kk + lc];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const double v = cur[(kk + lc) * BJ_LDB + ((wn0 + j * 8 + lr) ^ 1)];
+                    bs[j] = (lr & 1) ? v : -v;
+                }
+#pragma unroll
+                for (int i = 0; i < 2; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) bj_dmma(acc[i][j][0], acc[i][j][1], ai[i], bs[j]);
+            }
         }
         const int64_t n0 = cbeg + ch * BJ_BN;
 #pragma unroll
@@ -177,7 +200,7 @@ __device__ __forceinline__ void bj_apply(const double* sQ, double* sBuf, double*
     bj_wait<0>();
 }
 
-struct BjRot { int p, q; double cs, sn; };
+struct BjRot { int p, q; double cs, sn, si; };   // rotation [[cs, -s], [conj(s), cs]], s = sn + i si (si = 0 for real sectors)
 
 __device__ __forceinline__ void bj_fill_rows(int* s_rows, const BjItem& it, const int* __restrict__ rowmap)
 {
@@ -188,7 +211,8 @@ __device__ __forceinline__ void bj_fill_rows(int* s_rows, const BjItem& it, cons
 }
 
 // ---- 1. partial Gram matrices -----------------------------------------------------------------
-__global__ void __launch_bounds__(BJ_THREADS, 3)
+template <bool CX>
+__global__ void __launch_bounds__(BJ_THREADS, CX ? 2 : 3)
 bj_gram_kernel(const double* __restrict__ ws, const FzDesc* __restrict__ descs, const BjItem* __restrict__ items,
                const BjWork* __restrict__ works, const int* __restrict__ active, const int* __restrict__ rowmap,
                double* __restrict__ gpart)
@@ -201,12 +225,18 @@ bj_gram_kernel(const double* __restrict__ ws, const FzDesc* __restrict__ descs, 
     if (!active[it.mat]) return;
     bj_fill_rows(s_rows, it, rowmap);
     const FzDesc D = descs[it.mat];
-    const int64_t c = D.c;
-    const double* W = ws + D.w_off;
+    constexpr int CM = CX ? 2 : 1;            // real columns per element
+    const int64_t c = D.c * CM;
+    const double* W = ws + D.w_off * CM;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int lr = lane >> 2, lc = lane & 3;
     const bool vec = (c & 1) == 0;
     const int wm0 = (warp >> 2) * 32, wn0 = (warp & 3) * 16;
+    double acci[CX ? 4 : 1][2][2];
+#pragma unroll
+    for (int i = 0; i < (CX ? 4 : 1); ++i)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) { acci[i][j][0] = 0.0; acci[i][j][1] = 0.0; }
     const int64_t k_beg = (int64_t)wk.arg * BJ_KS;
     const int64_t k_end = k_beg + BJ_KS < c ? k_beg + BJ_KS : c;
     __syncthreads();
@@ -235,31 +265,50 @@ bj_gram_kernel(const double* __restrict__ ws, const FzDesc* __restrict__ descs, 
             for (int i = 0; i < 4; ++i)
 #pragma unroll
                 for (int j = 0; j < 2; ++j) bj_dmma(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+            if (CX) {
+                // Im G[p][q] = sum_k (Wp[2k+1] Wq[2k] - Wp[2k] Wq[2k+1]): B fragment from the neighbouring column
+                double bs[2];
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const double v = cur[(wn0 + j * 8 + lr) * BJ_LDT + kk + (lc ^ 1)];
+                    bs[j] = (lc & 1) ? v : -v;
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) bj_dmma(acci[CX ? i : 0][j][0], acci[CX ? i : 0][j][1], a[i], bs[j]);
+            }
         }
         __syncthreads();
     }
     bj_wait<0>();
-    double* out = gpart + (size_t)blockIdx.x * (BJ_R * BJ_R);
+    double* out = gpart + (size_t)blockIdx.x * (BJ_R * BJ_R * CM);
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
             const int row = wm0 + i * 8 + lr, col = wn0 + j * 8 + lc * 2;
             __stcg(reinterpret_cast<double2*>(out + row * BJ_R + col), make_double2(acc[i][j][0], acc[i][j][1]));
+            if (CX) __stcg(reinterpret_cast<double2*>(out + BJ_R * BJ_R + row * BJ_R + col), make_double2(acci[CX ? i : 0][j][0], acci[CX ? i : 0][j][1]));
         }
 }
 
 // ---- 2. convergence test + one cyclic pass of rotations ----------------------------------------------
 constexpr int BJ_RT = 1024;              // threads of the rotation kernel
 
+template <bool CX>
 __global__ void __launch_bounds__(BJ_RT)
 bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ items, const int* __restrict__ active,
                  int* __restrict__ flags, const double* __restrict__ floor2, int use_floor,
                  const double* __restrict__ gpart, double* __restrict__ qbuf, int* __restrict__ skip)
 {
     extern __shared__ __align__(16) double bj_smem[];
-    double* sG = bj_smem;                    // [64][65]
-    double* sQ = bj_smem + BJ_R * BJ_LDG;    // [64][65]
+    constexpr int CM = CX ? 2 : 1;
+    constexpr int PL = BJ_R * BJ_LDG;        // one [64][65] plane
+    double* sG = bj_smem;                    // Re G
+    double* sQ = bj_smem + PL;               // Re Q
+    double* sGi = bj_smem + 2 * PL;          // Im G, Im Q (complex sectors only)
+    double* sQi = bj_smem + 3 * PL;
     __shared__ BjRot s_rot[BJ_B];
     __shared__ int s_any;
     const BjItem it = items[blockIdx.x];
@@ -271,9 +320,14 @@ bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ it
     const bool cross = it.nj > 0;
     // G = sum of the partials, in slice order
     for (int e = tid; e < BJ_R * BJ_R; e += BJ_RT) {
-        double g = 0.0;
-        for (int w = 0; w < it.nw; ++w) g += __ldcg(gpart + (size_t)(it.w0 + w) * (BJ_R * BJ_R) + e);
+        double g = 0.0, gi = 0.0;
+        for (int w = 0; w < it.nw; ++w) {
+            const double* part = gpart + (size_t)(it.w0 + w) * (BJ_R * BJ_R * CM);
+            g += __ldcg(part + e);
+            if (CX) gi += __ldcg(part + BJ_R * BJ_R + e);
+        }
         sG[(e / BJ_R) * BJ_LDG + e % BJ_R] = g;
+        if (CX) sGi[(e / BJ_R) * BJ_LDG + e % BJ_R] = gi;
     }
     if (tid == 0) s_any = 0;
     __syncthreads();
@@ -286,7 +340,8 @@ bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ it
             else { p = e / BJ_B; q = e % BJ_B; valid = p < q && q < it.ni; }
             if (valid) {
                 const double al = sG[p * BJ_LDG + p], be = sG[q * BJ_LDG + q], ga = sG[p * BJ_LDG + q];
-                bad |= (al >= FZ_TINY && be >= FZ_TINY && !(al <= fl && be <= fl) && ga * ga > tol2 * al * be);
+                const double gi = CX ? sGi[p * BJ_LDG + q] : 0.0;
+                bad |= (al >= FZ_TINY && be >= FZ_TINY && !(al <= fl && be <= fl) && ga * ga + gi * gi > tol2 * al * be);
             }
         }
         if (bad) s_any = 1;
@@ -294,7 +349,10 @@ bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ it
         if (!s_any) { if (tid == 0) skip[blockIdx.x] = 1; return; }   // every pair of this item is orthogonal
         if (tid == 0) { flags[it.mat] = 1; skip[blockIdx.x] = 0; }
     }
-    for (int e = tid; e < BJ_R * BJ_R; e += BJ_RT) sQ[(e / BJ_R) * BJ_LDG + e % BJ_R] = (e / BJ_R == e % BJ_R) ? 1.0 : 0.0;
+    for (int e = tid; e < BJ_R * BJ_R; e += BJ_RT) {
+        sQ[(e / BJ_R) * BJ_LDG + e % BJ_R] = (e / BJ_R == e % BJ_R) ? 1.0 : 0.0;
+        if (CX) sQi[(e / BJ_R) * BJ_LDG + e % BJ_R] = 0.0;
+    }
     const int nsteps = cross ? BJ_B : BJ_B - 1;
     const int nrot = cross ? BJ_B : BJ_B / 2;
     __syncthreads();
@@ -311,82 +369,123 @@ bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ it
                 if (p > q) { const int t = p; p = q; q = t; }
                 valid = q < it.ni;
             }
-            double cs = 1.0, sn = 0.0;
+            double cs = 1.0, sn = 0.0, si = 0.0;
             if (valid) {
-                const double al = sG[p * BJ_LDG + p], be = sG[q * BJ_LDG + q], ga = sG[p * BJ_LDG + q];
-                if (al >= FZ_TINY && be >= FZ_TINY && !(al <= fl && be <= fl) && ga * ga > tol2 * al * be) {
+                const double al = sG[p * BJ_LDG + p], be = sG[q * BJ_LDG + q], gr = sG[p * BJ_LDG + q];
+                const double gi = CX ? sGi[p * BJ_LDG + q] : 0.0;
+                const double g2 = gr * gr + gi * gi;
+                if (al >= FZ_TINY && be >= FZ_TINY && !(al <= fl && be <= fl) && g2 > tol2 * al * be) {
+                    // rows x_p, x_q with <x_p, x_q> = ga = |ga| e^{i phi}:  x_p' = cs x_p - s x_q,
+                    // x_q' = conj(s) x_p + cs x_q,  s = sn e^{i phi}  (real sectors: phi = 0 or pi)
+                    const double ga = CX ? sqrt(g2) : gr;
                     const double zeta = (be - al) / (2.0 * ga);
                     const double t = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
                     cs = 1.0 / sqrt(1.0 + t * t);
-                    sn = cs * t;
+                    const double s0 = cs * t;
+                    if (CX) { sn = s0 * gr / ga; si = s0 * gi / ga; }
+                    else sn = s0;
                 }
             }
-            s_rot[tid].p = p; s_rot[tid].q = q; s_rot[tid].cs = cs; s_rot[tid].sn = sn;
+            s_rot[tid].p = p; s_rot[tid].q = q; s_rot[tid].cs = cs; s_rot[tid].sn = sn; s_rot[tid].si = si;
         }
         __syncthreads();
-        // G <- J G J^T, one 2x2 block G[{p,q}][{p',q'}] per (rotation a, rotation b): the blocks are disjoint,
+        // G <- J G J^H, one 2x2 block G[{p,q}][{p',q'}] per (rotation a, rotation b): the blocks are disjoint,
         // so rows and columns are updated in ONE phase;  Q <- J Q (rows p, q) in the same phase
         for (int e = tid; e < nrot * nrot; e += BJ_RT) {
             const BjRot Ra = s_rot[e / nrot], Rb = s_rot[e % nrot];
-            if (Ra.sn == 0.0 && Rb.sn == 0.0) continue;
-            const double g00 = sG[Ra.p * BJ_LDG + Rb.p], g01 = sG[Ra.p * BJ_LDG + Rb.q];
-            const double g10 = sG[Ra.q * BJ_LDG + Rb.p], g11 = sG[Ra.q * BJ_LDG + Rb.q];
-            // rows:  [x; y] <- [cs x - sn y; sn x + cs y]
-            const double h00 = Ra.cs * g00 - Ra.sn * g10, h01 = Ra.cs * g01 - Ra.sn * g11;
-            const double h10 = Ra.sn * g00 + Ra.cs * g10, h11 = Ra.sn * g01 + Ra.cs * g11;
-            // columns with rotation b
-            sG[Ra.p * BJ_LDG + Rb.p] = Rb.cs * h00 - Rb.sn * h01;
-            sG[Ra.p * BJ_LDG + Rb.q] = Rb.sn * h00 + Rb.cs * h01;
-            sG[Ra.q * BJ_LDG + Rb.p] = Rb.cs * h10 - Rb.sn * h11;
-            sG[Ra.q * BJ_LDG + Rb.q] = Rb.sn * h10 + Rb.cs * h11;
+            if (Ra.sn == 0.0 && Rb.sn == 0.0 && Ra.si == 0.0 && Rb.si == 0.0) continue;
+            const int i00 = Ra.p * BJ_LDG + Rb.p, i01 = Ra.p * BJ_LDG + Rb.q;
+            const int i10 = Ra.q * BJ_LDG + Rb.p, i11 = Ra.q * BJ_LDG + Rb.q;
+            if (!CX) {
+                const double g00 = sG[i00], g01 = sG[i01], g10 = sG[i10], g11 = sG[i11];
+                // rows:  [x; y] <- [cs x - sn y; sn x + cs y]
+                const double h00 = Ra.cs * g00 - Ra.sn * g10, h01 = Ra.cs * g01 - Ra.sn * g11;
+                const double h10 = Ra.sn * g00 + Ra.cs * g10, h11 = Ra.sn * g01 + Ra.cs * g11;
+                // columns with rotation b
+                sG[i00] = Rb.cs * h00 - Rb.sn * h01;
+                sG[i01] = Rb.sn * h00 + Rb.cs * h01;
+                sG[i10] = Rb.cs * h10 - Rb.sn * h11;
+                sG[i11] = Rb.sn * h10 + Rb.cs * h11;
+            } else {
+                const double g00r = sG[i00], g01r = sG[i01], g10r = sG[i10], g11r = sG[i11];
+                const double g00i = sGi[i00], g01i = sGi[i01], g10i = sGi[i10], g11i = sGi[i11];
+                // rows: h0 = cs g0 - s g1,  h1 = conj(s) g0 + cs g1   (s = sn + i si of rotation a)
+                const double h00r = Ra.cs * g00r - (Ra.sn * g10r - Ra.si * g10i), h00i = Ra.cs * g00i - (Ra.sn * g10i + Ra.si * g10r);
+                const double h01r = Ra.cs * g01r - (Ra.sn * g11r - Ra.si * g11i), h01i = Ra.cs * g01i - (Ra.sn * g11i + Ra.si * g11r);
+                const double h10r = (Ra.sn * g00r + Ra.si * g00i) + Ra.cs * g10r, h10i = (Ra.sn * g00i - Ra.si * g00r) + Ra.cs * g10i;
+                const double h11r = (Ra.sn * g01r + Ra.si * g01i) + Ra.cs * g11r, h11i = (Ra.sn * g01i - Ra.si * g01r) + Ra.cs * g11i;
+                // columns: new[.][p] = cs h_p - conj(s) h_q,  new[.][q] = s h_p + cs h_q   (rotation b)
+                sG[i00] = Rb.cs * h00r - (Rb.sn * h01r + Rb.si * h01i);  sGi[i00] = Rb.cs * h00i - (Rb.sn * h01i - Rb.si * h01r);
+                sG[i01] = (Rb.sn * h00r - Rb.si * h00i) + Rb.cs * h01r;  sGi[i01] = (Rb.sn * h00i + Rb.si * h00r) + Rb.cs * h01i;
+                sG[i10] = Rb.cs * h10r - (Rb.sn * h11r + Rb.si * h11i);  sGi[i10] = Rb.cs * h10i - (Rb.sn * h11i - Rb.si * h11r);
+                sG[i11] = (Rb.sn * h10r - Rb.si * h10i) + Rb.cs * h11r;  sGi[i11] = (Rb.sn * h10i + Rb.si * h10r) + Rb.cs * h11i;
+            }
         }
         for (int e = tid; e < nrot * BJ_R; e += BJ_RT) {
             const BjRot R = s_rot[e / BJ_R];
-            if (R.sn == 0.0) continue;
+            if (R.sn == 0.0 && R.si == 0.0) continue;
             const int col = e % BJ_R;
-            const double x = sQ[R.p * BJ_LDG + col], y = sQ[R.q * BJ_LDG + col];
-            sQ[R.p * BJ_LDG + col] = R.cs * x - R.sn * y;
-            sQ[R.q * BJ_LDG + col] = R.sn * x + R.cs * y;
+            const int ip = R.p * BJ_LDG + col, iq = R.q * BJ_LDG + col;
+            if (!CX) {
+                const double x = sQ[ip], y = sQ[iq];
+                sQ[ip] = R.cs * x - R.sn * y;
+                sQ[iq] = R.sn * x + R.cs * y;
+            } else {
+                const double xr = sQ[ip], xi = sQi[ip], yr = sQ[iq], yi = sQi[iq];
+                sQ[ip] = R.cs * xr - (R.sn * yr - R.si * yi);   sQi[ip] = R.cs * xi - (R.sn * yi + R.si * yr);
+                sQ[iq] = (R.sn * xr + R.si * xi) + R.cs * yr;   sQi[iq] = (R.sn * xi - R.si * xr) + R.cs * yi;
+            }
         }
         __syncthreads();
     }
-    double* out = qbuf + (size_t)blockIdx.x * (BJ_R * BJ_R);
-    for (int e = tid; e < BJ_R * BJ_R; e += BJ_RT) __stcg(out + e, sQ[(e / BJ_R) * BJ_LDG + e % BJ_R]);
+    double* out = qbuf + (size_t)blockIdx.x * (BJ_R * BJ_R * CM);
+    for (int e = tid; e < BJ_R * BJ_R; e += BJ_RT) {
+        __stcg(out + e, sQ[(e / BJ_R) * BJ_LDG + e % BJ_R]);
+        if (CX) __stcg(out + BJ_R * BJ_R + e, sQi[(e / BJ_R) * BJ_LDG + e % BJ_R]);
+    }
 }
 
 // ---- 3. rows <- Q rows -------------------------------------------------------------------------------
-__global__ void __launch_bounds__(BJ_THREADS, 2)
+template <bool CX>
+__global__ void __launch_bounds__(BJ_THREADS, CX ? 1 : 2)
 bj_apply_kernel(double* __restrict__ ws, const FzDesc* __restrict__ descs, const BjItem* __restrict__ items,
                 const BjWork* __restrict__ works, const int* __restrict__ rowmap, const double* __restrict__ qbuf,
                 const int* __restrict__ skip)
 {
     extern __shared__ __align__(16) double bj_smem[];
-    double* sQ = bj_smem;                    // [64][68]
-    double* sBuf = bj_smem + BJ_SQ;          // two tiles [64][68]
+    constexpr int CM = CX ? 2 : 1;
+    double* sQ = bj_smem;                              // Re Q [64][68]
+    double* sQi = bj_smem + BJ_SQ;                     // Im Q (complex sectors only)
+    double* sBuf = bj_smem + (CX ? 2 : 1) * BJ_SQ;     // two tiles [64][68]
     __shared__ int s_rows[BJ_R];
     const BjWork wk = works[blockIdx.x];
     if (skip[wk.item]) return;
     const BjItem it = items[wk.item];
     bj_fill_rows(s_rows, it, rowmap);
-    const double* q = qbuf + (size_t)wk.item * (BJ_R * BJ_R);
+    const double* q = qbuf + (size_t)wk.item * (BJ_R * BJ_R * CM);
     for (int e = threadIdx.x; e < BJ_R * BJ_R / 2; e += BJ_THREADS) {
-        const double2 v = __ldcg(reinterpret_cast<const double2*>(q) + e);
         const int row = (2 * e) / BJ_R, col = (2 * e) % BJ_R;
+        const double2 v = __ldcg(reinterpret_cast<const double2*>(q) + e);
         sQ[row * BJ_LDQ + col] = v.x;
         sQ[row * BJ_LDQ + col + 1] = v.y;
+        if (CX) {
+            const double2 vi = __ldcg(reinterpret_cast<const double2*>(q + BJ_R * BJ_R) + e);
+            sQi[row * BJ_LDQ + col] = vi.x;
+            sQi[row * BJ_LDQ + col + 1] = vi.y;
+        }
     }
     __syncthreads();
     const FzDesc D = descs[it.mat];
     const int which = wk.arg >> 24;
     const int64_t cbeg = (int64_t)(wk.arg & 0xffffff) * BJ_AC;
-    if (which == 0) bj_apply(sQ, sBuf, ws + D.w_off, D.c, D.c, s_rows, cbeg, cbeg + BJ_AC);
-    else bj_apply(sQ, sBuf, ws + D.z_off, D.r, D.r, s_rows, cbeg, cbeg + BJ_AC);
+    if (which == 0) bj_apply<CX>(sQ, sQi, sBuf, ws + D.w_off * CM, D.c * CM, D.c * CM, s_rows, cbeg, cbeg + BJ_AC);
+    else bj_apply<CX>(sQ, sQi, sBuf, ws + D.z_off * CM, D.r * CM, D.r * CM, s_rows, cbeg, cbeg + BJ_AC);
 }
 
 // squared row norms of the working copies: one warp per row, grid-stride over (matrix, row)
 __global__ void __launch_bounds__(256)
 bj_norms_kernel(const double* __restrict__ ws, const FzDesc* __restrict__ descs, const int64_t* __restrict__ mats,
-                const int* __restrict__ rowbase, int nmats, double* __restrict__ norm2)
+                const int* __restrict__ rowbase, int nmats, double* __restrict__ norm2, int cm)
 {
     const int lane = threadIdx.x & 31;
     const int64_t gwarp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -396,9 +495,10 @@ bj_norms_kernel(const double* __restrict__ ws, const FzDesc* __restrict__ descs,
         int lo = 0, hi = nmats;
         while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (rowbase[mid] <= g) lo = mid; else hi = mid; }
         const FzDesc D = descs[mats[lo]];
-        const double* x = ws + D.w_off + (g - rowbase[lo]) * D.c;
+        const int64_t cr = D.c * cm;     // real columns (cm = 2: interleaved complex rows)
+        const double* x = ws + D.w_off * cm + (g - rowbase[lo]) * cr;
         double acc = 0.0;
-        for (int64_t q = lane; q < D.c; q += 32) { const double v = __ldcg(x + q); acc = fma(v, v, acc); }
+        for (int64_t q = lane; q < cr; q += 32) { const double v = __ldcg(x + q); acc = fma(v, v, acc); }
         acc = warp_sum(acc);
         if (lane == 0) norm2[g] = acc;
     }

@@ -538,7 +538,7 @@ struct BjRounds {
 
 // items over the blocks [kb[mat], nb) of every listed matrix
 static void bj_build_rounds(BjRounds& R, const std::vector<FzDesc>& descs, const std::vector<int64_t>& mats,
-                            const std::vector<int>& rowbase, const std::vector<int>& first_block)
+                            const std::vector<int>& rowbase, const std::vector<int>& first_block, int cm)
 {
     R.rounds.assign(1, {});
     for (size_t q = 0; q < mats.size(); ++q) {
@@ -582,12 +582,12 @@ static void bj_build_rounds(BjRounds& R, const std::vector<FzDesc>& descs, const
         int32_t w = 0;
         for (size_t idx = 0; idx < rd.size(); ++idx) {
             const FzDesc& D = descs[(size_t)rd[idx].mat];
-            const int32_t nsl = (int32_t)((D.c + BJ_KS - 1) / BJ_KS);
+            const int32_t nsl = (int32_t)((D.c * cm + BJ_KS - 1) / BJ_KS);   // cm = 2: real columns of a complex row
             rd[idx].w0 = w; rd[idx].nw = nsl;
             for (int32_t sl = 0; sl < nsl; ++sl) R.gworks.push_back(BjWork{(int32_t)idx, sl});
             w += nsl;
-            for (int32_t ch = 0; ch < (int32_t)((D.c + BJ_AC - 1) / BJ_AC); ++ch) R.aworks.push_back(BjWork{(int32_t)idx, ch});
-            for (int32_t ch = 0; ch < (int32_t)((D.r + BJ_AC - 1) / BJ_AC); ++ch) R.aworks.push_back(BjWork{(int32_t)idx, (1 << 24) | ch});
+            for (int32_t ch = 0; ch < (int32_t)((D.c * cm + BJ_AC - 1) / BJ_AC); ++ch) R.aworks.push_back(BjWork{(int32_t)idx, ch});
+            for (int32_t ch = 0; ch < (int32_t)((D.r * cm + BJ_AC - 1) / BJ_AC); ++ch) R.aworks.push_back(BjWork{(int32_t)idx, (1 << 24) | ch});
         }
         R.max_items = std::max(R.max_items, rd.size());
         R.max_gworks = std::max(R.max_gworks, (size_t)w);
@@ -598,36 +598,38 @@ static void bj_build_rounds(BjRounds& R, const std::vector<FzDesc>& descs, const
     R.astart.push_back(R.aworks.size());
 }
 
-template <bool EIGH>
+template <bool EIGH, bool CX>
 static int run_block_jacobi(const void* a, void* o0, double* s_out, void* o2, void* d_ws, double* d_aux,
                             FzDesc* d_desc, const std::vector<FzDesc>& descs, const std::vector<int64_t>& big,
                             const int64_t* sel_big, int64_t* info, cudaStream_t stream)
 {
+    constexpr int CM = CX ? 2 : 1;
+    constexpr size_t SMEM_ROT = CX ? BJ_SMEM_ROT_CX : BJ_SMEM_ROT, SMEM_APPLY = CX ? BJ_SMEM_APPLY_CX : BJ_SMEM_APPLY;
     static bool configured = false;
     if (!configured) {
-        CYB_CHECK_CUDA(cudaFuncSetAttribute(bj_gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BJ_SMEM_GRAM));
-        CYB_CHECK_CUDA(cudaFuncSetAttribute(bj_rotate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BJ_SMEM_ROT));
-        CYB_CHECK_CUDA(cudaFuncSetAttribute(bj_apply_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BJ_SMEM_APPLY));
+        CYB_CHECK_CUDA(cudaFuncSetAttribute(bj_gram_kernel<CX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BJ_SMEM_GRAM));
+        CYB_CHECK_CUDA(cudaFuncSetAttribute(bj_rotate_kernel<CX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_ROT));
+        CYB_CHECK_CUDA(cudaFuncSetAttribute(bj_apply_kernel<CX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_APPLY));
         configured = true;
     }
     const int nbig = (int)big.size();
     const size_t nmat = descs.size();
-    cudaError_t err = launch_team(jacobi_svd_kernel<false, FZ_BIG_G, EIGH, PH_INIT>, FZ_BIG_G, nbig, stream,
+    cudaError_t err = launch_team(jacobi_svd_kernel<CX, FZ_BIG_G, EIGH, PH_INIT>, FZ_BIG_G, nbig, stream,
                                   a, o0, s_out, o2, d_ws, d_aux, d_desc, sel_big, info);
     if (err != cudaSuccess) { set_error("block jacobi: load launch failed: %s", cudaGetErrorString(err)); return CYB_ERR_CUDA; }
     std::vector<int> rowbase((size_t)nbig + 1, 0);
     for (int q = 0; q < nbig; ++q) rowbase[(size_t)q + 1] = rowbase[(size_t)q] + (int)descs[(size_t)big[(size_t)q]].r;
     const size_t nrows = (size_t)rowbase[(size_t)nbig];
     BjRounds R1, R2;
-    bj_build_rounds(R1, descs, big, rowbase, std::vector<int>((size_t)nbig, 0));
+    bj_build_rounds(R1, descs, big, rowbase, std::vector<int>((size_t)nbig, 0), CM);
     // device scratch: items | Gram works | apply works (pass-2 lists are never longer than pass-1 ones) |
     //                 active | flags | nnoise | rowbase | rowmap | norm2 | floor2 | skip | Gpart | Q
     const size_t items_bytes = align_up(sizeof(BjItem) * std::max<size_t>(R1.flat.size(), 1), 256);
     const size_t gw_bytes = align_up(sizeof(BjWork) * std::max<size_t>(R1.gworks.size(), 1), 256);
     const size_t aw_bytes = align_up(sizeof(BjWork) * std::max<size_t>(R1.aworks.size(), 1), 256);
     const size_t skip_bytes = align_up(sizeof(int) * std::max<size_t>(R1.max_items, 1), 256);
-    const size_t gpart_bytes = align_up(sizeof(double) * BJ_R * BJ_R * std::max<size_t>(R1.max_gworks, 1), 256);
-    const size_t q_bytes = align_up(sizeof(double) * BJ_R * BJ_R * std::max<size_t>(R1.max_items, 1), 256);
+    const size_t gpart_bytes = align_up(sizeof(double) * BJ_R * BJ_R * CM * std::max<size_t>(R1.max_gworks, 1), 256);
+    const size_t q_bytes = align_up(sizeof(double) * BJ_R * BJ_R * CM * std::max<size_t>(R1.max_items, 1), 256);
     const size_t ints_bytes = align_up(sizeof(int) * nmat, 256);
     const size_t rb_bytes = align_up(sizeof(int) * ((size_t)nbig + 1), 256);
     const size_t map_bytes = align_up(sizeof(int) * std::max<size_t>(nrows, 1), 256);
@@ -657,7 +659,7 @@ static int run_block_jacobi(const void* a, void* o0, double* s_out, void* o2, vo
     CYB_CHECK_CUDA(cudaMemsetAsync(d_floor2, 0, sizeof(double) * nmat, stream));
     const int norm_grid = sm_count() * 4;
     auto sort_rows = [&](int init) {
-        bj_norms_kernel<<<norm_grid, 256, 0, stream>>>(static_cast<const double*>(d_ws), d_desc, sel_big, d_rowbase, nbig, d_norm2);
+        bj_norms_kernel<<<norm_grid, 256, 0, stream>>>(static_cast<const double*>(d_ws), d_desc, sel_big, d_rowbase, nbig, d_norm2, CM);
         bj_sort_kernel<<<nbig, 1024, 0, stream>>>(d_desc, sel_big, d_rowbase, d_norm2, d_rowmap, d_floor2, d_nnoise, d_active, init);
     };
     // runs sweeps over the item lists of R until no item rotates; returns false on a CUDA error
@@ -678,11 +680,11 @@ static int run_block_jacobi(const void* a, void* o0, double* s_out, void* o2, vo
                 if (!live) continue;
                 const unsigned ni = (unsigned)R.rounds[rd].size();
                 const unsigned ng = (unsigned)(R.gstart[rd + 1] - R.gstart[rd]), na = (unsigned)(R.astart[rd + 1] - R.astart[rd]);
-                bj_gram_kernel<<<ng, BJ_THREADS, BJ_SMEM_GRAM, stream>>>(
+                bj_gram_kernel<CX><<<ng, BJ_THREADS, BJ_SMEM_GRAM, stream>>>(
                     static_cast<const double*>(d_ws), d_desc, d_items + R.start[rd], d_gworks + R.gstart[rd], d_active, d_rowmap, d_gpart);
-                bj_rotate_kernel<<<ni, BJ_RT, BJ_SMEM_ROT, stream>>>(
+                bj_rotate_kernel<CX><<<ni, BJ_RT, SMEM_ROT, stream>>>(
                     d_desc, d_items + R.start[rd], d_active, d_flags, d_floor2, phase1 ? 1 : 0, d_gpart, d_qbuf, d_skip);
-                bj_apply_kernel<<<na, BJ_THREADS, BJ_SMEM_APPLY, stream>>>(
+                bj_apply_kernel<CX><<<na, BJ_THREADS, SMEM_APPLY, stream>>>(
                     static_cast<double*>(d_ws), d_desc, d_items + R.start[rd], d_aworks + R.astart[rd], d_rowmap, d_qbuf, d_skip);
             }
             CYB_LAUNCH_CHECK();
@@ -719,11 +721,11 @@ static int run_block_jacobi(const void* a, void* o0, double* s_out, void* o2, vo
             active[(size_t)mat] = nn > 1;
             first_block[(size_t)q] = nn > 1 ? (int)((r - nn) / BJ_B) : (int)((r + BJ_B - 1) / BJ_B);
         }
-        bj_build_rounds(R2, descs, big, rowbase, first_block);
+        bj_build_rounds(R2, descs, big, rowbase, first_block, CM);
         rc = run_sweeps(R2, false);
         if (rc != CYB_OK) return rc;
     }
-    err = launch_team(jacobi_svd_kernel<false, FZ_BIG_G, EIGH, PH_FINISH>, FZ_BIG_G, nbig, stream,
+    err = launch_team(jacobi_svd_kernel<CX, FZ_BIG_G, EIGH, PH_FINISH>, FZ_BIG_G, nbig, stream,
                       a, o0, s_out, o2, d_ws, d_aux, d_desc, sel_big, info);
     if (err != cudaSuccess) { set_error("block jacobi: output launch failed: %s", cudaGetErrorString(err)); return CYB_ERR_CUDA; }
     // info: sweeps used (negative: not converged within FZ_MAX_SWEEPS)
@@ -793,11 +795,13 @@ static int run_factorize(FzKind kind, const void* a, void* o0, double* o1d, void
     cudaError_t err = cudaSuccess;
 #define FZ_LAUNCH(KERN, G, NT, ...) \
     do { if ((NT) > 0) { err = launch_team(KERN, G, (int)(NT), stream, __VA_ARGS__); if (err != cudaSuccess) { set_error("factorize launch failed: %s", cudaGetErrorString(err)); return CYB_ERR_CUDA; } } } while (0)
-    if (!cx && kind != FZ_QR && !big.empty()) {
-        // large real sectors: block Jacobi (block_jacobi.cuh) between the load and the output phases
+    if (kind != FZ_QR && !big.empty()) {
+        // large sectors: block Jacobi (block_jacobi.cuh) between the load and the output phases
         const int rc = (kind == FZ_EIGH)
-            ? run_block_jacobi<true>(a, o0, o1d, o2, d_ws, d_aux, d_desc, descs, big, sel_big, info, stream)
-            : run_block_jacobi<false>(a, o0, o1d, o2, d_ws, d_aux, d_desc, descs, big, sel_big, info, stream);
+            ? (cx ? run_block_jacobi<true, true>(a, o0, o1d, o2, d_ws, d_aux, d_desc, descs, big, sel_big, info, stream)
+                  : run_block_jacobi<true, false>(a, o0, o1d, o2, d_ws, d_aux, d_desc, descs, big, sel_big, info, stream))
+            : (cx ? run_block_jacobi<false, true>(a, o0, o1d, o2, d_ws, d_aux, d_desc, descs, big, sel_big, info, stream)
+                  : run_block_jacobi<false, false>(a, o0, o1d, o2, d_ws, d_aux, d_desc, descs, big, sel_big, info, stream));
         if (rc != CYB_OK) return rc;
         big.clear();
     }

@@ -79,6 +79,18 @@ __host__ __device__ __forceinline__ int64_t sk_units(int64_t M, int64_t N, int64
     return (M > 0 && M <= SK_MAXM && N > 0) ? (N + ucols - 1) / ucols : 0;
 }
 
+// Unit width of a streaming block: a unit moves ucols * (J + M) doubles (J rows of B read, M rows of C
+// written), so the width is chosen per block such that every unit carries about `target` doubles --
+// units of equal cost, handed out by an atomic ticket, keep all CTAs busy until the end.
+__host__ __device__ __forceinline__ int64_t sk_ucols(int64_t target, int64_t J, int64_t M)
+{
+    const int64_t rows = J + M > 0 ? J + M : 1;
+    int64_t u = (target / rows + SK_CHUNK - 1) / SK_CHUNK * SK_CHUNK;
+    if (u < SK_CHUNK) u = SK_CHUNK;
+    if (u > 64 * SK_CHUNK) u = 64 * SK_CHUNK;
+    return u;
+}
+
 // single CTA: cost-sorted processing order, tile prefix, ticket reset.
 // SKINNY = false: tiles of the DMMA kernel (blocks with M > SK_MAXM); true: column chunks of the
 // streaming kernel (blocks with M <= SK_MAXM).
@@ -97,8 +109,7 @@ __global__ void __launch_bounds__(1024) gemm_schedule_kernel(const int64_t* __re
     __shared__ int64_t s_target;
     const int tid = threadIdx.x;
     if (SKINNY) {
-        // unit width of the streaming kernel: all skinny columns / target_units, rounded up to whole
-        // SK_CHUNKs: long enough to amortise the per-unit table lookups, short enough to balance the grid
+        // doubles moved by all streaming blocks / target_units = doubles per unit (see sk_ucols)
         int64_t carry = 0;
         for (int64_t base = 0; base < nblocks; base += 1024) {
             const int64_t i = base + tid;
@@ -106,7 +117,11 @@ __global__ void __launch_bounds__(1024) gemm_schedule_kernel(const int64_t* __re
             if (i < nblocks) {
                 const int64_t blk = subset ? subset[i] : i;
                 const int64_t M = out_mn[2 * blk], N = out_mn[2 * blk + 1];
-                v = (M > 0 && M <= SK_MAXM && N > 0) ? N : 0;
+                if (M > 0 && M <= SK_MAXM && N > 0) {
+                    int64_t J = 0;
+                    for (int64_t q = out_pair_ptr[blk]; q < out_pair_ptr[blk + 1]; ++q) J += pairs[3 * q + 2];
+                    v = N * (J + M);
+                }
             }
             int64_t total;
             block_exclusive_scan<int64_t>(v, s_scan, &total);
@@ -114,7 +129,7 @@ __global__ void __launch_bounds__(1024) gemm_schedule_kernel(const int64_t* __re
         }
         if (tid == 0) {
             const int64_t t = (carry + target_units - 1) / (target_units > 0 ? target_units : 1);
-            s_target = ((t > SK_CHUNK ? t : SK_CHUNK) + SK_CHUNK - 1) / SK_CHUNK * SK_CHUNK;
+            s_target = t > SK_CHUNK ? t : SK_CHUNK;
         }
         __syncthreads();
     }
@@ -122,7 +137,7 @@ __global__ void __launch_bounds__(1024) gemm_schedule_kernel(const int64_t* __re
         const int64_t blk = subset ? subset[i] : i;
         double ksum = 0;
         for (int64_t q = out_pair_ptr[blk]; q < out_pair_ptr[blk + 1]; ++q) ksum += (double)pairs[3 * q + 2];
-        const int64_t nt = SKINNY ? sk_units(out_mn[2 * blk], out_mn[2 * blk + 1], s_target)
+        const int64_t nt = SKINNY ? sk_units(out_mn[2 * blk], out_mn[2 * blk + 1], sk_ucols(s_target, (int64_t)ksum, out_mn[2 * blk]))
                                   : n_units<BM, BN, SKINNY>(out_mn[2 * blk], out_mn[2 * blk + 1]);
         // per-tile cost decides the order (long k-loops first), ties keep table order
         cost[i] = (nt > 0) ? ksum : -1.0;
@@ -144,8 +159,11 @@ __global__ void __launch_bounds__(1024) gemm_schedule_kernel(const int64_t* __re
         int64_t v = 0;
         if (i < nblocks) {
             const int64_t blk = order[i];
-            v = SKINNY ? sk_units(out_mn[2 * blk], out_mn[2 * blk + 1], s_target)
-                       : n_units<BM, BN, SKINNY>(out_mn[2 * blk], out_mn[2 * blk + 1]);
+            if (SKINNY) {
+                int64_t J = 0;
+                for (int64_t q = out_pair_ptr[blk]; q < out_pair_ptr[blk + 1]; ++q) J += pairs[3 * q + 2];
+                v = sk_units(out_mn[2 * blk], out_mn[2 * blk + 1], sk_ucols(s_target, J, out_mn[2 * blk]));
+            } else v = n_units<BM, BN, SKINNY>(out_mn[2 * blk], out_mn[2 * blk + 1]);
         }
         int64_t total;
         int64_t pos = block_exclusive_scan<int64_t>(v, s_scan, &total);
@@ -154,7 +172,8 @@ __global__ void __launch_bounds__(1024) gemm_schedule_kernel(const int64_t* __re
     }
     if (tid == 0) {
         tile_start[nblocks] = carry;
-        *ticket = SKINNY ? (unsigned long long)s_target : 0ull;   // the streaming kernel reads its unit width here
+        *ticket = SKINNY ? (unsigned long long)s_target : 0ull;   // the streaming kernel reads its doubles-per-unit target here
+        if (SKINNY) ticket[1] = 0ull;                             // ... and draws its units from this counter
     }
 }
 
@@ -498,86 +517,131 @@ __device__ __forceinline__ void skinny_unit(const double* __restrict__ A, const 
 // its RB * W / 2 16-byte loads back to back, then does the FMAs with coefficients broadcast from shared memory.
 constexpr int SK_J = 64;     // rows the tables hold; blocks with more rows take the generic path
 
-template <bool CPLX, int W, int MM>
-__device__ __noinline__ void skinny_rows(const double* __restrict__ B, double* __restrict__ Cb,
-                                            const int64_t* s_row, const double* s_coef, int J, int M,
-                                            int64_t N, int64_t n)
+// Streaming loop of the fast path.  Every thread owns CW adjacent columns at each of the unit's column
+// positions (stride PS) and a PRIVATE ring of SK_RING 16-byte slots in shared memory that it fills with
+// cp.async: a step = SR table rows of one position, D = SK_RING / SR steps are in flight per thread (up to
+// 256 bytes, 768 threads per SM), independent of how few rows J a block has -- with plain loads a block
+// with J = 1 .. 4 rows kept only J * 16 bytes per thread in flight and the kernel sat at 30 % of HBM speed.
+// Nobody else reads a thread's slots, so there is no barrier in the loop, only cp.async.wait_group.
+constexpr int SK_RING = 16;
+constexpr size_t SK_SMEM_RING = (size_t)SK_RING * SK_THREADS * 16;
+
+__device__ __forceinline__ void sk_cp(void* smem, const void* g, int bytes, bool pred)
 {
-    constexpr int ES = CPLX ? 2 : 1;
-    constexpr int RB = 8;   // rows in flight per thread: 8 x 16 bytes
-    double acc[MM][W];
-#pragma unroll
-    for (int m = 0; m < MM; ++m)
-#pragma unroll
-        for (int w = 0; w < W; ++w) acc[m][w] = 0.0;
-    for (int j0 = 0; j0 < J; j0 += RB) {
-        double b[RB][W];
-#pragma unroll
-        for (int r = 0; r < RB; ++r) {
-            if (j0 + r < J) {
-                const double* row = B + (s_row[j0 + r] + n) * ES;
-                if (W == 1) b[r][0] = __ldcs(row);
-                else {
-#pragma unroll
-                    for (int w = 0; w < W; w += 2) {
-                        const double2 t = __ldcs(reinterpret_cast<const double2*>(row + w));
-                        b[r][w] = t.x; b[r][w + 1 < W ? w + 1 : w] = t.y;
-                    }
-                }
-            } else {
-#pragma unroll
-                for (int w = 0; w < W; ++w) b[r][w] = 0.0;
-            }
-        }
-#pragma unroll
-        for (int r = 0; r < RB; ++r) {
-            const int jj = (j0 + r < J) ? j0 + r : J - 1;   // b is zero beyond J
-#pragma unroll
-            for (int m = 0; m < MM; ++m) {
-                if (m < M) {
-                    if (!CPLX) {
-                        const double a = s_coef[m * SK_J + jj];
-#pragma unroll
-                        for (int w = 0; w < W; ++w) acc[m][w] = fma(a, b[r][w], acc[m][w]);
-                    } else {
-                        const double ax = s_coef[(m * SK_J + jj) * 2], ay = s_coef[(m * SK_J + jj) * 2 + 1];
-#pragma unroll
-                        for (int w = 0; w < W; w += 2) {
-                            acc[m][w] = fma(ax, b[r][w], fma(-ay, b[r][w + 1], acc[m][w]));
-                            acc[m][w + 1] = fma(ax, b[r][w + 1], fma(ay, b[r][w], acc[m][w + 1]));
-                        }
-                    }
-                }
-            }
-        }
-    }
-#pragma unroll
-    for (int m = 0; m < MM; ++m) {
-        if (m < M) {
-            double* c = Cb + ((int64_t)m * N + n) * ES;
-            if (W == 1) __stcs(c, acc[m][0]);
-            else {
-#pragma unroll
-                for (int w = 0; w < W; w += 2) __stcs(reinterpret_cast<double2*>(c + w), make_double2(acc[m][w], acc[m][w + 1]));
-            }
-        }
-    }
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+    const int sz = pred ? bytes : 0;
+    if (bytes == 16) asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(sa), "l"(g), "r"(sz) : "memory");
+    else asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" ::"r"(sa), "l"(g), "r"(sz) : "memory");
 }
 
-template <bool CPLX, int W>
-__device__ __forceinline__ void skinny_rows_m(const double* __restrict__ B, double* __restrict__ Cb,
-                                              const int64_t* s_row, const double* s_coef, int J, int M,
-                                              int64_t N, int64_t n)
+// CPLX: one complex element per slot; real: VEC2 ? two columns (16-byte slot) : one column (8-byte slot)
+template <bool CPLX, bool VEC2, int MM, int SR>
+__device__ __noinline__ void skinny_stream(const double* __restrict__ B, double* __restrict__ Cb,
+                                           const int64_t* s_row, const double* s_coef, double2* ring,
+                                           int J, int64_t N, int64_t c0, int npos)
 {
-    if (M <= SK_MAXM / 2) skinny_rows<CPLX, W, SK_MAXM / 2>(B, Cb, s_row, s_coef, J, M, N, n);
-    else if (W == 4) {      // 8 rows x 4 columns of accumulators would spill
-        skinny_rows<CPLX, 2, SK_MAXM>(B, Cb, s_row, s_coef, J, M, N, n);
-        skinny_rows<CPLX, 2, SK_MAXM>(B, Cb, s_row, s_coef, J, M, N, n + 2);
-    } else skinny_rows<CPLX, W, SK_MAXM>(B, Cb, s_row, s_coef, J, M, N, n);
+    constexpr int D = SK_RING / SR;                 // steps in flight
+    constexpr int CW = (!CPLX && VEC2) ? 2 : 1;     // columns per thread per position
+    constexpr int SB = (CPLX || VEC2) ? 16 : 8;     // bytes per slot
+    constexpr int ES = CPLX ? 2 : 1;
+    constexpr int W = CPLX ? 2 : CW;                // doubles per slot
+    const int tid = threadIdx.x;
+    const int nb = (J + SR - 1) / SR;               // steps per position
+    const int nsteps = npos * nb;
+    const int64_t n0 = c0 + (int64_t)tid * CW;
+    double2* my = ring + tid;                       // slot q of this thread: my[q * SK_THREADS]
+    auto issue = [&](int step) {
+        if (step < nsteps) {
+            const int pos = step / nb, bt = step - pos * nb;
+            const int64_t n = n0 + (int64_t)pos * (SK_THREADS * CW);
+            const bool inb = n < N;
+#pragma unroll
+            for (int r = 0; r < SR; ++r) {
+                const int j = bt * SR + r;
+                const bool ok = inb && j < J;
+                const double* src = ok ? B + (s_row[j] + n) * ES : B;
+                sk_cp(my + ((step % D) * SR + r) * SK_THREADS, src, SB, ok);
+            }
+        }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+#pragma unroll 1
+    for (int st = 0; st < D - 1; ++st) issue(st);
+    double acc[MM][W];
+#pragma unroll 1
+    for (int step = 0; step < nsteps; ++step) {
+        issue(step + D - 1);
+        asm volatile("cp.async.wait_group %0;\n" ::"n"(D - 1) : "memory");
+        const int pos = step / nb, bt = step - pos * nb;
+        if (bt == 0) {
+#pragma unroll
+            for (int m = 0; m < MM; ++m)
+#pragma unroll
+                for (int w = 0; w < W; ++w) acc[m][w] = 0.0;
+        }
+#pragma unroll
+        for (int r = 0; r < SR; ++r) {
+            const int j = bt * SR + r;          // slots beyond J were zero-filled
+            const int jj = j < J ? j : J - 1;
+            const double2 t = my[((step % D) * SR + r) * SK_THREADS];
+#pragma unroll
+            for (int m = 0; m < MM; ++m) {
+                if (!CPLX) {
+                    const double a = s_coef[m * SK_J + jj];
+                    acc[m][0] = fma(a, t.x, acc[m][0]);
+                    if (W == 2) acc[m][W - 1] = fma(a, t.y, acc[m][W - 1]);
+                } else {
+                    const double ax = s_coef[(m * SK_J + jj) * 2], ay = s_coef[(m * SK_J + jj) * 2 + 1];
+                    acc[m][0] = fma(ax, t.x, fma(-ay, t.y, acc[m][0]));
+                    acc[m][W - 1] = fma(ax, t.y, fma(ay, t.x, acc[m][W - 1]));
+                }
+            }
+        }
+        if (bt == nb - 1) {
+            const int64_t n = n0 + (int64_t)pos * (SK_THREADS * CW);
+            if (n < N) {
+#pragma unroll
+                for (int m = 0; m < MM; ++m) {
+                    double* c = Cb + ((int64_t)m * N + n) * ES;
+                    if (W == 1) __stcs(c, acc[m][0]);
+                    else __stcs(reinterpret_cast<double2*>(c), make_double2(acc[m][0], acc[m][W - 1]));
+                }
+            }
+        }
+    }
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+}
+
+template <bool CPLX, bool VEC2, int MM>
+__device__ __forceinline__ void skinny_stream_sr(const double* __restrict__ B, double* __restrict__ Cb,
+                                                 const int64_t* s_row, const double* s_coef, double2* ring,
+                                                 int J, int64_t N, int64_t c0, int npos)
+{
+    if (J == 1) skinny_stream<CPLX, VEC2, MM, 1>(B, Cb, s_row, s_coef, ring, J, N, c0, npos);
+    else if (J == 2) skinny_stream<CPLX, VEC2, MM, 2>(B, Cb, s_row, s_coef, ring, J, N, c0, npos);
+    else if (J <= 4) skinny_stream<CPLX, VEC2, MM, 4>(B, Cb, s_row, s_coef, ring, J, N, c0, npos);
+    else skinny_stream<CPLX, VEC2, MM, 8>(B, Cb, s_row, s_coef, ring, J, N, c0, npos);
+}
+
+template <bool CPLX, bool VEC2>
+__device__ __forceinline__ void skinny_stream_m(const double* __restrict__ B, double* __restrict__ Cb,
+                                                const int64_t* s_row, const double* s_coef, double2* ring,
+                                                int J, int M, int64_t N, int64_t c0, int npos)
+{
+    switch (M) {   // uniform over the CTA
+    case 1: skinny_stream_sr<CPLX, VEC2, 1>(B, Cb, s_row, s_coef, ring, J, N, c0, npos); break;
+    case 2: skinny_stream_sr<CPLX, VEC2, 2>(B, Cb, s_row, s_coef, ring, J, N, c0, npos); break;
+    case 3: skinny_stream_sr<CPLX, VEC2, 3>(B, Cb, s_row, s_coef, ring, J, N, c0, npos); break;
+    case 4: skinny_stream_sr<CPLX, VEC2, 4>(B, Cb, s_row, s_coef, ring, J, N, c0, npos); break;
+    case 5: skinny_stream_sr<CPLX, VEC2, 5>(B, Cb, s_row, s_coef, ring, J, N, c0, npos); break;
+    case 6: skinny_stream_sr<CPLX, VEC2, 6>(B, Cb, s_row, s_coef, ring, J, N, c0, npos); break;
+    case 7: skinny_stream_sr<CPLX, VEC2, 7>(B, Cb, s_row, s_coef, ring, J, N, c0, npos); break;
+    default: skinny_stream_sr<CPLX, VEC2, 8>(B, Cb, s_row, s_coef, ring, J, N, c0, npos); break;
+    }
 }
 
 template <bool CPLX>
-__global__ void __launch_bounds__(SK_THREADS, 4) skinny_gemm_kernel(const double* __restrict__ A,
+__global__ void __launch_bounds__(SK_THREADS, 3) skinny_gemm_kernel(const double* __restrict__ A,
                                                                  const double* __restrict__ B,
                                                                  double* __restrict__ C, GemmTables T)
 {
@@ -585,19 +649,28 @@ __global__ void __launch_bounds__(SK_THREADS, 4) skinny_gemm_kernel(const double
     // global loads per unit would cost as much as streaming the unit)
     constexpr int SK_CACHE = 1024;
     constexpr int ES = CPLX ? 2 : 1;
+    constexpr int SK_PMAX = 32;                 // pairs the fast path handles
     __shared__ int64_t s_start[SK_CACHE + 1];
     __shared__ int64_t s_row[SK_J];
     __shared__ double s_coef[SK_MAXM * SK_J * ES];
+    __shared__ int64_t s_pa[SK_PMAX], s_pb[SK_PMAX];
+    __shared__ int s_pk[SK_PMAX], s_pj[SK_PMAX + 1];
     __shared__ int s_J;
+    __shared__ long long s_unit;
+    extern __shared__ __align__(16) double2 ring[];   // SK_RING x SK_THREADS private slots
     const bool cached = T.nblocks <= SK_CACHE;
     if (cached) for (int64_t i = threadIdx.x; i <= T.nblocks; i += SK_THREADS) s_start[i] = T.tile_start[i];
     __syncthreads();
     const int64_t* start = cached ? s_start : T.tile_start;
     const int64_t total_units = start[T.nblocks];
-    const int64_t ucols = (int64_t)*T.ticket;   // unit width chosen by the schedule kernel
-    const int npass = (int)(ucols / SK_CHUNK);
+    const int64_t target = (int64_t)T.ticket[0];   // doubles per unit chosen by the schedule kernel
     const int lane = threadIdx.x & 31;
-    for (int64_t unit = blockIdx.x; unit < total_units; unit += gridDim.x) {
+    for (;;) {
+        __syncthreads();                            // the previous unit is done with the tables
+        if (threadIdx.x == 0) s_unit = (long long)atomicAdd(T.ticket + 1, 1ull);
+        __syncthreads();
+        const int64_t unit = s_unit;
+        if (unit >= total_units) break;
         int64_t lo = 0, hi = T.nblocks;
         while (hi - lo > 1) {
             const int64_t mid = (lo + hi) >> 1;
@@ -606,16 +679,14 @@ __global__ void __launch_bounds__(SK_THREADS, 4) skinny_gemm_kernel(const double
         const int64_t blk = T.order[lo];
         const int M = (int)T.out_mn[2 * blk];
         const int64_t N = T.out_mn[2 * blk + 1];
-        const int64_t u0 = (unit - start[lo]) * ucols;
         const int64_t p_begin = T.out_pair_ptr[blk], p_end = T.out_pair_ptr[blk + 1];
         double* Cb = C + T.out_off[blk] * ES;
         const bool vec2 = !CPLX && (N & 1) == 0;   // real with even N: rows stay 16-byte aligned
-        // ---- row / coefficient tables of this block (warp 0) ----
-        __syncthreads();                            // the previous unit is done with the tables
+        // ---- pair table (warp 0), then row / coefficient tables (all threads) ----
+        const int np = (int)(p_end - p_begin);
         if (threadIdx.x < 32) {
-            const int np = (int)(p_end - p_begin);
             int J = SK_J + 1;
-            if (np <= 32) {
+            if (np <= SK_PMAX) {
                 int64_t a_off = 0, b_off = 0;
                 int K = 0;
                 if (lane < np) {
@@ -629,44 +700,53 @@ __global__ void __launch_bounds__(SK_THREADS, 4) skinny_gemm_kernel(const double
                     if (lane >= d) incl += o;
                 }
                 J = __shfl_sync(0xffffffffu, incl, 31);
-                if (J <= SK_J) {
-                    const int j0 = incl - K;
-                    for (int k = 0; k < K; ++k) {
-                        s_row[j0 + k] = b_off + (int64_t)k * N;
-                        for (int m = 0; m < M; ++m) {
-                            if (!CPLX) s_coef[m * SK_J + j0 + k] = __ldg(A + a_off + m * K + k);
-                            else {
-                                const double2 v = __ldg(reinterpret_cast<const double2*>(A) + a_off + m * K + k);
-                                s_coef[(m * SK_J + j0 + k) * 2] = v.x;
-                                s_coef[(m * SK_J + j0 + k) * 2 + 1] = v.y;
-                            }
-                        }
-                    }
-                }
+                s_pa[lane] = a_off; s_pb[lane] = b_off; s_pk[lane] = K; s_pj[lane] = incl - K;
             }
             if (lane == 0) s_J = J;
         }
         __syncthreads();
         const int J = s_J;
         const bool fast = J <= SK_J;
+        if (fast) {
+            for (int idx = threadIdx.x; idx < J * (M + 1); idx += SK_THREADS) {
+                const int j = idx % J, m = idx / J;
+                int pi = 0;
+                while (pi + 1 < np && s_pj[pi + 1] <= j) ++pi;
+                const int k = j - s_pj[pi], K = s_pk[pi];
+                if (m == M) s_row[j] = s_pb[pi] + (int64_t)k * N;
+                else if (!CPLX) s_coef[m * SK_J + j] = __ldg(A + s_pa[pi] + m * K + k);
+                else {
+                    const double2 v = __ldg(reinterpret_cast<const double2*>(A) + s_pa[pi] + m * K + k);
+                    s_coef[(m * SK_J + j) * 2] = v.x;
+                    s_coef[(m * SK_J + j) * 2 + 1] = v.y;
+                }
+            }
+        }
+        __syncthreads();
+        int64_t Jtot = J;
+        if (!fast) { Jtot = 0; for (int64_t q = p_begin; q < p_end; ++q) Jtot += T.pairs[3 * q + 2]; }
+        const int64_t ucols = sk_ucols(target, Jtot, M);
+        const int npass = (int)(ucols / SK_CHUNK);
+        const int64_t u0 = (unit - start[lo]) * ucols;
+        if (fast) {
+            // column positions of this unit that start inside the block
+            const int64_t cols = (N - u0 < ucols) ? N - u0 : ucols;
+            if (vec2) skinny_stream_m<CPLX, true>(B, Cb, s_row, s_coef, ring, J, M, N, u0, (int)((cols + SK_CHUNK - 1) / SK_CHUNK));
+            else skinny_stream_m<CPLX, false>(B, Cb, s_row, s_coef, ring, J, M, N, u0, (int)((cols + SK_THREADS - 1) / SK_THREADS));
+            continue;
+        }
 #pragma unroll 1
         for (int pass = 0; pass < npass; ++pass) {
             const int64_t c0 = u0 + (int64_t)pass * SK_CHUNK;
             if (c0 >= N) break;
             if (vec2) {
                 const int64_t n = c0 + (int64_t)threadIdx.x * 2;
-                if (n < N) {
-                    if (fast) skinny_rows_m<CPLX, 2>(B, Cb, s_row, s_coef, J, M, N, n);
-                    else skinny_unit<CPLX, CPLX ? 1 : 2>(A, B, Cb, T.pairs, p_begin, p_end, M, N, n);
-                }
+                if (n < N) skinny_unit<CPLX, CPLX ? 1 : 2>(A, B, Cb, T.pairs, p_begin, p_end, M, N, n);
             } else {
 #pragma unroll 1
                 for (int h = 0; h < 2; ++h) {
                     const int64_t n = c0 + threadIdx.x + h * SK_THREADS;
-                    if (n < N) {
-                        if (fast) skinny_rows_m<CPLX, CPLX ? 2 : 1>(B, Cb, s_row, s_coef, J, M, N, n);
-                        else skinny_unit<CPLX, 1>(A, B, Cb, T.pairs, p_begin, p_end, M, N, n);
-                    }
+                    if (n < N) skinny_unit<CPLX, 1>(A, B, Cb, T.pairs, p_begin, p_end, M, N, n);
                 }
             }
         }
@@ -753,8 +833,8 @@ int cyb_grouped_gemm_prepare(int dtype, const int64_t* out_mn, const int64_t* ou
     double* cost[2];
     gemm_tables(T, cost, out_mn, nullptr, out_pair_ptr, pairs, nblocks, workspace);
     // streaming kernel: aim at SK_UNITS_PER_SLOT work units per resident CTA (3 per SM)
-    static const int ups = [] { const char* e = getenv("CYB_SK_UNITS_PER_SLOT"); return e ? atoi(e) : 4; }();
-    const int64_t sk_target = (int64_t)sm_count() * 4 * ups;
+    static const int ups = [] { const char* e = getenv("CYB_SK_UNITS_PER_SLOT"); return e ? atoi(e) : 8; }();
+    const int64_t sk_target = (int64_t)sm_count() * 3 * ups;
     if (dtype == CYB_F64) {
         const int v = gemm_variant();
         if (v == 10 || v == 12)
@@ -788,12 +868,19 @@ int cyb_grouped_gemm_run(const void* a, const void* b, void* c, int dtype, const
     gemm_tables(T, cost, out_mn, out_off, out_pair_ptr, pairs, nblocks, workspace);
     // the dynamic tile counter of the persistent DMMA kernel starts at 0 for every run
     CYB_CHECK_CUDA(cudaMemsetAsync(T[0].ticket, 0, sizeof(unsigned long long), stream));
+    CYB_CHECK_CUDA(cudaMemsetAsync(T[1].ticket + 1, 0, sizeof(unsigned long long), stream));   // unit counter of the streaming kernel
     const double* A = static_cast<const double*>(a);
     const double* B = static_cast<const double*>(b);
     double* C = static_cast<double*>(c);
-    const int sk_grid = sm_count() * 8;
+    static bool sk_configured = false;
+    if (!sk_configured) {
+        CYB_CHECK_CUDA(cudaFuncSetAttribute(skinny_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SK_SMEM_RING));
+        CYB_CHECK_CUDA(cudaFuncSetAttribute(skinny_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SK_SMEM_RING));
+        sk_configured = true;
+    }
+    const int sk_grid = sm_count() * 3;   // resident CTAs; units are drawn from an atomic ticket
     if (dtype == CYB_F64) {
-        skinny_gemm_kernel<false><<<sk_grid, SK_THREADS, 0, stream>>>(A, B, C, T[1]);
+        skinny_gemm_kernel<false><<<sk_grid, SK_THREADS, SK_SMEM_RING, stream>>>(A, B, C, T[1]);
         CYB_LAUNCH_CHECK();
         switch (gemm_variant()) {
             case 0: return launch_gemm<CfgR0>(a, b, c, T[0], stream);
@@ -811,7 +898,7 @@ int cyb_grouped_gemm_run(const void* a, const void* b, void* c, int dtype, const
             default: return launch_gemm<CfgR>(a, b, c, T[0], stream);
         }
     }
-    skinny_gemm_kernel<true><<<sk_grid, SK_THREADS, 0, stream>>>(A, B, C, T[1]);
+    skinny_gemm_kernel<true><<<sk_grid, SK_THREADS, SK_SMEM_RING, stream>>>(A, B, C, T[1]);
     CYB_LAUNCH_CHECK();
     return launch_gemm<CfgC>(a, b, c, T[0], stream);
 }
