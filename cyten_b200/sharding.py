@@ -107,10 +107,37 @@ def sector_owner_of_leg(T: SymmetricTensor, leg, world: int):
     return ax, lpt_assign(cost, world), cost
 
 
-def shard_by_leg(T: SymmetricTensor, leg, pg: ProcessGroup):
+def flop_costs_of_leg(T: SymmetricTensor, leg, chain) -> np.ndarray:
+    """Flops that every sector of ``leg`` causes in ``chain(T_part)`` (a callable running the downstream
+    contractions): a plan-only pass (``dry_run``: integer bookkeeping on the device, no arena is touched,
+    nothing is cached) per sector, summing ``M*K*N`` over the matrix_dot lists of its composes.  This is
+    the "flop-cost" of the LPT assignment; block volume alone underestimates the
+    central sectors, whose blocks meet the largest partners."""
+    be = T.backend
+    ax = T.get_leg_idcs([leg])[0]
+    nsec = conventional_leg_order(T.codomain, T.domain)[ax].num_sectors
+    saved = (be.dry_run, be.plan_cache, be.plan_mkn)
+    costs = np.zeros(nsec, dtype=np.float64)
+    be.dry_run, be.plan_cache = True, False
+    try:
+        for s in range(nsec):
+            mine = np.nonzero(T.data.block_inds[:, ax] == s)[0]
+            if len(mine) == 0:
+                continue
+            be.plan_mkn = []
+            chain(take_blocks(T, mine))
+            costs[s] = float(sum(be.plan_mkn))
+    finally:
+        be.dry_run, be.plan_cache, be.plan_mkn = saved
+    return costs
+
+
+def shard_by_leg(T: SymmetricTensor, leg, pg: ProcessGroup, costs=None):
     """Rank-local part of T: the blocks whose sector on ``leg`` is owned by this rank.
     Returns (local tensor, owner table of the leg's sectors)."""
     ax, owner, _ = sector_owner_of_leg(T, leg, pg.world)
+    if costs is not None:
+        owner = lpt_assign(np.asarray(costs, dtype=np.float64), pg.world)
     mine = np.nonzero(owner[T.data.block_inds[:, ax]] == pg.rank)[0]
     return take_blocks(T, mine), owner
 
@@ -119,6 +146,14 @@ def expand_to_full(T: SymmetricTensor) -> SymmetricTensor:
     """T re-laid-out on the arena of ALL symmetry-allowed blocks (valid_block_inds,
     abelian.cpp:329-399), absent blocks zero: the layout every rank shares."""
     be = T.backend
+    # structure-only bookkeeping: cached like every other plan (one zero-fill + one copy launch per call)
+    key = ("expand_full", T.data.sig, T.codomain.sig, T.domain.sig)
+    plan = be._plan_get(key)
+    if plan is not None:
+        res = be._empty(T.data.dtype, be.device, plan["bi"], plan["shapes"], zero=True)
+        res._sig = plan["sig"]
+        be._run_copy(T.data.buf, res.buf, plan["copy"], T.data.cyb_dtype)
+        return SymmetricTensor(res, T.codomain, T.domain, be, T.labels)
     full_bi = valid_block_inds(T.codomain, T.domain)
     legs = conventional_leg_order(T.codomain, T.domain)
     shapes = (np.stack([np.asarray(l.multiplicities)[full_bi[:, ax]] for ax, l in enumerate(legs)], axis=1)
@@ -136,7 +171,9 @@ def expand_to_full(T: SymmetricTensor) -> SymmetricTensor:
         sizes = d.sizes.reshape(-1, 1)
         ones = np.ones_like(sizes)
         jobs = be._make_jobs(d.offsets, res.offsets[pos], sizes, ones, ones)
-        be._copy_blocks(d.buf, res.buf, jobs, d.cyb_dtype)
+        prepared = be._prepare_copy(jobs)
+        be._run_copy(d.buf, res.buf, prepared, d.cyb_dtype)
+        be._plan_put(key, dict(bi=full_bi, shapes=shapes, copy=prepared, sig=res.sig))
     return SymmetricTensor(res, T.codomain, T.domain, be, T.labels)
 
 
@@ -175,7 +212,13 @@ class ShardedHEffective:
         self.H, self.pg, self.shard_leg = H, pg, shard_leg
 
     def shard(self, theta: SymmetricTensor) -> SymmetricTensor:
-        return shard_by_leg(theta, self.shard_leg, self.pg)[0]
+        """Rank-local part of theta: sectors of ``shard_leg`` assigned by LPT on the flops each sector
+        causes in the matvec chain (identical on every rank: pure integer bookkeeping)."""
+        if self.pg.world == 1:
+            return theta
+        costs = flop_costs_of_leg(theta, self.shard_leg, self.H.matvec)
+        self.costs = costs
+        return shard_by_leg(theta, self.shard_leg, self.pg, costs=costs)[0]
 
     def matvec_local(self, theta_local: SymmetricTensor) -> SymmetricTensor:
         return self.H.matvec(theta_local)

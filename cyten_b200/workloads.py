@@ -8,7 +8,7 @@ from __future__ import annotations
 
 import numpy as np
 
-from .spaces import ElementarySpace, TensorProduct, u1_symmetry
+from .spaces import AbelianSymmetry, ElementarySpace, TensorProduct, u1_symmetry
 from .tensors import SymmetricTensor
 
 CONFIG_LEGS = {128: (3, 1.2), 1024: (6, 2.2), 4096: (9, 3.2), 16384: (12, 4.4)}
@@ -30,6 +30,30 @@ def u1_phys_leg(is_dual: bool = False) -> ElementarySpace:
 
 def u1_mpo_leg(is_dual: bool = False) -> ElementarySpace:
     return ElementarySpace(u1_symmetry, [[-2], [0], [2]], [1, 3, 1], is_dual)
+
+
+# ---- Fermi-Hubbard legs, U(1) x U(1) = (charge N, 2 Sz): BASELINE config 4 / SURVEY section 8(d) ----
+u1u1_symmetry = AbelianSymmetry((0, 0))
+
+
+def hubbard_bond_leg(chi: int, Q: int = 6, sigma=(2.0, 2.0), is_dual: bool = False) -> ElementarySpace:
+    """2-D Gaussian multiplicities over (N, 2Sz) in [-Q, Q]^2 with N + 2Sz even (N fermions have 2Sz of
+    the same parity), ``m = max(1, floor(chi g / sum g))``, remainder added to (0, 0): many small
+    irregular blocks."""
+    qs = [(n, s) for n in range(-Q, Q + 1) for s in range(-Q, Q + 1) if (n + s) % 2 == 0]
+    q = np.asarray(qs, dtype=np.int64)
+    g = np.exp(-q[:, 0].astype(float) ** 2 / (2 * sigma[0] ** 2) - q[:, 1].astype(float) ** 2 / (2 * sigma[1] ** 2))
+    m = np.maximum(1, np.floor(chi * g / g.sum()).astype(np.int64))
+    i0 = qs.index((0, 0))
+    m[i0] += chi - int(m.sum())
+    if m[i0] < 1:
+        raise ValueError("chi too small for this (Q, sigma)")
+    return ElementarySpace.from_defining_sectors(u1u1_symmetry, q, m, is_dual)
+
+
+def hubbard_phys_leg(is_dual: bool = False) -> ElementarySpace:
+    """d = 4: (N, 2Sz) in {(0,0), (1,1), (1,-1), (2,0)}."""
+    return ElementarySpace.from_defining_sectors(u1u1_symmetry, [[0, 0], [1, -1], [1, 1], [2, 0]], [1, 1, 1, 1], is_dual)
 
 
 def random_tensor(codomain, domain, backend, seed=0, dtype="float64", labels=None) -> SymmetricTensor:

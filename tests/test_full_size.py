@@ -1,0 +1,169 @@
+"""Parity at BASELINE.json's full sizes through size-independent properties (GPU only).
+
+The oracle finishes chi = 128 .. 1024 in seconds, so configs 1 and 2 are compared with it directly; at
+chi = 4096 (config 3) and for the U(1) x U(1) complex128 case (config 4) the checks are the properties the
+reference's own tests use (tests/python_tests/test_tensors.py:3406-3429, 3754-3764): linearity of the
+matvec, bit-exact permute / combine->split round trips, reconstruction ``U S Vh = theta``, isometry,
+``sum S^2 = |theta|^2``, and the global truncation cut evaluated by the oracle on the same singular values.
+"""
+from __future__ import annotations
+
+import numpy as np
+import pytest
+
+from cyten_b200 import tensors as ct
+from cyten_b200.tensors import SymmetricTensor
+from cyten_b200.workloads import (CONFIG_LEGS, build_heff, hubbard_bond_leg, hubbard_phys_leg, mps_tensor,
+                                  random_tensor, u1_bond_leg, u1_mpo_leg, u1_phys_leg)
+
+pytestmark = pytest.mark.gpu
+
+
+def _axpby(a, x, b, y):
+    """a*x + b*y on tensors of identical structure (same tables => same arena layout)."""
+    import torch
+    assert np.array_equal(x.data.block_inds, y.data.block_inds) and np.array_equal(x.data.offsets, y.data.offsets)
+    d = type(x.data)(x.data.dtype, x.data.device, a * x.data.buf + b * y.data.buf, x.data.block_inds, x.data.offsets,
+                     x.data.shapes)
+    return SymmetricTensor(d, x.codomain, x.domain, x.backend, x.labels)
+
+
+def _blocks_close(x, y, tol):
+    assert np.array_equal(x.data.block_inds, y.data.block_inds)
+    assert np.array_equal(x.data.shapes, y.data.shapes)
+    scale = max(float(ct.norm(y)), 1e-300)
+    for bx, by in zip(x.data.to_numpy_blocks(), y.data.to_numpy_blocks()):
+        assert np.abs(bx - by).max() <= tol * scale
+
+
+def test_config1_tdot_mps_mpo_chi128_vs_oracle(cuda_backend, oracle_backend):
+    """BASELINE config 1: tdot of a 3-leg MPS tensor (chi = 128, d = 2) with a 4-leg MPO tensor (D = 5)."""
+    Q, sigma = CONFIG_LEGS[128]
+    v, p, w = u1_bond_leg(128, Q, sigma), u1_phys_leg(), u1_mpo_leg()
+    res = []
+    for be in (cuda_backend, oracle_backend):
+        A = mps_tensor(v, p, v, be, seed=3)
+        W = random_tensor([w, p], [p, w], be, seed=4, labels=["wL", "p", "wR", "p*"])
+        res.append(ct.tdot(A, W, ["p"], ["p*"]))
+    assert np.array_equal(res[0].data.block_inds, res[1].data.block_inds)
+    for g, c in zip(res[0].data.to_numpy_blocks(), res[1].data.to_numpy_blocks()):
+        assert np.allclose(g, c, rtol=1e-13, atol=1e-13)
+
+
+def test_config2_heff_matvec_chi1024_vs_oracle(cuda_backend, oracle_backend):
+    """BASELINE config 2: H_eff matvec at chi = 1024, float64, against the numpy oracle of the C-ABI."""
+    outs = []
+    for be in (cuda_backend, oracle_backend):
+        H, theta, _, _ = build_heff(1024, be)
+        outs.append(H.matvec(theta))
+    g, c = outs
+    assert np.array_equal(g.data.block_inds, c.data.block_inds)
+    scale = float(ct.norm(c))
+    for bg, bc in zip(g.data.to_numpy_blocks(), c.data.to_numpy_blocks()):
+        assert np.abs(bg - bc).max() <= 1e-12 * scale      # fp64 accumulation order differs (DMMA tiles vs BLAS)
+
+
+def test_heff_matvec_chi4096_linearity_and_roundtrips(cuda_backend):
+    be = cuda_backend
+    H, theta, _, _ = build_heff(4096, be)
+    theta2 = SymmetricTensor.from_numpy_blocks(
+        [np.random.default_rng(5 + i).standard_normal(b.shape) for i, b in enumerate(theta.data.to_numpy_blocks())],
+        theta.data.block_inds, theta.codomain, theta.domain, be, labels=theta.labels)
+    y1, y2 = H.matvec(theta), H.matvec(theta2)
+    y12 = H.matvec(_axpby(0.75, theta, -1.25, theta2))
+    ref = _axpby(0.75, y1, -1.25, y2)
+    import torch
+    scale = float(ct.norm(y1)) + float(ct.norm(y2))
+    for b12, bref in zip(y12.data.to_numpy_blocks(), ref.data.to_numpy_blocks()):
+        assert np.abs(b12 - bref).max() <= 1e-12 * scale
+    # permute there and back: bit-exact
+    back = ct.permute_legs(ct.permute_legs(theta, ["vR", "p1"], ["vL", "p0"]), ["vL", "p0"], ["vR", "p1"])
+    assert np.array_equal(back.data.block_inds, theta.data.block_inds)
+    assert all(np.array_equal(a, b) for a, b in zip(back.data.to_numpy_blocks(), theta.data.to_numpy_blocks()))
+    # combine -> split: bit-exact
+    rt = ct.split_legs(ct.combine_legs(theta, [0, 1], [2, 3]))
+    assert np.array_equal(rt.data.block_inds, theta.data.block_inds)
+    assert all(np.array_equal(a, b) for a, b in zip(rt.data.to_numpy_blocks(), theta.data.to_numpy_blocks()))
+
+
+def _svd_properties(be, theta, chi_max, oracle_backend):
+    import torch
+    nrm = float(ct.norm(theta))
+    U, S, Vh = ct.svd(theta)
+    s = S.to_numpy()
+    assert np.all(s >= 0)
+    assert abs(float(np.sum(s ** 2)) - nrm ** 2) <= 1e-12 * nrm ** 2
+    # reconstruction and isometry through the GPU path itself (compose)
+    US = ct.compose(U, _diag_as_tensor(S, be))
+    rec = ct.compose(US, Vh)
+    _same_layout(rec, theta)
+    for br, bt in zip(rec.data.to_numpy_blocks(), theta.data.to_numpy_blocks()):     # (arena padding is not data)
+        assert np.abs(br - bt).max() <= 1e-12 * nrm
+    UhU = ct.compose(_dagger(U, be), U)
+    for blk in UhU.data.to_numpy_blocks():
+        assert np.abs(blk - np.eye(blk.shape[0])).max() <= 1e-11
+    VVh = ct.compose(Vh, _dagger(Vh, be))
+    for blk in VVh.data.to_numpy_blocks():
+        assert np.abs(blk - np.eye(blk.shape[0])).max() <= 1e-11
+    # the global truncation cut: the oracle's selection on the SAME singular values keeps the same dimensions
+    Ut, St, Vt, err, _ = ct.truncated_svd(theta, chi_max=chi_max, svd_min=1e-12)
+    leg = S.leg
+    sd = S.data
+    sdata_cpu = type(sd)(sd.dtype, "cpu", sd.buf.cpu(), sd.block_inds, sd.offsets, sd.shapes)
+    keep, small, err_c, _ = oracle_backend.truncate_singular_values(
+        sdata_cpu, leg, chi_max=chi_max, chi_min=1, degeneracy_tol=0.0, trunc_cut=0.0, svd_min=1e-12, scale=1.0 / nrm)
+    assert np.array_equal(np.asarray(small.multiplicities), np.asarray(St.leg.multiplicities))
+    assert np.array_equal(np.asarray(small.defining_sectors), np.asarray(St.leg.defining_sectors))
+    assert abs(err - err_c) <= 1e-12
+    assert int(np.sum(St.leg.multiplicities)) <= chi_max
+    return s
+
+
+def _diag_as_tensor(S, be):
+    """DiagonalTensor -> 2-leg SymmetricTensor [leg] <- [leg] with diagonal blocks."""
+    blocks = [np.diag(b) for b in S.data.to_numpy_blocks()]
+    return SymmetricTensor.from_numpy_blocks(blocks, S.data.block_inds, [S.leg], [S.leg], be, labels=["b", "c"])
+
+
+def _dagger(T, be):
+    """Hermitian conjugate through host blocks (test helper): legs of codomain and domain swap."""
+    nc = T.num_codomain_legs
+    r = T.num_legs
+    blocks = [np.conj(b).transpose(list(range(r - 1, -1, -1))) for b in T.data.to_numpy_blocks()]
+    bi = T.data.block_inds[:, ::-1]
+    return SymmetricTensor.from_numpy_blocks(blocks, bi, list(T.domain.factors), list(T.codomain.factors), be,
+                                             labels=list(reversed(T.labels)))
+
+
+def _same_layout(like, T):
+    """T permuted (if necessary) to the leg partition of ``like`` -- here both are [vL,p0 | p1,vR]."""
+    assert np.array_equal(like.data.block_inds, T.data.block_inds)
+    assert np.array_equal(like.data.offsets, T.data.offsets)
+    return T
+
+
+def test_config3_truncated_svd_chi4096_properties(cuda_backend, oracle_backend):
+    """BASELINE config 3: truncated SVD of a two-site theta, U(1), chi = 4096."""
+    be = cuda_backend
+    Q, sigma = CONFIG_LEGS[4096]
+    v, p = u1_bond_leg(4096, Q, sigma), u1_phys_leg()
+    theta = random_tensor([v, p], [p.dual, v], be, seed=9, labels=["vL", "p0", "p1", "vR"])
+    _svd_properties(be, theta, 4096, oracle_backend)
+
+
+def test_config4_hubbard_u1u1_complex_tdot_svd(cuda_backend, oracle_backend):
+    """BASELINE config 4 (reduced to chi = 1024 so the host-side checks stay in seconds): Fermi-Hubbard
+    U(1) x U(1) legs, complex128, many small irregular blocks: tdot against the oracle, SVD properties."""
+    v, p = hubbard_bond_leg(1024), hubbard_phys_leg()
+    res = []
+    for be in (cuda_backend, oracle_backend):
+        A = mps_tensor(v, p, v, be, seed=1, dtype="complex128")
+        B = mps_tensor(v, p, v, be, seed=2, dtype="complex128")
+        res.append(ct.tdot(A, B, [2], [0]))
+    g, c = res
+    assert np.array_equal(g.data.block_inds, c.data.block_inds)
+    scale = float(ct.norm(c))
+    for bg, bc in zip(g.data.to_numpy_blocks(), c.data.to_numpy_blocks()):
+        assert np.abs(bg - bc).max() <= 1e-12 * scale
+    theta = random_tensor([v, p], [p.dual, v], cuda_backend, seed=3, dtype="complex128", labels=["vL", "p0", "p1", "vR"])
+    _svd_properties(cuda_backend, theta, 1024, oracle_backend)

@@ -8,6 +8,12 @@ from cyten_b200.workloads import build_heff
 chi = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 be = B200AbelianBackend("cuda:0")
 H, theta, _, _ = build_heff(chi, be)
+if os.environ.get("SHARD"):     # "r/N": the rank-local part of the sharded matvec (no collective), single process
+    from cyten_b200 import sharding as sh
+    r, N = (int(x) for x in os.environ["SHARD"].split("/"))
+    pg = sh.ProcessGroup(None)
+    pg.rank, pg.world = r, N
+    theta = sh.ShardedHEffective(H, pg).shard(theta)    # flop-cost LPT
 for _ in range(3):
     y = H.matvec(theta)
 ref = y.data.buf.clone()
@@ -22,5 +28,6 @@ fl = be.gemm_event_flops
 fat = [(m, f) for m, f in zip(ms, fl) if f > 0.05 * max(fl)]
 thin = [m for m, f in zip(ms, fl) if f <= 0.05 * max(fl)]
 g = np.mean([m for m, _ in fat]); f = np.mean([f for _, f in fat])
-print(f"variant={os.environ.get('CYB_GEMM_VARIANT', 'default')} fat_gemm_ms={g:.4f} TFLOPs={f / g / 1e9:.2f} skinny_ms={np.mean(thin):.4f} "
+per = {}
+print(f"shard={os.environ.get('SHARD')} variant={os.environ.get('CYB_GEMM_VARIANT', 'default')} fat_gemm_ms={g:.4f} TFLOPs={f / g / 1e9:.2f} skinny_ms={np.mean(thin):.4f} "
       f"step_ms={np.mean([a.elapsed_time(b) for a, b in evs]):.3f} checksum={float(y.data.buf.double().abs().sum()):.6e}")
