@@ -8,7 +8,9 @@ import ctypes as C
 from pathlib import Path
 
 _HERE = Path(__file__).resolve().parent
-LIB_PATH = _HERE / "libcyten_b200.so"
+import os as _os
+# CYB_LIB: tuning aid (a library built from the same sources with other compile-time tile parameters)
+LIB_PATH = Path(_os.environ["CYB_LIB"]) if _os.environ.get("CYB_LIB") else _HERE / "libcyten_b200.so"
 
 CYB_F64, CYB_C128 = 0, 1
 MAX_RANK = 8

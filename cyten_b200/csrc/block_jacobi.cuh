@@ -39,8 +39,14 @@ constexpr int BJ_SBUF_A = BJ_R * BJ_LDG + 2 * BJ_R * BJ_LDT;   // phases 1-2: G 
 constexpr int BJ_SBUF_B = 2 * BJ_R * BJ_LDB;                   // phase 3: two update tiles (aliases the above)
 constexpr int BJ_SBUF = BJ_SBUF_A > BJ_SBUF_B ? BJ_SBUF_A : BJ_SBUF_B;
 constexpr size_t BJ_SMEM = sizeof(double) * (size_t)(BJ_SQ + BJ_SBUF);
-constexpr int BJ_KS = 256;               // columns per partial Gram matrix
-constexpr int BJ_AC = 128;               // columns per apply work unit
+#ifndef CYB_BJ_KS
+#define CYB_BJ_KS 128
+#endif
+#ifndef CYB_BJ_AC
+#define CYB_BJ_AC 128
+#endif
+constexpr int BJ_KS = CYB_BJ_KS;         // columns per partial Gram matrix
+constexpr int BJ_AC = CYB_BJ_AC;         // columns per apply work unit
 constexpr size_t BJ_SMEM_GRAM = sizeof(double) * (size_t)(2 * BJ_R * BJ_LDT);
 constexpr size_t BJ_SMEM_ROT = sizeof(double) * (size_t)(2 * BJ_R * BJ_LDG);
 constexpr size_t BJ_SMEM_APPLY = sizeof(double) * (size_t)(BJ_SQ + BJ_SBUF_B);
@@ -377,13 +383,16 @@ bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ it
                 if (al >= FZ_TINY && be >= FZ_TINY && !(al <= fl && be <= fl) && g2 > tol2 * al * be) {
                     // rows x_p, x_q with <x_p, x_q> = ga = |ga| e^{i phi}:  x_p' = cs x_p - s x_q,
                     // x_q' = conj(s) x_p + cs x_q,  s = sn e^{i phi}  (real sectors: phi = 0 or pi)
-                    const double ga = CX ? sqrt(g2) : gr;
-                    const double zeta = (be - al) / (2.0 * ga);
-                    const double t = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
-                    cs = 1.0 / sqrt(1.0 + t * t);
+                    // t = sign(zeta) / (|zeta| + sqrt(1 + zeta^2)), zeta = (be - al) / (2 |ga|), written without
+                    // the division by ga (one sqrt, one division, one rsqrt on the serial path of a step)
+                    const double rg = CX ? rsqrt(g2) : 0.0;
+                    const double gabs = CX ? g2 * rg : fabs(gr);
+                    const double d = be - al, g2x = 2.0 * gabs;
+                    const double t = (d >= 0.0 ? g2x : -g2x) / (fabs(d) + sqrt(d * d + g2x * g2x));
+                    cs = rsqrt(1.0 + t * t);
                     const double s0 = cs * t;
-                    if (CX) { sn = s0 * gr / ga; si = s0 * gi / ga; }
-                    else sn = s0;
+                    if (CX) { sn = s0 * gr * rg; si = s0 * gi * rg; }
+                    else sn = gr >= 0.0 ? s0 : -s0;
                 }
             }
             s_rot[tid].p = p; s_rot[tid].q = q; s_rot[tid].cs = cs; s_rot[tid].sn = sn; s_rot[tid].si = si;

@@ -767,6 +767,9 @@ using CfgR9 = GemmCfg<false, 64, 128, 16, 2, 4, 3, false, false, false, 2>;
 using CfgR10 = GemmCfg<false, 64, 64, 16, 2, 2, 3, false, false, false, 4>;   // 4 warps, 4 CTAs per SM
 using CfgR11 = GemmCfg<false, 128, 64, 8, 4, 2, 4, false, false, false, 2>;   // BK = 8, 4 stages
 using CfgR12 = GemmCfg<false, 64, 64, 32, 2, 2, 3, false, false, false, 3>;   // 64 x 64, BK = 32
+using CfgR13 = GemmCfg<false, 64, 64, 16, 2, 2, 3, true, true, true, 4>;      // 64 x 64, interleaved groups + edge skipping
+using CfgR14 = GemmCfg<false, 64, 64, 16, 2, 2, 3, false, false, true, 4>;    // 64 x 64, contiguous groups + edge skipping
+using CfgR15 = GemmCfg<false, 64, 64, 16, 2, 2, 4, false, false, true, 4>;    // ... 4 stages
 
 static int gemm_variant()
 {
@@ -837,7 +840,7 @@ int cyb_grouped_gemm_prepare(int dtype, const int64_t* out_mn, const int64_t* ou
     const int64_t sk_target = (int64_t)sm_count() * 3 * ups;
     if (dtype == CYB_F64) {
         const int v = gemm_variant();
-        if (v == 10 || v == 12)
+        if (v == 10 || v == 12 || v == 13 || v == 14 || v == 15)
             gemm_schedule_kernel<64, 64, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket, 0);
         else if (v == 7 || v == 8 || v == 11)
             gemm_schedule_kernel<128, 64, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket, 0);
@@ -895,6 +898,9 @@ int cyb_grouped_gemm_run(const void* a, const void* b, void* c, int dtype, const
             case 10: return launch_gemm<CfgR10>(a, b, c, T[0], stream);
             case 11: return launch_gemm<CfgR11>(a, b, c, T[0], stream);
             case 12: return launch_gemm<CfgR12>(a, b, c, T[0], stream);
+            case 13: return launch_gemm<CfgR13>(a, b, c, T[0], stream);
+            case 14: return launch_gemm<CfgR14>(a, b, c, T[0], stream);
+            case 15: return launch_gemm<CfgR15>(a, b, c, T[0], stream);
             default: return launch_gemm<CfgR>(a, b, c, T[0], stream);
         }
     }
