@@ -83,6 +83,19 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
+def ncu_traffic(kernel):
+    """DRAM bytes per launch of ``kernel`` from the newest committed ncu --set full capture
+    (profiles/<round>/traffic.json), or None."""
+    files = sorted((ROOT / "profiles").glob("*/traffic.json"))
+    if not files:
+        return None, None
+    try:
+        d = json.loads(files[-1].read_text()).get(kernel)
+        return (d["bytes"], str(files[-1].relative_to(ROOT))) if d else (None, None)
+    except Exception:
+        return None, None
+
+
 def measured_peaks():
     f = ROOT / "MEASURED_PEAKS.json"
     if f.exists():
@@ -462,8 +475,10 @@ def run_b200(args):
             g_ms = float(np.mean([m for m, _ in fat]))
             g_fl = float(np.mean([f for _, f in fat]))
             ach = g_fl / (g_ms * 1e-3) / 1e12
+            traffic, traffic_src = ncu_traffic("grouped_gemm_kernel") if (world == 1 and chi == 4096) else (None, None)
             roof = {"bound": "tensor", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf,
-                    "traffic": None, "kernel": "grouped_gemm_kernel (DMMA f64)", "peak_source": peak_src,
+                    "traffic": traffic, "traffic_source": traffic_src,
+                    "kernel": "grouped_gemm_kernel (DMMA f64)", "peak_source": peak_src,
                     "launch_ms": g_ms, "launch_flops": g_fl,
                     "gemm_share_of_step": sum(gemm_ms) / total_ms if total_ms else None}
         cpu = None
