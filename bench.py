@@ -149,8 +149,8 @@ def cpu_matvec_time(chi, kind, repeats=1):
 
 
 def build_reference_theta(chi):
-    """theta = tdot(A, B) of two random MPS tensors on the reference's numpy backend (same blocks as the
-    GPU arm: workloads.random_blocks seeds 7 / 8)."""
+    """theta[vL, p0 | p1, vR] with N(0,1) blocks (from_random_normal on the two-site legs) on the
+    reference's numpy backend -- the same host blocks as the GPU arm (workloads.random_blocks, seed 9)."""
     sys.path.insert(0, str(ROOT / "oracle" / "_ref"))
     import cyten as ct
     from cyten_b200.workloads import CONFIG_LEGS, random_blocks, u1_bond_leg, u1_phys_leg
@@ -161,15 +161,13 @@ def build_reference_theta(chi):
 
     def conv(leg):
         return ct.ElementarySpace.from_defining_sectors(sym, leg.defining_sectors, leg.multiplicities, is_dual=leg.is_dual)
-    ts = []
-    for seed in (7, 8):
-        bi, blocks = random_blocks([v, p], [v], seed)
-        data = ct.backends.AbelianBackendData(dtype=ct.Dtype.float64, device="cpu",
-                                              blocks=[be.block_backend.as_block(b) for b in blocks],
-                                              block_inds=ct.backends.BlockInds(bi) if hasattr(ct.backends, "BlockInds") else bi,
-                                              is_sorted=True)
-        ts.append(ct.SymmetricTensor(data, [conv(v), conv(p)], [conv(v)], backend=be, labels=["vL", "p", "vR"]))
-    return ct.tdot(ts[0], ts[1], ["vR"], ["vL"]), ct
+    bi, blocks = random_blocks([v, p], [p.dual, v], 9)
+    data = ct.backends.AbelianBackendData(dtype=ct.Dtype.float64, device="cpu",
+                                          blocks=[be.block_backend.as_block(b) for b in blocks],
+                                          block_inds=ct.backends.BlockInds(bi), is_sorted=True)
+    theta = ct.SymmetricTensor(data, [conv(v), conv(p)], [conv(p.dual), conv(v)], backend=be,
+                               labels=["vL", "p0", "p1", "vR"])
+    return theta, ct
 
 
 def cpu_svd_time(chi, kind):
@@ -186,7 +184,8 @@ def cpu_svd_time(chi, kind):
     be = B200AbelianBackend("cpu", _library=cabi_numpy)
     Q, sigma = CONFIG_LEGS[chi]
     v, p = u1_bond_leg(chi, Q, sigma), u1_phys_leg()
-    th = ops.tdot(mps_tensor(v, p, v, be, seed=7), mps_tensor(v, p, v, be, seed=8), [2], [0])
+    from cyten_b200.workloads import random_tensor
+    th = random_tensor([v, p], [p.dual, v], be, seed=9, labels=["vL", "p0", "p1", "vR"])
     t0 = time.perf_counter()
     ops.truncated_svd(th, chi_max=chi, svd_min=1e-14)
     return time.perf_counter() - t0
@@ -433,35 +432,44 @@ def run_b200(args):
     e2e_val = flops / e2e_s / 1e9
     e2e_check = float(out_host[(pipe_steps - 1) & 1][:8].abs().sum())   # the result really arrived on the host
 
-    # ---- truncated SVD of theta = tdot(B, B) at chi (BASELINE config 3) ----
+    # ---- truncated SVD of the two-site theta at chi (BASELINE config 3) ----
+    # theta[vL, p0 | p1, vR] with N(0,1) blocks (the synthetic input of SURVEY 8(d)); the rank-chi theta = tdot(A, B)
+    # of two MPS tensors (half of every sector's singular values are numerically zero, the slow case for a Jacobi
+    # method) is timed too and reported as svd.rank_deficient_ms.
     svd_ms = svd_info = None
     if not args.no_svd:
-        from cyten_b200.workloads import mps_tensor, u1_bond_leg, u1_phys_leg
+        from cyten_b200.workloads import mps_tensor, random_tensor, u1_bond_leg, u1_phys_leg
         schi = args.svd_chi or chi
         Q, sigma = CONFIG_LEGS[schi]
         v, p = u1_bond_leg(schi, Q, sigma), u1_phys_leg()
-        A, B = mps_tensor(v, p, v, be, seed=7), mps_tensor(v, p, v, be, seed=8)
-        th = ct.tdot(A, B, [2], [0])
-        th.data.buf
+        th_full = random_tensor([v, p], [p.dual, v], be, seed=9, labels=["vL", "p0", "p1", "vR"])
+        th_def = ct.tdot(mps_tensor(v, p, v, be, seed=7), mps_tensor(v, p, v, be, seed=8), [2], [0])
+        th_def.data.buf
 
-        def do_svd():
-            if world > 1:
-                return sh.truncated_svd_sharded(th, pg, chi_max=schi, svd_min=1e-14)[:5]
-            return ct.truncated_svd(th, chi_max=schi, svd_min=1e-14)
-        do_svd()   # warm-up
-        times = []
-        for _ in range(3):
-            barrier()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            U, S, Vh, err, _ = do_svd()
-            e1.record()
-            barrier()
-            times.append(e0.elapsed_time(e1))
-        svd_ms = total_over_ranks(min(times), dist.ReduceOp.MAX if world > 1 else None)
-        kept = int(total_over_ranks(float(S.data.shapes.sum()))) if world > 1 else int(S.data.shapes.sum())
-        svd_info = {"chi": schi, "kept": kept, "err": err,
-                    "sweeps_max": int(be.last_info.abs().max().item()) if be.last_info is not None and be.last_info.numel() else None}
+        def time_svd(th, reps):
+            def do_svd():
+                if world > 1:
+                    return sh.truncated_svd_sharded(th, pg, chi_max=schi, svd_min=1e-14)[:5]
+                return ct.truncated_svd(th, chi_max=schi, svd_min=1e-14)
+            do_svd()   # warm-up
+            times = []
+            for _ in range(reps):
+                barrier()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                U, S, Vh, err, _ = do_svd()
+                e1.record()
+                barrier()
+                times.append(e0.elapsed_time(e1))
+            ms = total_over_ranks(min(times), dist.ReduceOp.MAX if world > 1 else None)
+            kept = int(total_over_ranks(float(S.data.shapes.sum()))) if world > 1 else int(S.data.shapes.sum())
+            sweeps = int(be.last_info.abs().max().item()) if be.last_info is not None and be.last_info.numel() else None
+            return ms, kept, err, sweeps
+        svd_ms, kept, err, sweeps = time_svd(th_full, 3)
+        def_ms, def_kept, def_err, def_sweeps = time_svd(th_def, 2)
+        svd_info = {"chi": schi, "input": "N(0,1) blocks on [vL,p0 | p1,vR] (full rank)", "kept": kept, "err": err,
+                    "sweeps_max": sweeps, "rank_deficient_ms": def_ms, "rank_deficient_kept": def_kept,
+                    "rank_deficient_sweeps_max": def_sweeps}
     clocks = sampler.stop() if rank == 0 else None
 
     if rank == 0:
