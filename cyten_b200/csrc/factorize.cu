@@ -11,8 +11,10 @@
 //  * EIGH : the same kernel on W_0 = H + sigma*I (sigma = 1.5*||H||_F, positive definite), whose
 //           left/right singular vectors coincide with the eigenvectors; lambda = S - sigma.
 //           Replaces block_backend->eigh (abelian.cpp:1781; numpy.cpp:658-680 np.linalg.eigh).
-//  * QR   : Householder QR on the transposed copy (columns of A become contiguous rows), one warp
-//           per trailing column, then backward accumulation of Q.
+//  * QR   : blocked Householder QR (compact WY, panels of QR_NB reflectors) on the transposed copy (columns of
+//           A become contiguous rows): the panel is factored in shared memory by CTA 0 of the team, every
+//           trailing column takes the whole panel in one pass (one warp per column), then blocked backward
+//           accumulation of Q.
 //           Replaces block_backend->matrix_qr(block, full=false) (abelian.cpp:3123;
 //           numpy.cpp:1236-1245 scipy.linalg.qr economic).
 //  Gauge: singular/eigen vectors are defined up to phases (and rotations in degenerate spaces), R's
@@ -27,6 +29,7 @@ namespace cyb {
 constexpr int FZ_THREADS = 1024;
 constexpr int FZ_WARPS = FZ_THREADS / 32;
 constexpr int FZ_MAX_SWEEPS = 60;
+constexpr int QR_NB = 4;                // reflectors per panel of the blocked Householder QR
 constexpr double FZ_EPS = 2.220446049250313e-16;
 constexpr double FZ_TINY = 1e-280;
 
@@ -397,10 +400,12 @@ template <bool CX, int G>
 __global__ void __launch_bounds__(FZ_THREADS, 1)
 householder_qr_kernel(const void* __restrict__ a_, void* __restrict__ q_, void* __restrict__ r_,
                       void* __restrict__ ws_, double* __restrict__ aux_, FzDesc* __restrict__ descs,
-                      const int64_t* __restrict__ sel)
+                      const int64_t* __restrict__ sel, int use_smem)
 {
     using E = El<CX>;
     using T = typename E::T;
+    extern __shared__ __align__(16) unsigned char qr_smem[];
+    T* s_U = reinterpret_cast<T*>(qr_smem);      // use_smem: the QR_NB x m panel (working rows, then reflectors)
     const int64_t mat = sel[Team<G>::id()];
     const FzDesc D = descs[mat];
     const int64_t m = D.m, n = D.n, k = m < n ? m : n;
@@ -422,38 +427,172 @@ householder_qr_kernel(const void* __restrict__ a_, void* __restrict__ q_, void* 
     }
     Team<G>::sync();
 
-    for (int64_t j = 0; j < k; ++j) {
-        // reflector from x = Wt[j][j:m]  (one warp of the team's CTA 0... every CTA's warp 0
-        // computes it redundantly from the same data so no extra barrier is needed)
-        T* x = Wt + j * m;
-        double nrm2 = 0.0;
-        for (int64_t q = j + lane; q < m; q += 32) nrm2 += E::abs2(E::ldcg(x + q));
-        nrm2 = warp_sum(nrm2);
-        const T x0 = E::ldcg(x + j);
-        const double ax0 = sqrt(E::abs2(x0));
-        const double nrm = sqrt(nrm2);
-        // alpha = -phase(x0) * ||x||
-        T ph = ax0 > 0.0 ? E::scale(x0, 1.0 / ax0) : E::one();
-        const T alpha = E::scale(ph, -nrm);
-        const T u0 = E::sub(x0, alpha);
-        // u^H u = ||x||^2 - |x0|^2 + |u0|^2
-        const double uu = nrm2 - ax0 * ax0 + E::abs2(u0);
-        const double tj = (nrm > 0.0 && uu > 0.0) ? 2.0 / uu : 0.0;
-        Team<G>::sync();   // everybody has read row j before it is modified
-        if (gwarp == 0 && lane == 0) {
-            tau[j] = tj;
-            uhead[j] = u0;
-            E::stcg(x + j, tj != 0.0 ? alpha : x0);
+    // Blocked Householder (compact WY, panels of QR_NB reflectors): H_j0 ... H_j0+nb-1 = I - U T U^H.
+    // The panel is factored by CTA 0 of the team (unblocked, on the nb panel rows only); every trailing row
+    // then takes ALL nb reflectors in one pass (nb dots, w = T^H d, one update) -- a quarter of the L2
+    // traffic and of the team barriers of the column-by-column version.
+    __shared__ T s_T[QR_NB][QR_NB];
+    __shared__ T s_z[QR_NB][QR_NB];
+    // element q of reflector j (j zeros, head, then the stored tail)
+    int64_t cur_j0 = 0;                           // panel currently held in s_U
+    auto uget = [&](int64_t j, int64_t q) -> T {
+        if (use_smem) return s_U[(j - cur_j0) * m + q];
+        return q > j ? E::ldcg(Wt + j * m + q) : (q == j ? E::ldcg(&uhead[j]) : E::zero());
+    };
+    // reflectors of the panel [j0, j0 + nb) -> s_U (zeros before the head), every CTA of the team
+    auto load_panel = [&](int64_t j0, int nb) {
+        cur_j0 = j0;
+        if (!use_smem) return;
+        __syncthreads();
+        for (int64_t e = tid; e < (int64_t)nb * m; e += FZ_THREADS) {
+            const int64_t j = j0 + e / m, q = e % m;
+            s_U[e] = q > j ? E::ldcg(Wt + j * m + q) : (q == j ? E::ldcg(&uhead[j]) : E::zero());
         }
-        // apply H_j to the trailing columns (rows i > j of Wt): y <- y - tau u (u^H y)
-        for (int64_t i = j + 1 + gwarp; i < n; i += gwarps) {
-            T* y = Wt + i * m;
-            T dot = (lane == 0) ? E::mul(E::conj(u0), E::ldcg(y + j)) : E::zero();
-            for (int64_t q = j + 1 + lane; q < m; q += 32) dot = E::add(dot, E::mul(E::conj(E::ldcg(x + q)), E::ldcg(y + q)));
+        __syncthreads();
+    };
+    // T of the panel [j0, j0 + nb) into s_T (every CTA builds its own copy): z[b][a] = u_b^H u_a, b < a
+    auto build_T = [&](int64_t j0, int nb) {
+        for (int pr = warp; pr < nb * nb; pr += FZ_WARPS) {
+            const int bb = pr / nb, aa = pr % nb;
+            if (bb >= aa) continue;
+            T dot = E::zero();
+            for (int64_t q = j0 + aa + lane; q < m; q += 32) dot = E::add(dot, E::mul(E::conj(uget(j0 + bb, q)), uget(j0 + aa, q)));
             dot = E::warp_sum(dot);
-            const T f = E::scale(dot, tj);
-            if (lane == 0) E::stcg(y + j, E::sub(E::ldcg(y + j), E::mul(f, u0)));
-            for (int64_t q = j + 1 + lane; q < m; q += 32) E::stcg(y + q, E::sub(E::ldcg(y + q), E::mul(f, E::ldcg(x + q))));
+            if (lane == 0) s_z[bb][aa] = dot;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            for (int aa = 0; aa < nb; ++aa) {
+                const double ta = __ldcg(&tau[j0 + aa]);
+                for (int bb = 0; bb < QR_NB; ++bb) s_T[bb][aa] = E::zero();
+                s_T[aa][aa] = E::from_re(ta);
+                for (int bb = 0; bb < aa; ++bb) {          // T[0:a, a] = -tau_a T[0:a, 0:a] z[0:a, a]
+                    T acc = E::zero();
+                    for (int cc = bb; cc < aa; ++cc) acc = E::add(acc, E::mul(s_T[bb][cc], s_z[cc][aa]));
+                    s_T[bb][aa] = E::scale(acc, -ta);
+                }
+            }
+        }
+        __syncthreads();
+    };
+    // y <- (I - U X U^H) y for one row y (length m) by one warp; X = T^H (ADJ) or T
+    auto apply_panel = [&](T* y, int64_t j0, int nb, bool adj) {
+        T d[QR_NB];
+#pragma unroll
+        for (int aa = 0; aa < QR_NB; ++aa) d[aa] = E::zero();
+#pragma unroll 4
+        for (int64_t q = j0 + lane; q < m; q += 32) {
+            const T yv = E::ldcg(y + q);
+#pragma unroll
+            for (int aa = 0; aa < QR_NB; ++aa)
+                if (aa < nb) d[aa] = E::add(d[aa], E::mul(E::conj(uget(j0 + aa, q)), yv));
+        }
+        T w[QR_NB];
+#pragma unroll
+        for (int aa = 0; aa < QR_NB; ++aa) d[aa] = E::warp_sum(d[aa]);
+#pragma unroll
+        for (int aa = 0; aa < QR_NB; ++aa) {
+            T acc = E::zero();
+#pragma unroll
+            for (int bb = 0; bb < QR_NB; ++bb) {
+                if (bb >= nb || aa >= nb) continue;
+                if (adj) { if (bb <= aa) acc = E::add(acc, E::mul(E::conj(s_T[bb][aa]), d[bb])); }
+                else { if (bb >= aa) acc = E::add(acc, E::mul(s_T[aa][bb], d[bb])); }
+            }
+            w[aa] = acc;
+        }
+#pragma unroll 4
+        for (int64_t q = j0 + lane; q < m; q += 32) {
+            T yv = E::ldcg(y + q);
+#pragma unroll
+            for (int aa = 0; aa < QR_NB; ++aa)
+                if (aa < nb) yv = E::sub(yv, E::mul(uget(j0 + aa, q), w[aa]));
+            E::stcg(y + q, yv);
+        }
+    };
+
+    for (int64_t j0 = 0; j0 < k; j0 += QR_NB) {
+        const int nb = (int)((k - j0) < QR_NB ? (k - j0) : QR_NB);
+        if (trank == 0 && use_smem) {
+            // the nb panel rows are factored in shared memory: one coalesced load, no L2 round trip per step
+            __syncthreads();
+            for (int64_t e = tid; e < (int64_t)nb * m; e += FZ_THREADS) s_U[e] = E::ldcg(Wt + j0 * m + e);
+            __syncthreads();
+            for (int aa = 0; aa < nb; ++aa) {
+                const int64_t j = j0 + aa;
+                T* x = s_U + (int64_t)aa * m;
+                double nrm2 = 0.0;
+                for (int64_t q = j + lane; q < m; q += 32) nrm2 += E::abs2(x[q]);
+                nrm2 = warp_sum(nrm2);
+                const T x0 = x[j];
+                const double ax0 = sqrt(E::abs2(x0));
+                const double nrm = sqrt(nrm2);
+                T ph = ax0 > 0.0 ? E::scale(x0, 1.0 / ax0) : E::one();
+                const T alpha = E::scale(ph, -nrm);
+                const T u0 = E::sub(x0, alpha);
+                const double uu = nrm2 - ax0 * ax0 + E::abs2(u0);
+                const double tj = (nrm > 0.0 && uu > 0.0) ? 2.0 / uu : 0.0;
+                __syncthreads();   // everybody has read row j before it is modified
+                if (tid == 0) {
+                    tau[j] = tj;
+                    uhead[j] = u0;
+                    x[j] = tj != 0.0 ? alpha : x0;
+                }
+                for (int i = aa + 1 + warp; i < nb; i += FZ_WARPS) {
+                    T* y = s_U + (int64_t)i * m;
+                    T dot = (lane == 0) ? E::mul(E::conj(u0), y[j]) : E::zero();
+                    for (int64_t q = j + 1 + lane; q < m; q += 32) dot = E::add(dot, E::mul(E::conj(x[q]), y[q]));
+                    dot = E::warp_sum(dot);
+                    const T f = E::scale(dot, tj);
+                    if (lane == 0) y[j] = E::sub(y[j], E::mul(f, u0));
+                    for (int64_t q = j + 1 + lane; q < m; q += 32) y[q] = E::sub(y[q], E::mul(f, x[q]));
+                }
+                __syncthreads();
+            }
+            for (int64_t e = tid; e < (int64_t)nb * m; e += FZ_THREADS)
+                if (e % m >= j0) E::stcg(Wt + j0 * m + e, s_U[e]);
+            __threadfence();
+        } else if (trank == 0) {
+            for (int aa = 0; aa < nb; ++aa) {
+                const int64_t j = j0 + aa;
+                // reflector from x = Wt[j][j:m]; every warp computes the scalars redundantly from the same data
+                T* x = Wt + j * m;
+                double nrm2 = 0.0;
+                for (int64_t q = j + lane; q < m; q += 32) nrm2 += E::abs2(E::ldcg(x + q));
+                nrm2 = warp_sum(nrm2);
+                const T x0 = E::ldcg(x + j);
+                const double ax0 = sqrt(E::abs2(x0));
+                const double nrm = sqrt(nrm2);
+                T ph = ax0 > 0.0 ? E::scale(x0, 1.0 / ax0) : E::one();
+                const T alpha = E::scale(ph, -nrm);       // alpha = -phase(x0) * ||x||
+                const T u0 = E::sub(x0, alpha);
+                const double uu = nrm2 - ax0 * ax0 + E::abs2(u0);   // u^H u
+                const double tj = (nrm > 0.0 && uu > 0.0) ? 2.0 / uu : 0.0;
+                __syncthreads();   // everybody has read row j before it is modified
+                if (warp == 0 && lane == 0) {
+                    tau[j] = tj;
+                    uhead[j] = u0;
+                    E::stcg(x + j, tj != 0.0 ? alpha : x0);
+                }
+                // H_j on the remaining panel rows
+                for (int64_t i = j + 1 + warp; i < j0 + nb; i += FZ_WARPS) {
+                    T* y = Wt + i * m;
+                    T dot = (lane == 0) ? E::mul(E::conj(u0), E::ldcg(y + j)) : E::zero();
+                    for (int64_t q = j + 1 + lane; q < m; q += 32) dot = E::add(dot, E::mul(E::conj(E::ldcg(x + q)), E::ldcg(y + q)));
+                    dot = E::warp_sum(dot);
+                    const T f = E::scale(dot, tj);
+                    if (lane == 0) E::stcg(y + j, E::sub(E::ldcg(y + j), E::mul(f, u0)));
+                    for (int64_t q = j + 1 + lane; q < m; q += 32) E::stcg(y + q, E::sub(E::ldcg(y + q), E::mul(f, E::ldcg(x + q))));
+                }
+                __threadfence();
+                __syncthreads();
+            }
+        }
+        Team<G>::sync();
+        if (j0 + nb < n) {
+            load_panel(j0, nb);
+            build_T(j0, nb);
+            for (int64_t i = j0 + nb + gwarp; i < n; i += gwarps) apply_panel(Wt + i * m, j0, nb, true);
         }
         Team<G>::sync();
     }
@@ -465,21 +604,12 @@ householder_qr_kernel(const void* __restrict__ a_, void* __restrict__ q_, void* 
     // Qt = [I_k 0] (k x m), then Q <- H_0 ... H_{k-1} [I;0] by backward accumulation
     for (int64_t e = gtid; e < k * m; e += gthreads) E::stcg(&Qt[e], (e / m == e % m) ? E::one() : E::zero());
     Team<G>::sync();
-    for (int64_t j = k - 1; j >= 0; --j) {
-        const double tj = __ldcg(&tau[j]);
-        const T u0 = E::ldcg(&uhead[j]);
-        const T* x = Wt + j * m;
-        if (tj != 0.0) {
-            for (int64_t cidx = j + gwarp; cidx < k; cidx += gwarps) {
-                T* y = Qt + cidx * m;
-                T dot = (lane == 0) ? E::mul(E::conj(u0), E::ldcg(y + j)) : E::zero();
-                for (int64_t q = j + 1 + lane; q < m; q += 32) dot = E::add(dot, E::mul(E::conj(E::ldcg(x + q)), E::ldcg(y + q)));
-                dot = E::warp_sum(dot);
-                const T f = E::scale(dot, tj);
-                if (lane == 0) E::stcg(y + j, E::sub(E::ldcg(y + j), E::mul(f, u0)));
-                for (int64_t q = j + 1 + lane; q < m; q += 32) E::stcg(y + q, E::sub(E::ldcg(y + q), E::mul(f, E::ldcg(x + q))));
-            }
-        }
+    for (int64_t j0 = ((k - 1) / QR_NB) * QR_NB; j0 >= 0; j0 -= QR_NB) {
+        const int nb = (int)((k - j0) < QR_NB ? (k - j0) : QR_NB);
+        load_panel(j0, nb);
+        build_T(j0, nb);
+        // columns c < j0 of Q are still unit vectors e_c, orthogonal to every u of this panel
+        for (int64_t cidx = j0 + gwarp; cidx < k; cidx += gwarps) apply_panel(Qt + cidx * m, j0, nb, false);
         Team<G>::sync();
     }
     for (int64_t e = gtid; e < m * k; e += gthreads) {
@@ -506,12 +636,16 @@ __global__ void fill_eye_kernel(void* __restrict__ dst_, const int64_t* __restri
 enum FzKind { FZ_SVD = 0, FZ_EIGH = 1, FZ_QR = 2 };
 
 template <class K, class... Args>
-static cudaError_t launch_team(K kernel, int G, int nteams, cudaStream_t stream, Args... args)
+static cudaError_t launch_team_smem(K kernel, int G, int nteams, size_t smem, cudaStream_t stream, Args... args)
 {
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(nteams * G), 1, 1);
     cfg.blockDim = dim3(FZ_THREADS, 1, 1);
-    cfg.dynamicSmemBytes = 0;
+    cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -521,6 +655,12 @@ static cudaError_t launch_team(K kernel, int G, int nteams, cudaStream_t stream,
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
+
+template <class K, class... Args>
+static cudaError_t launch_team(K kernel, int G, int nteams, cudaStream_t stream, Args... args)
+{
+    return launch_team_smem(kernel, G, nteams, 0, stream, args...);
 }
 
 constexpr int FZ_BIG_G = 8;          // CTAs per team for large sectors (portable cluster size)
@@ -795,6 +935,20 @@ static int run_factorize(FzKind kind, const void* a, void* o0, double* o1d, void
     cudaError_t err = cudaSuccess;
 #define FZ_LAUNCH(KERN, G, NT, ...) \
     do { if ((NT) > 0) { err = launch_team(KERN, G, (int)(NT), stream, __VA_ARGS__); if (err != cudaSuccess) { set_error("factorize launch failed: %s", cudaGetErrorString(err)); return CYB_ERR_CUDA; } } } while (0)
+#define FZ_LAUNCH_SMEM(KERN, G, NT, SMEM, ...) \
+    do { if ((NT) > 0) { err = launch_team_smem(KERN, G, (int)(NT), SMEM, stream, __VA_ARGS__); if (err != cudaSuccess) { set_error("factorize launch failed: %s", cudaGetErrorString(err)); return CYB_ERR_CUDA; } } } while (0)
+    // QR: the QR_NB x m panel lives in shared memory when it fits (else the kernels work through L2)
+    size_t qr_smem_small = 0, qr_smem_big = 0;
+    if (kind == FZ_QR) {
+        int64_t m_small = 0, m_big = 0;
+        for (int64_t i : small) m_small = std::max(m_small, descs[(size_t)i].m);
+        for (int64_t i : big) m_big = std::max(m_big, descs[(size_t)i].m);
+        const size_t lim = 200 * 1024;
+        qr_smem_small = (size_t)QR_NB * (size_t)m_small * esz;
+        qr_smem_big = (size_t)QR_NB * (size_t)m_big * esz;
+        if (qr_smem_small > lim) qr_smem_small = 0;
+        if (qr_smem_big > lim) qr_smem_big = 0;
+    }
     if (kind != FZ_QR && !big.empty()) {
         // large sectors: block Jacobi (block_jacobi.cuh) between the load and the output phases
         const int rc = (kind == FZ_EIGH)
@@ -823,14 +977,15 @@ static int run_factorize(FzKind kind, const void* a, void* o0, double* o1d, void
         }
     } else {
         if (cx) {
-            FZ_LAUNCH((householder_qr_kernel<true, 1>), 1, small.size(), a, o0, o1, d_ws, d_aux, d_desc, sel_small);
-            FZ_LAUNCH((householder_qr_kernel<true, FZ_BIG_G>), FZ_BIG_G, big.size(), a, o0, o1, d_ws, d_aux, d_desc, sel_big);
+            FZ_LAUNCH_SMEM((householder_qr_kernel<true, 1>), 1, small.size(), qr_smem_small, a, o0, o1, d_ws, d_aux, d_desc, sel_small, (int)(qr_smem_small > 0));
+            FZ_LAUNCH_SMEM((householder_qr_kernel<true, FZ_BIG_G>), FZ_BIG_G, big.size(), qr_smem_big, a, o0, o1, d_ws, d_aux, d_desc, sel_big, (int)(qr_smem_big > 0));
         } else {
-            FZ_LAUNCH((householder_qr_kernel<false, 1>), 1, small.size(), a, o0, o1, d_ws, d_aux, d_desc, sel_small);
-            FZ_LAUNCH((householder_qr_kernel<false, FZ_BIG_G>), FZ_BIG_G, big.size(), a, o0, o1, d_ws, d_aux, d_desc, sel_big);
+            FZ_LAUNCH_SMEM((householder_qr_kernel<false, 1>), 1, small.size(), qr_smem_small, a, o0, o1, d_ws, d_aux, d_desc, sel_small, (int)(qr_smem_small > 0));
+            FZ_LAUNCH_SMEM((householder_qr_kernel<false, FZ_BIG_G>), FZ_BIG_G, big.size(), qr_smem_big, a, o0, o1, d_ws, d_aux, d_desc, sel_big, (int)(qr_smem_big > 0));
         }
     }
 #undef FZ_LAUNCH
+#undef FZ_LAUNCH_SMEM
     return CYB_OK;
 }
 
