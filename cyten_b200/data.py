@@ -118,7 +118,10 @@ class AbelianBackendData:
     # -- construction ------------------------------------------------------------------------------
     @classmethod
     def empty(cls, dtype, device, block_inds, shapes, zero=False):
-        shapes = np.asarray(shapes, dtype=np.int64).reshape(len(block_inds), -1)
+        block_inds = np.asarray(block_inds, dtype=np.int64)
+        nlegs = block_inds.shape[1] if block_inds.ndim == 2 else 0
+        shapes = np.asarray(shapes, dtype=np.int64)
+        shapes = shapes.reshape(len(block_inds), -1) if len(block_inds) else shapes.reshape(0, nlegs)   # no blocks at all
         sizes = np.prod(shapes, axis=1).astype(np.int64) if shapes.shape[1] else np.ones(len(shapes), np.int64)
         offs, total = aligned_offsets(sizes)
         tdt = _TORCH_DTYPES[dtype_name(dtype)]

@@ -1,3 +1,2 @@
 #!/bin/bash
-mkdir -p gpurun_out
-timeout 300 ncu --set full --import-source on --clock-control none -k regex:householder_qr --launch-skip 2 -c 1 -f -o gpurun_out/qr_full python tools/qr_probe.py 974 520 1 2>&1 | tail -2
+timeout 600 python -m pytest tests/test_live_reference.py tests/test_full_size.py -m gpu -x -q 2>&1 | tail -5
