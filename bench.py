@@ -41,6 +41,7 @@ def parse():
     ap.add_argument("--svd-chi", type=int, default=None)
     ap.add_argument("--no-svd", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch every kernel eagerly instead of replaying a CUDA graph")
     ap.add_argument("--cpu-chi", type=int, default=None, help="bond dimension of the bounded CPU sample")
     return ap.parse_args()
 
@@ -285,13 +286,27 @@ def run_b200(args):
     pg = sh.attach_process_group(be, dist.group.WORLD if world > 1 else None)
     chi = args.chi
     H, theta_full, host, sp = build_heff(chi, be)
-    SH = sh.ShardedHEffective(H, pg)
+    SH = sh.ShardedHEffective(H, pg, split_heavy=os.environ.get("CYB_SPLIT_HEAVY", "0") == "1")
     # multi-GPU: theta lives sharded along the sectors of vR (LPT by block volume); the matvec chain is
     # rank-local until vR is contracted, then one all_reduce of the (small) result arena
     theta = SH.shard(theta_full) if world > 1 else theta_full
 
-    def step():
-        return SH.matvec(theta) if world > 1 else H.matvec(theta)
+    def eager(t):
+        return SH.matvec(t) if world > 1 else H.matvec(t)
+
+    def local_chain(t):      # the part of a step without a collective: what a CUDA graph captures
+        return SH.matvec_local(t) if world > 1 else H.matvec(t)
+    captured = {}
+
+    def step(t=None):
+        t = theta if t is None else t
+        cap = captured.get(id(t))
+        if cap is None:
+            return eager(t)
+        y = cap()
+        if world > 1:
+            pg.all_reduce(y.data.buf)
+        return y
 
     def barrier():
         if world > 1:
@@ -316,47 +331,51 @@ def run_b200(args):
         y = step()
     be.plan_mkn = None
     l2_flush = torch.empty(192 * 1024 * 1024, dtype=torch.uint8, device=dev)
+    # the plan-cached chain is pure kernel launches: capture it once into a CUDA graph and replay it
+    use_graph = not args.no_graph
+    if use_graph:
+        from cyten_b200.graphs import CapturedStep
+        captured[id(theta)] = CapturedStep(local_chain, theta, warmup=2)
+        for _ in range(2):
+            y = step()
 
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     # ---- timed region: K steps, device time, L2 flushed between steps (flush excluded via events) ----
+    def timed_steps(fn, nsteps):
+        evs = []
+        barrier()
+        for _ in range(nsteps):
+            l2_flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            evs.append((e0, e1))
+        barrier()
+        return sum(a.elapsed_time(b) for a, b in evs)
+    be.launches = 0
+    total_ms = timed_steps(step, args.steps)
+    launches = be.launches
+    # per-launch timing of the GEMM kernels (roofline): the same kernels launched eagerly with CUDA events around
+    # each launch on the launching stream (events cannot be recorded inside a graph replay)
     be.gemm_events = []
     be.gemm_event_flops = []
-    be.launches = 0
-    step_ev = []
-    barrier()
-    for _ in range(args.steps):
-        l2_flush.zero_()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        y = step()
-        e1.record()
-        step_ev.append((e0, e1))
-    barrier()
-    launches = be.launches
-    total_ms = sum(a.elapsed_time(b) for a, b in step_ev)
+    eager_total_ms = timed_steps(lambda: eager(theta), args.steps)
     gemm_ms = [a.elapsed_time(b) for a, b in be.gemm_events]
     gemm_flops = list(be.gemm_event_flops)
     be.gemm_events = None
+    eager_ms_per_step = total_over_ranks(eager_total_ms, dist.ReduceOp.MAX if world > 1 else None) / args.steps
     total_ms = total_over_ranks(total_ms, dist.ReduceOp.MAX if world > 1 else None)
     ms_per_step = total_ms / args.steps
     value = flops / (ms_per_step * 1e-3) / 1e9
 
     # ---- the same step with the plan cache disabled (bookkeeping recomputed on device every call) ----
     be.plan_cache = False
-    step()
-    barrier()
-    ev = []
-    for _ in range(min(args.steps, 3)):
-        l2_flush.zero_()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        step()
-        e1.record()
-        ev.append((e0, e1))
-    barrier()
-    noplan_ms = total_over_ranks(sum(a.elapsed_time(b) for a, b in ev) / len(ev), dist.ReduceOp.MAX if world > 1 else None)
+    eager(theta)
+    nnp = min(args.steps, 3)
+    noplan_ms = total_over_ranks(timed_steps(lambda: eager(theta), nnp) / nnp, dist.ReduceOp.MAX if world > 1 else None)
     be.plan_cache = True
 
     # ---- end to end: theta from pinned host memory every step, result back to the host ----
@@ -374,8 +393,9 @@ def run_b200(args):
                             theta.data.offsets, theta.data.shapes, sig=theta.data.sig)
     thetas = [theta, SymmetricTensor(d2, theta.codomain, theta.domain, be, theta.labels)]
 
-    def stepk(t):
-        return SH.matvec(t) if world > 1 else H.matvec(t)
+    if use_graph:
+        captured[id(thetas[1])] = CapturedStep(local_chain, thetas[1], warmup=2)   # one graph per theta arena
+    stepk = step
     y = stepk(thetas[1])
     nres = y.data.buf.numel()
     lo, hi = (rank * nres) // world, ((rank + 1) * nres) // world
@@ -408,6 +428,8 @@ def run_b200(args):
                 e_in = torch.cuda.Event()
                 e_in.record(s_in)
             cur.wait_event(e_in)
+            if ev_out[k] is not None:
+                cur.wait_event(ev_out[k])            # a graph's result arena is static: step i-2's download must be done
             yk = stepk(thetas[k])
             yb = yk.data.buf                         # materialises the final (lazy) permute_legs
             ec = torch.cuda.Event()
@@ -488,7 +510,7 @@ def run_b200(args):
                     "traffic": traffic, "traffic_source": traffic_src,
                     "kernel": "grouped_gemm_kernel (DMMA f64)", "peak_source": peak_src,
                     "launch_ms": g_ms, "launch_flops": g_fl,
-                    "gemm_share_of_step": sum(gemm_ms) / total_ms if total_ms else None}
+                    "gemm_share_of_step": sum(gemm_ms) / eager_total_ms if eager_total_ms else None}
         cpu = None
         if not args.no_cpu_baseline and world == 1:
             cpu = cpu_baseline(args)
@@ -497,6 +519,8 @@ def run_b200(args):
                 "data": "synthetic",
                 "config": {"workload": f"U(1) DMRG two-site H_eff matvec (4 tdot + 5 permute_legs), chi={chi}, D=5, d=2, float64",
                            "l2": "192 MiB buffer written between timed steps", "flops_per_step": flops,
+                           "cuda_graph": {"enabled": use_graph, "ms_per_step_eager": eager_ms_per_step,
+                                          "launches_per_replay": (captured[id(theta)].launches_per_replay if use_graph else None)},
                            "plan_cache": {"enabled": True, "hits": be.plan_hits, "misses": be.plan_misses,
                                           "ms_per_step_without": noplan_ms, "ms_first_call": first_call_ms},
                            "sharding": ("theta sharded along vR sectors (LPT), rank-local chain, one all_reduce per matvec"

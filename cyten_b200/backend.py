@@ -80,7 +80,9 @@ class B200AbelianBackend:
 
     def _empty(self, dtype, device, block_inds, shapes, zero=False):
         if self.dry_run:
-            shapes = np.asarray(shapes, dtype=np.int64).reshape(len(block_inds), -1)
+            block_inds = np.asarray(block_inds, dtype=np.int64)
+            shapes = np.asarray(shapes, dtype=np.int64)
+            shapes = shapes.reshape(len(block_inds), -1) if len(block_inds) else shapes.reshape(0, block_inds.shape[1])
             sizes = np.prod(shapes, axis=1) if shapes.shape[1] else np.ones(len(shapes), np.int64)
             offs, _ = aligned_offsets(sizes)
             return AbelianBackendData(dtype, device, torch.empty(ALIGN, dtype=torch.float64), block_inds, offs, shapes)

@@ -26,7 +26,8 @@ import torch.distributed as dist
 
 from . import tensors as ct
 from .backend import B200AbelianBackend, conventional_leg_order, _c_strides
-from .data import AbelianBackendData
+from . import _lib
+from .data import AbelianBackendData, ptr
 from .spaces import TensorProduct
 from .tensors import DiagonalTensor, SymmetricTensor, valid_block_inds
 
@@ -85,16 +86,26 @@ def attach_process_group(backend: B200AbelianBackend, group=None) -> ProcessGrou
 # ---- block subsets ---------------------------------------------------------------------------------
 def take_blocks(T: SymmetricTensor, which) -> SymmetricTensor:
     """The tensor holding only blocks ``which`` (ascending positions) of T, in a new arena (one batched
-    copy launch)."""
+    copy launch; the job list is a cached plan)."""
     be = T.backend
     which = np.asarray(which, dtype=np.int64)
     d = T.data
-    res = be._empty(d.dtype, be.device, d.block_inds[which], d.shapes[which])
-    if len(which):
-        sizes = d.sizes[which].reshape(-1, 1)
-        ones = np.ones_like(sizes)
-        jobs = be._make_jobs(d.offsets[which], res.offsets, sizes, ones, ones)
-        be._copy_blocks(d.buf, res.buf, jobs, d.cyb_dtype)
+    key = ("take", d.sig, which.tobytes())
+    plan = be._plan_get(key)
+    if plan is None:
+        res = be._empty(d.dtype, be.device, d.block_inds[which], d.shapes[which])
+        prepared = (0, None)
+        if len(which):
+            sizes = d.sizes[which].reshape(-1, 1)
+            ones = np.ones_like(sizes)
+            prepared = be._prepare_copy(be._make_jobs(d.offsets[which], res.offsets, sizes, ones, ones))
+        plan = dict(bi=res.block_inds, shapes=res.shapes, copy=prepared, sig=res.sig)
+        if not be.dry_run:
+            be._plan_put(key, plan)
+    else:
+        res = be._empty(d.dtype, be.device, plan["bi"], plan["shapes"])
+        res._sig = plan["sig"]
+    be._run_copy(d.buf, res.buf, plan["copy"], d.cyb_dtype)
     return SymmetricTensor(res, T.codomain, T.domain, be, T.labels)
 
 
@@ -130,6 +141,18 @@ def flop_costs_of_leg(T: SymmetricTensor, leg, chain) -> np.ndarray:
     finally:
         be.dry_run, be.plan_cache, be.plan_mkn = saved
     return costs
+
+
+def flop_costs_total(T: SymmetricTensor, chain) -> float:
+    """``sum M*K*N`` over the composes of ``chain(T)`` (plan-only pass, nothing cached, no arena touched)."""
+    be = T.backend
+    saved = (be.dry_run, be.plan_cache, be.plan_mkn)
+    be.dry_run, be.plan_cache, be.plan_mkn = True, False, []
+    try:
+        chain(T)
+        return float(sum(be.plan_mkn))
+    finally:
+        be.dry_run, be.plan_cache, be.plan_mkn = saved
 
 
 def shard_by_leg(T: SymmetricTensor, leg, pg: ProcessGroup, costs=None):
@@ -174,6 +197,8 @@ def expand_to_full(T: SymmetricTensor) -> SymmetricTensor:
         prepared = be._prepare_copy(jobs)
         be._run_copy(d.buf, res.buf, prepared, d.cyb_dtype)
         be._plan_put(key, dict(bi=full_bi, shapes=shapes, copy=prepared, sig=res.sig))
+    elif not be.dry_run:
+        be._plan_put(key, dict(bi=full_bi, shapes=shapes, copy=(0, None), sig=res.sig))
     return SymmetricTensor(res, T.codomain, T.domain, be, T.labels)
 
 
@@ -208,24 +233,95 @@ class ShardedHEffective:
     contractions leave ``vR`` open and are rank-local; the last one contracts ``vR`` with RP, so each
     rank holds a partial sum over its ``vR`` sectors and one all_reduce finishes the matvec."""
 
-    def __init__(self, H, pg: ProcessGroup, shard_leg="vR"):
-        self.H, self.pg, self.shard_leg = H, pg, shard_leg
+    def __init__(self, H, pg: ProcessGroup, shard_leg="vR", split_heavy=False):
+        self.H, self.pg, self.shard_leg, self.split_heavy = H, pg, shard_leg, split_heavy
+        self.chains = [(H, None)]
 
     def shard(self, theta: SymmetricTensor) -> SymmetricTensor:
-        """Rank-local part of theta: sectors of ``shard_leg`` assigned by LPT on the flops each sector
-        causes in the matvec chain (identical on every rank: pure integer bookkeeping)."""
+        """Rank-local part of theta.  Work items are the sectors of ``shard_leg`` weighted by the flops each causes
+        in the matvec chain; a sector heavier than ~one rank's share (the central sectors: 20 % of the flops sit
+        on q = 0 at chi = 4096) is split further along the OUTPUT sectors ``vL'`` of LP -- LP restricted to a subset
+        of its row sectors is again just a block subset, every later contraction keeps ``vL'`` open, so the parts
+        stay disjoint in work and their results add up.  Items go to ranks by LPT; identical on every rank
+        (pure integer bookkeeping).  The split is OFF by default (``split_heavy``): measured at chi = 4096 / 8 ranks
+        (profiles/r1c/README.md) every extra chain pays the fixed cost of 11 more small kernels and the GEMM rate
+        of the pieces drops to 5-8 TFLOP/s, so the balanced parts run slower (0.9-1.4 ms per rank, graph replay)
+        than the unbalanced whole sectors (0.41-0.68 ms)."""
+        self.chains = [(self.H, None)]
         if self.pg.world == 1:
             return theta
-        costs = flop_costs_of_leg(theta, self.shard_leg, self.H.matvec)
+        from .workloads import HEffective
+        H, pg = self.H, self.pg
+        costs = flop_costs_of_leg(theta, self.shard_leg, H.matvec)
         self.costs = costs
-        return shard_by_leg(theta, self.shard_leg, self.pg, costs=costs)[0]
+        ideal = float(costs.sum()) / pg.world
+        ax = theta.get_leg_idcs([self.shard_leg])[0]
+        lp = H.LP.data
+        w_rows = np.bincount(lp.block_inds[:, 0], weights=lp.sizes.astype(np.float64),
+                             minlength=H.LP.codomain.factors[0].num_sectors)
+        items = []          # (cost, vR sector, vL' sectors of LP or None)
+        for sec, c in enumerate(costs):
+            if c <= 0:
+                continue
+            nparts = int(np.ceil(c / (0.5 * ideal))) if (self.split_heavy and c > 0.9 * ideal) else 1
+            nparts = min(nparts, int(np.count_nonzero(w_rows)))
+            if nparts <= 1:
+                items.append((float(c), sec, None))
+                continue
+            # exact flops of (this vR sector) x (each row sector of LP): one more plan-only pass per row sector
+            th_sec = take_blocks(theta, np.nonzero(theta.data.block_inds[:, ax] == sec)[0])
+            w_sec = np.zeros(len(w_rows))
+            for a in np.nonzero(w_rows > 0)[0]:
+                LP_a = take_blocks(H.LP, np.nonzero(lp.block_inds[:, 0] == a)[0])
+                w_sec[a] = flop_costs_total(th_sec, HEffective(LP_a, H.RP, H.W1, H.W2, H.ct).matvec)
+            part_of_row = lpt_assign(w_sec, nparts)
+            for k in range(nparts):
+                rows = np.nonzero((part_of_row == k) & (w_sec > 0))[0]
+                if len(rows):
+                    items.append((float(w_sec[rows].sum()), sec, rows))
+        owner = lpt_assign(np.asarray([it[0] for it in items]), pg.world)
+        mine = [it for it, o in zip(items, owner) if o == pg.rank]
+        self.items, self.item_owner = items, owner
+        my_secs = sorted({it[1] for it in mine})
+        bi_ax = theta.data.block_inds[:, ax]
+        theta_local = take_blocks(theta, np.nonzero(np.isin(bi_ax, my_secs))[0])
+        loc_ax = theta_local.data.block_inds[:, ax]
+        chains = []
+        full_secs = [it[1] for it in mine if it[2] is None]
+        if full_secs:
+            idx = np.nonzero(np.isin(loc_ax, full_secs))[0]
+            chains.append((H, None if len(idx) == theta_local.data.num_blocks else idx))
+        for _, sec, rows in mine:
+            if rows is None:
+                continue
+            LP_A = take_blocks(H.LP, np.nonzero(np.isin(lp.block_inds[:, 0], rows))[0])
+            chains.append((HEffective(LP_A, H.RP, H.W1, H.W2, H.ct), np.nonzero(loc_ax == sec)[0]))
+        self.chains = chains
+        return theta_local
 
     def matvec_local(self, theta_local: SymmetricTensor) -> SymmetricTensor:
-        return self.H.matvec(theta_local)
+        """This rank's partial sum of ``H_eff . theta`` on the shared all-blocks layout (sum over its chains)."""
+        be = theta_local.backend
+        acc = None
+        for H_i, idx in self.chains:
+            th = theta_local if idx is None else take_blocks(theta_local, idx)
+            y = expand_to_full(H_i.matvec(th))
+            if acc is None:
+                acc = y
+            elif not be.dry_run:
+                n = acc.data.buf.numel() * (2 if acc.data.dtype == "complex128" else 1)
+                with be._ctx():
+                    be._call("cyb_axpby", ptr(y.data.buf), ptr(acc.data.buf), n, _lib.CYB_F64, 1.0, 1.0, be._stream())
+        if acc is None:      # a rank without work (theta_local has no blocks): zeros on the full layout
+            acc = expand_to_full(self.H.matvec(theta_local))
+        return acc
 
     def matvec(self, theta_local: SymmetricTensor) -> SymmetricTensor:
-        """Replicated ``H_eff . theta`` from the rank-local shard of theta."""
-        return all_reduce_blocks(self.matvec_local(theta_local), self.pg)
+        """Replicated ``H_eff . theta`` from the rank-local shard of theta: one all_reduce of the result arena."""
+        full = self.matvec_local(theta_local)
+        if not full.backend.dry_run:
+            self.pg.all_reduce(full.data.buf)
+        return full
 
 
 def svd_costs(tens: SymmetricTensor) -> np.ndarray:

@@ -13,7 +13,12 @@ if os.environ.get("SHARD"):     # "r/N": the rank-local part of the sharded matv
     r, N = (int(x) for x in os.environ["SHARD"].split("/"))
     pg = sh.ProcessGroup(None)
     pg.rank, pg.world = r, N
-    theta = sh.ShardedHEffective(H, pg).shard(theta)    # flop-cost LPT
+    SH = sh.ShardedHEffective(H, pg, split_heavy=os.environ.get("SPLIT", "0") == "1")
+    theta = SH.shard(theta)    # flop-cost LPT (+ 2-D split of the heavy sectors)
+    class _Loc:
+        matvec = staticmethod(SH.matvec_local)
+    H = _Loc()
+    print("chains:", len(SH.chains), "items:", len(SH.items))
 for _ in range(3):
     y = H.matvec(theta)
 ref = y.data.buf.clone()
@@ -23,11 +28,23 @@ for _ in range(10):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(); y = H.matvec(theta); e1.record(); evs.append((e0, e1))
 torch.cuda.synchronize()
+graph_ms = None
+if os.environ.get("GRAPH"):
+    from cyten_b200.graphs import CapturedStep
+    ge, be.gemm_events = be.gemm_events, None
+    cap = CapturedStep(H.matvec, theta)
+    gev = []
+    for _ in range(10):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); cap(); e1.record(); gev.append((e0, e1))
+    torch.cuda.synchronize()
+    graph_ms = np.mean([a.elapsed_time(b) for a, b in gev])
+    be.gemm_events = ge
 ms = [a.elapsed_time(b) for a, b in be.gemm_events]
 fl = be.gemm_event_flops
 fat = [(m, f) for m, f in zip(ms, fl) if f > 0.05 * max(fl)]
 thin = [m for m, f in zip(ms, fl) if f <= 0.05 * max(fl)]
 g = np.mean([m for m, _ in fat]); f = np.mean([f for _, f in fat])
 per = {}
-print(f"shard={os.environ.get('SHARD')} variant={os.environ.get('CYB_GEMM_VARIANT', 'default')} fat_gemm_ms={g:.4f} TFLOPs={f / g / 1e9:.2f} skinny_ms={np.mean(thin):.4f} "
+print(f"graph_ms={graph_ms} shard={os.environ.get('SHARD')} variant={os.environ.get('CYB_GEMM_VARIANT', 'default')} fat_gemm_ms={g:.4f} TFLOPs={f / g / 1e9:.2f} skinny_ms={np.mean(thin):.4f} "
       f"step_ms={np.mean([a.elapsed_time(b) for a, b in evs]):.3f} checksum={float(y.data.buf.double().abs().sum()):.6e}")

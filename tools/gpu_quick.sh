@@ -1,2 +1,2 @@
 #!/bin/bash
-timeout 600 python -m pytest tests/test_live_reference.py tests/test_full_size.py -m gpu -x -q 2>&1 | tail -5
+for sh in 0/8 1/8 2/8 3/8 4/8 5/8 6/8 7/8; do SPLIT=1 GRAPH=1 SHARD=$sh timeout 300 python tools/gemm_probe.py 2>&1 | tail -2 | tr '\n' ' ' | cut -c1-150; echo; done
