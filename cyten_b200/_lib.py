@@ -50,6 +50,11 @@ SIGNATURES = {
     "cyb_axpby": (_int, [_vp, _vp, _i64, _int, _dbl, _dbl, _vp]),
     "cyb_scale_rows_cols": (_int, [_vp, _vp, _vp, _vp, _vp, _i64, _int, _int, _vp]),
     "cyb_gather_rows_cols": (_int, [_vp, _vp, _vp, _vp, _i64, _int, _int, _vp]),
+    "cyb_blas1_workspace_bytes": (_i64, []),
+    "cyb_blas1_chunk_elems": (_i64, [_int]),
+    "cyb_block_dot": (_int, [_vp, _vp, _vp, _vp, _i64, _i64, _int, _int, _vp, _vp, _vp]),
+    "cyb_block_lincomb": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _int, _vp, _vp, _vp, _vp, _vp]),
+    "cyb_scale_axis": (_int, [_vp, _vp, _vp, _vp, _i64, _i64, _vp, _int, _int, _vp]),
 }
 
 _lib = None

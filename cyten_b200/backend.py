@@ -20,6 +20,7 @@ import numpy as np
 import torch
 
 from . import _lib
+from .blas1 import Blas1Mixin
 from .data import AbelianBackendData, aligned_offsets, ptr, stream_ptr, to_device_i64, ALIGN
 from .spaces import (AbelianLegPipe, ElementarySpace, TensorProduct, find_row_differences,
                      make_stride)
@@ -41,7 +42,7 @@ def _c_strides(shapes: np.ndarray) -> np.ndarray:
     return st
 
 
-class B200AbelianBackend:
+class B200AbelianBackend(Blas1Mixin):
     """Abelian block-sparse backend on one B200."""
 
     def __init__(self, device="cuda:0", _library=None):
@@ -49,6 +50,7 @@ class B200AbelianBackend:
         used by the CPU test-suite to drive this host logic with the numpy oracle.  The product path
         never passes it: the CUDA library is mandatory and the device must be a GPU."""
         self.device = torch.device(device)
+        self._library = _library
         if _library is None:
             if self.device.type != "cuda":
                 raise _lib.CytenB200Error("B200AbelianBackend needs a CUDA device (no CPU fallback)")
@@ -873,19 +875,6 @@ class B200AbelianBackend:
             self._call("cyb_gather_rows_cols", ptr(T.buf), ptr(res.buf), ptr(d_desc), ptr(d_idx), len(sel),
                        0 if diag else axis, T.cyb_dtype, self._stream())
         return res
-
-    def norm(self, data: AbelianBackendData) -> float:
-        """Frobenius norm over all blocks (abelian.cpp:2780-2791).  The arena padding between blocks
-        is uninitialised, so the sum runs block by block."""
-        esz = 16 if data.dtype == "complex128" else 8
-        with self._ctx():
-            out = torch.zeros(1, dtype=torch.float64, device=self.device)
-            tot = torch.zeros(1, dtype=torch.float64, device=self.device)
-            for off, size in zip(data.offsets, data.sizes):
-                self._call("cyb_sumsq", C.c_void_p(data.buf.data_ptr() + int(off) * esz), int(size),
-                           data.cyb_dtype, ptr(out), self._stream())
-                tot += out
-            return float(tot.sqrt().item())
 
 
 class _Retyped:

@@ -1,0 +1,303 @@
+// Block-batched BLAS-1 over tensor arenas: the Krylov/Lanczos vector operations that sit between two H_eff
+// matvecs (reference: src/backends/abelian.cpp:2159-2211 inner, 2253-2301
+// linear_combination, 2759-2778 mul, 2780-2791 norm, 3177-3232 scale_axis; loop: src/tensors/krylov_based.cpp:844-882).
+//
+// The reference walks the block lists on the host and makes one numpy call per block.  Here one launch covers
+// all blocks of the tensors: a segment table (one row per pair of matching blocks: the element offsets of the
+// block in every operand arena + its size) is cut into chunks of CHUNK double2 "pairs"; a warp takes chunks
+// grid-stride, finds the chunk's segment by binary search in the (L1-resident) chunk prefix array and streams
+// the chunk with 16-byte loads.  All kernels are HBM-bound; the algorithmic bytes are (operands read + result
+// written) x block bytes.  Reductions are deterministic: one partial per CTA in a fixed chunk assignment, the
+// last CTA to finish sums the partials in index order (no floating-point atomics).
+#include "common.cuh"
+#include <algorithm>
+
+namespace cyb {
+
+constexpr int B1_THREADS = 256;
+constexpr int B1_CHUNK = 512;        // double2 pairs per chunk: 8 KB per operand, 16 pairs per lane
+constexpr int B1_MAX_GRID = 148 * 8;
+
+struct B1Seg {                        // device view of the segment table
+    const int64_t* seg;               // [nseg][ncol]: operand offsets (elements, -1 = block absent), then size
+    const int64_t* chunk0;            // [nseg + 1]: first chunk of every segment
+    int nseg, ncol;
+    int64_t nchunk;
+};
+
+__device__ __forceinline__ int b1_find(const int64_t* __restrict__ chunk0, int nseg, int64_t c)
+{
+    int lo = 0, hi = nseg;            // chunk0[lo] <= c < chunk0[hi]
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(chunk0 + mid) <= c) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+__device__ __forceinline__ double2 b1_ld(const double* p, int64_t d, int64_t nd)
+{
+    if (d + 1 < nd) return *reinterpret_cast<const double2*>(p + d);
+    return make_double2(p[d], 0.0);
+}
+
+__device__ __forceinline__ double2 cmul(double2 a, double2 b) { return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+
+// CTA-wide deterministic sum of NV values per thread into partial[blockIdx.x * NV + v]; the last CTA adds the
+// partials in order, applies nothing else and writes out[v]; it re-arms the counter for the next launch.
+template <int NV>
+__device__ __forceinline__ void b1_finish(double (&acc)[NV], double* __restrict__ partial, unsigned* __restrict__ counter,
+                                          double* __restrict__ out)
+{
+    __shared__ double s_red[NV][B1_THREADS / 32];
+    __shared__ bool s_last;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int v = 0; v < NV; ++v) {
+        double a = acc[v];
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) a += __shfl_xor_sync(0xffffffffu, a, d);
+        if (lane == 0) s_red[v][warp] = a;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+            double a = 0.0;
+            for (int w = 0; w < B1_THREADS / 32; ++w) a += s_red[v][w];
+            partial[(size_t)blockIdx.x * NV + v] = a;
+        }
+        __threadfence();
+        s_last = atomicAdd(counter, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    if (threadIdx.x < 32) {
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+            double a = 0.0;                                   // lane l sums blocks l, l+32, ... in order
+            for (unsigned b = threadIdx.x; b < gridDim.x; b += 32) a += __ldcg(partial + (size_t)b * NV + v);
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) a += __shfl_xor_sync(0xffffffffu, a, d);
+            if (threadIdx.x == 0) out[v] = a;
+        }
+        if (threadIdx.x == 0) *counter = 0u;
+    }
+}
+
+// out[0..1] = sum over segments of conj?(x) * y  (real dtype: out[1] = 0)
+template <bool CX>
+__global__ void __launch_bounds__(B1_THREADS) block_dot_kernel(const double* __restrict__ x, const double* __restrict__ y,
+                                                               B1Seg T, int conj_x, double* __restrict__ partial,
+                                                               unsigned* __restrict__ counter, double* __restrict__ out)
+{
+    constexpr int ES = CX ? 2 : 1;
+    const int lane = threadIdx.x & 31;
+    const int64_t warp0 = (int64_t)blockIdx.x * (B1_THREADS / 32) + (threadIdx.x >> 5);
+    const int64_t nwarp = (int64_t)gridDim.x * (B1_THREADS / 32);
+    double acc[2] = {0.0, 0.0};
+    for (int64_t c = warp0; c < T.nchunk; c += nwarp) {
+        const int s = b1_find(T.chunk0, T.nseg, c);
+        const int64_t* row = T.seg + (size_t)s * T.ncol;
+        const int64_t ox = __ldg(row), oy = __ldg(row + 1), nd = __ldg(row + 2) * ES;
+        const double* px = x + ox * ES;
+        const double* py = y + oy * ES;
+        const int64_t d0 = (c - __ldg(T.chunk0 + s)) * (2 * B1_CHUNK);
+#pragma unroll 4
+        for (int j = 0; j < B1_CHUNK / 32; ++j) {
+            const int64_t d = d0 + (int64_t)(j * 32 + lane) * 2;
+            if (d >= nd) break;
+            const double2 a = b1_ld(px, d, nd), b = b1_ld(py, d, nd);
+            if (CX) {
+                const double ay = (conj_x & 1) ? -a.y : a.y;
+                acc[0] += a.x * b.x - ay * b.y;
+                acc[1] += a.x * b.y + ay * b.x;
+            } else {
+                acc[0] += a.x * b.x + a.y * b.y;
+            }
+        }
+    }
+    if (conj_x & 2) acc[1] = 0.0;     // caller wants Re <x, y> only (the Lanczos alpha of a Hermitian operator)
+    b1_finish<2>(acc, partial, counter, out);
+}
+
+struct B1Coef {
+    double c[3][2];                   // host factors (re, im) of x, y, z
+    const double* dev[3];             // optional device factors (re, im): effective = host * device
+};
+
+// out = a x + b y + c z per segment (absent operands contribute 0); optional fused ||out||^2
+template <bool CX, bool NORM>
+__global__ void __launch_bounds__(B1_THREADS) block_lincomb_kernel(const double* x, const double* y, const double* z, double* o,   // o may alias an operand
+                                                                   B1Seg T, B1Coef K, double* __restrict__ partial,
+                                                                   unsigned* __restrict__ counter, double* __restrict__ sumsq)
+{
+    constexpr int ES = CX ? 2 : 1;
+    const int lane = threadIdx.x & 31;
+    const int64_t warp0 = (int64_t)blockIdx.x * (B1_THREADS / 32) + (threadIdx.x >> 5);
+    const int64_t nwarp = (int64_t)gridDim.x * (B1_THREADS / 32);
+    double2 k[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        k[i] = make_double2(K.c[i][0], K.c[i][1]);
+        if (K.dev[i]) {
+            const double2 d = make_double2(__ldg(K.dev[i]), CX ? __ldg(K.dev[i] + 1) : 0.0);
+            k[i] = CX ? cmul(k[i], d) : make_double2(k[i].x * d.x, 0.0);
+        }
+    }
+    const double* ops[3] = {x, y, z};
+    double acc[1] = {0.0};
+    for (int64_t c = warp0; c < T.nchunk; c += nwarp) {
+        const int s = b1_find(T.chunk0, T.nseg, c);
+        const int64_t* row = T.seg + (size_t)s * T.ncol;
+        const double* p[3];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            const int64_t off = __ldg(row + i);
+            p[i] = (ops[i] != nullptr && off >= 0) ? ops[i] + off * ES : nullptr;
+        }
+        double* po = o + __ldg(row + 3) * ES;
+        const int64_t nd = __ldg(row + 4) * ES;
+        const int64_t d0 = (c - __ldg(T.chunk0 + s)) * (2 * B1_CHUNK);
+#pragma unroll 4
+        for (int j = 0; j < B1_CHUNK / 32; ++j) {
+            const int64_t d = d0 + (int64_t)(j * 32 + lane) * 2;
+            if (d >= nd) break;
+            double2 r = make_double2(0.0, 0.0);
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+                if (p[i] == nullptr) continue;
+                const double2 v = b1_ld(p[i], d, nd);
+                if (CX) { const double2 t = cmul(k[i], v); r.x += t.x; r.y += t.y; }
+                else    { r.x += k[i].x * v.x; r.y += k[i].x * v.y; }
+            }
+            if (d + 1 < nd) *reinterpret_cast<double2*>(po + d) = r; else po[d] = r.x;
+            if (NORM) acc[0] += r.x * r.x + (d + 1 < nd ? r.y * r.y : 0.0);
+        }
+    }
+    if (NORM) b1_finish<1>(acc, partial, counter, sumsq);
+}
+
+// out block = in block scaled along one axis: block viewed as (outer, dleg, inner); element (a, r, b) *= d[r]
+// desc int64[nblk][6] = (off_in, off_out, outer, dleg, inner, d_off)
+template <bool CX, bool DCX>
+__global__ void __launch_bounds__(B1_THREADS) scale_axis_kernel(const double* __restrict__ in, double* __restrict__ out,
+                                                                const int64_t* __restrict__ desc, const double* __restrict__ dg,
+                                                                const int64_t* __restrict__ work0, int nblk, int64_t nwork)
+{
+    constexpr int ES = CX ? 2 : 1;
+    // work item = 1024 consecutive elements of one block
+    for (int64_t w = blockIdx.x; w < nwork; w += gridDim.x) {
+        const int b = b1_find(work0, nblk, w);
+        const int64_t* D = desc + (size_t)b * 6;
+        const int64_t dleg = __ldg(D + 3), inner = __ldg(D + 4), n = __ldg(D + 2) * dleg * inner;
+        const double* pi = in + __ldg(D) * ES;
+        double* po = out + __ldg(D + 1) * ES;
+        const double* pd = dg + __ldg(D + 5) * (DCX ? 2 : 1);
+        const int64_t e0 = (w - __ldg(work0 + b)) * 1024;
+#pragma unroll
+        for (int j = 0; j < 1024 / B1_THREADS; ++j) {
+            const int64_t e = e0 + j * B1_THREADS + threadIdx.x;
+            if (e >= n) break;
+            const int64_t r = (e / inner) % dleg;
+            if (CX) {
+                const double2 v = *reinterpret_cast<const double2*>(pi + 2 * e);
+                const double2 s = DCX ? *reinterpret_cast<const double2*>(pd + 2 * r) : make_double2(__ldg(pd + r), 0.0);
+                *reinterpret_cast<double2*>(po + 2 * e) = cmul(s, v);
+            } else {
+                po[e] = pi[e] * __ldg(pd + r);
+            }
+        }
+    }
+}
+
+static int b1_grid(int64_t nchunk)
+{
+    const int64_t want = (nchunk + B1_THREADS / 32 - 1) / (B1_THREADS / 32);
+    const int64_t cap = (int64_t)sm_count() * 8;
+    return (int)std::max<int64_t>(1, std::min<int64_t>(want, std::min<int64_t>(cap, B1_MAX_GRID)));
+}
+
+}  // namespace cyb
+
+using namespace cyb;
+
+extern "C" {
+
+int64_t cyb_blas1_workspace_bytes(void) { return (int64_t)(B1_MAX_GRID * 2 * sizeof(double) + 64); }
+
+int64_t cyb_blas1_chunk_elems(int dtype) { return dtype == CYB_C128 ? B1_CHUNK : 2 * B1_CHUNK; }
+
+int cyb_block_dot(const void* x, const void* y, const int64_t* seg, const int64_t* chunk0, int64_t nseg, int64_t nchunk,
+                  int dtype, int conj_x, double* out, void* work, cyb_stream_t stream_)
+{
+    CYB_REQUIRE(dtype == CYB_F64 || dtype == CYB_C128, "block_dot: dtype must be CYB_F64 or CYB_C128");
+    CYB_REQUIRE(out != nullptr && work != nullptr, "block_dot: out / work must not be null");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (nseg == 0 || nchunk == 0) { CYB_CHECK_CUDA(cudaMemsetAsync(out, 0, 2 * sizeof(double), stream)); return CYB_OK; }
+    B1Seg T{seg, chunk0, (int)nseg, 3, nchunk};
+    double* partial = static_cast<double*>(work);
+    unsigned* counter = reinterpret_cast<unsigned*>(static_cast<char*>(work) + B1_MAX_GRID * 2 * sizeof(double));
+    const int grid = b1_grid(nchunk);
+    if (dtype == CYB_C128)
+        block_dot_kernel<true><<<grid, B1_THREADS, 0, stream>>>((const double*)x, (const double*)y, T, conj_x, partial, counter, out);
+    else
+        block_dot_kernel<false><<<grid, B1_THREADS, 0, stream>>>((const double*)x, (const double*)y, T, conj_x, partial, counter, out);
+    CYB_LAUNCH_CHECK();
+    return CYB_OK;
+}
+
+int cyb_block_lincomb(const void* x, const void* y, const void* z, void* out, const int64_t* seg, const int64_t* chunk0,
+                      int64_t nseg, int64_t nchunk, int dtype, const double* coef, const double* const* coef_dev,
+                      double* sumsq, void* work, cyb_stream_t stream_)
+{
+    CYB_REQUIRE(dtype == CYB_F64 || dtype == CYB_C128, "block_lincomb: dtype must be CYB_F64 or CYB_C128");
+    CYB_REQUIRE(out != nullptr && coef != nullptr, "block_lincomb: out / coef must not be null");
+    CYB_REQUIRE(sumsq == nullptr || work != nullptr, "block_lincomb: the fused norm needs the workspace");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (nseg == 0 || nchunk == 0) {
+        if (sumsq) CYB_CHECK_CUDA(cudaMemsetAsync(sumsq, 0, sizeof(double), stream));
+        return CYB_OK;
+    }
+    B1Seg T{seg, chunk0, (int)nseg, 5, nchunk};
+    B1Coef K;
+    for (int i = 0; i < 3; ++i) {
+        K.c[i][0] = coef[2 * i]; K.c[i][1] = coef[2 * i + 1];
+        K.dev[i] = coef_dev ? coef_dev[i] : nullptr;
+    }
+    double* partial = static_cast<double*>(work);
+    unsigned* counter = work ? reinterpret_cast<unsigned*>(static_cast<char*>(work) + B1_MAX_GRID * 2 * sizeof(double)) : nullptr;
+    const int grid = b1_grid(nchunk);
+    const double *px = (const double*)x, *py = (const double*)y, *pz = (const double*)z;
+    double* po = (double*)out;
+    const bool cx = dtype == CYB_C128;
+    if (cx && sumsq)        block_lincomb_kernel<true, true><<<grid, B1_THREADS, 0, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
+    else if (cx)            block_lincomb_kernel<true, false><<<grid, B1_THREADS, 0, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
+    else if (sumsq)         block_lincomb_kernel<false, true><<<grid, B1_THREADS, 0, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
+    else                    block_lincomb_kernel<false, false><<<grid, B1_THREADS, 0, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
+    CYB_LAUNCH_CHECK();
+    return CYB_OK;
+}
+
+int cyb_scale_axis(const void* in, void* out, const int64_t* desc, const int64_t* work0, int64_t nblk, int64_t nwork,
+                   const void* diag, int dtype, int diag_dtype, cyb_stream_t stream_)
+{
+    CYB_REQUIRE(dtype == CYB_F64 || dtype == CYB_C128, "scale_axis: dtype must be CYB_F64 or CYB_C128");
+    CYB_REQUIRE(!(dtype == CYB_F64 && diag_dtype == CYB_C128), "scale_axis: promote the tensor to complex128 first");
+    if (nblk == 0 || nwork == 0) return CYB_OK;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int grid = (int)std::min<int64_t>(nwork, (int64_t)sm_count() * 8);
+    const double *pi = (const double*)in, *pd = (const double*)diag;
+    double* po = (double*)out;
+    if (dtype == CYB_C128 && diag_dtype == CYB_C128)
+        scale_axis_kernel<true, true><<<grid, B1_THREADS, 0, stream>>>(pi, po, desc, pd, work0, (int)nblk, nwork);
+    else if (dtype == CYB_C128)
+        scale_axis_kernel<true, false><<<grid, B1_THREADS, 0, stream>>>(pi, po, desc, pd, work0, (int)nblk, nwork);
+    else
+        scale_axis_kernel<false, false><<<grid, B1_THREADS, 0, stream>>>(pi, po, desc, pd, work0, (int)nblk, nwork);
+    CYB_LAUNCH_CHECK();
+    return CYB_OK;
+}
+
+}  // extern "C"

@@ -29,6 +29,9 @@ class CapturedStep:
             y = fn(input_tensor)
             y.data.buf
         torch.cuda.synchronize(be.device)
+        # compose caches re-laid-out copies of an (immutable) operand arena on the operand; the static input is NOT
+        # immutable -- its re-layout must be a node of the graph, not a buffer left over from the warm-up calls
+        input_tensor.data._relayout = None
         misses = be.plan_misses
         saved = (be.gemm_events, be.plan_mkn)
         be.gemm_events, be.plan_mkn = None, None        # timing events cannot be recorded inside a capture
@@ -45,6 +48,7 @@ class CapturedStep:
         if be.plan_misses != misses:
             raise RuntimeError("a plan was built during graph capture: run more warm-up calls first")
         self.output = y
+        input_tensor.data._relayout = None
 
     def __call__(self):
         self.graph.replay()

@@ -36,6 +36,21 @@ def from_reference(T, backend, symmetry: AbelianSymmetry) -> SymmetricTensor:
     return SymmetricTensor.from_numpy_blocks(blocks, bi, cod, dom, backend, labels=list(T.labels), dtype=dtype)
 
 
+def diagonal_from_reference(D, backend, symmetry: AbelianSymmetry) -> DiagonalTensor:
+    """Reference ``DiagonalTensor`` (blocks = vectors, block_inds rows ``[i, i]``) -> arena DiagonalTensor."""
+    import torch
+    from .data import AbelianBackendData
+    blocks = [np.asarray(b.to_numpy()).reshape(-1) for b in D.data.blocks]
+    bi = np.asarray(D.data.block_inds.to_numpy(), dtype=np.int64).reshape(len(blocks), 2)
+    dtype = "complex128" if any(np.iscomplexobj(b) for b in blocks) else "float64"
+    data = AbelianBackendData.empty(dtype, backend.device, bi, np.asarray([[b.size] for b in blocks], np.int64).reshape(-1, 1))
+    host = np.zeros(data.buf.numel(), dtype=np.complex128 if dtype == "complex128" else np.float64)
+    for b, off in zip(blocks, data.offsets):
+        host[off:off + b.size] = b
+    data.buf.copy_(torch.from_numpy(host))
+    return DiagonalTensor(data, leg_from_reference(D.leg, symmetry), backend, list(D.labels))
+
+
 def leg_to_reference(leg, ct, symmetry):
     """Host mirror -> ``ct.ElementarySpace`` / ``ct.AbelianLegPipe`` (``ct`` = the cyten module)."""
     if isinstance(leg, AbelianLegPipe):

@@ -18,7 +18,8 @@ from .data import AbelianBackendData
 from .spaces import AbelianLegPipe, ElementarySpace, TensorProduct
 
 __all__ = ["SymmetricTensor", "DiagonalTensor", "permute_legs", "combine_legs", "split_legs",
-           "compose", "tdot", "svd", "truncated_svd", "qr", "eigh", "norm"]
+           "compose", "tdot", "svd", "truncated_svd", "qr", "eigh", "norm", "inner", "linear_combination",
+           "scalar_multiply", "dagger", "scale_axis"]
 
 
 class SymmetricTensor:
@@ -349,4 +350,71 @@ def eigh(T: SymmetricTensor, new_labels=("a", "b", "c"), new_leg_dual=False, sor
 
 
 def norm(T) -> float:
+    """Frobenius norm (src/tensors/ops_algebra.cpp:2162-2165 -> abelian.cpp:2780-2791)."""
     return T.backend.norm(T.data)
+
+
+# ---- (f1) Krylov vector operations (ops_algebra.cpp:544-600, 700-760, 949-1010, 1575-1640) --------------------
+def _dual_label(label):
+    if label is None:
+        return None
+    return label[:-1] if label.endswith("*") else label + "*"
+
+
+def _check_same_legs(A, B, what: str, transposed: bool = False):
+    la, lb = A.legs, B.legs
+    if transposed:
+        lb = [l.dual for l in reversed(lb)]
+    if len(la) != len(lb) or any(x != y for x, y in zip(la, lb)):
+        raise ValueError(f"{what}: incompatible legs")
+    if (A.num_codomain_legs != (B.num_domain_legs if transposed else B.num_codomain_legs)):
+        raise ValueError(f"{what}: incompatible codomain / domain")
+
+
+def inner(A: SymmetricTensor, B: SymmetricTensor, do_dagger: bool = True):
+    """``<A|B>`` = trace(A^dagger B) if ``do_dagger`` else trace(A B) (B's legs = A's reversed and dualised)."""
+    _check_same_legs(A, B, "inner", transposed=not do_dagger)
+    return A.backend.inner(A.data, B.data, do_dagger)
+
+
+def linear_combination(a, v: SymmetricTensor, b, w: SymmetricTensor) -> SymmetricTensor:
+    """``a v + b w`` (tensors of equal legs; labels of ``v``)."""
+    _check_same_legs(v, w, "linear_combination")
+    return SymmetricTensor(v.backend.linear_combination(a, v.data, b, w.data), v.codomain, v.domain, v.backend, v.labels)
+
+
+def scalar_multiply(a, T: SymmetricTensor) -> SymmetricTensor:
+    return SymmetricTensor(T.backend.mul(a, T.data), T.codomain, T.domain, T.backend, T.labels)
+
+
+def dagger(T):
+    """Hermitian conjugate: codomain and domain swap, labels reversed and dualised (``p`` <-> ``p*``)."""
+    if isinstance(T, DiagonalTensor):
+        data = T.backend.lincomb_conj(T.data) if T.data.dtype == "complex128" else T.data
+        return DiagonalTensor(data, T.leg, T.backend, [_dual_label(l) for l in reversed(T.labels)])
+    return SymmetricTensor(T.backend.dagger(T.data), T.domain, T.codomain, T.backend,
+                           [_dual_label(l) for l in reversed(T.labels)])
+
+
+def scale_axis(T: SymmetricTensor, D: DiagonalTensor, leg) -> SymmetricTensor:
+    """Contracts the diagonal tensor ``D`` with one leg of ``T`` without moving it (``T.legs[leg]`` must be
+    ``D.leg`` or its dual): the U*S / S*Vh products of the sweep."""
+    i = T.get_leg_idcs(leg)[0]
+    tl = T.get_leg_co_domain(i)
+    if not (tl == D.leg or tl == D.leg.dual):     # block indices count the defining sectors: same for a leg and its dual
+        raise ValueError("scale_axis: incompatible legs")
+    return SymmetricTensor(T.backend.scale_axis(T.data, D.data, i), T.codomain, T.domain, T.backend, T.labels)
+
+
+def _install_operators():
+    ST = SymmetricTensor
+    ST.__add__ = lambda self, other: linear_combination(1.0, self, 1.0, other)
+    ST.__sub__ = lambda self, other: linear_combination(1.0, self, -1.0, other)
+    ST.__mul__ = lambda self, a: scalar_multiply(a, self)
+    ST.__rmul__ = lambda self, a: scalar_multiply(a, self)
+    ST.__truediv__ = lambda self, a: scalar_multiply(1.0 / a, self)
+    ST.__neg__ = lambda self: scalar_multiply(-1.0, self)
+    ST.hc = property(dagger)
+
+
+_install_operators()

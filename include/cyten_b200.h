@@ -217,6 +217,33 @@ int cyb_scale_rows_cols(void* x, const int64_t* dims, const int64_t* off, const 
                         const int64_t* d_off, int64_t nmat, int axis, int dtype,
                         cyb_stream_t stream);
 
+/* ---- (f1) Krylov vector operations over whole arenas (one launch for all blocks) ------------ *
+ * Segment tables (device int64): one row per pair of matching blocks, offsets in ELEMENTS of the operand
+ * arenas (-1 = the operand has no such block) followed by the block size; `chunk0[nseg + 1]` = running
+ * count of chunks of cyb_blas1_chunk_elems(dtype) elements per segment (ceil), `nchunk` = chunk0[nseg].
+ * `work` = device scratch of cyb_blas1_workspace_bytes(), zero-initialised ONCE by the caller (the kernels
+ * leave it re-armed); reductions are deterministic (fixed partial order, no floating-point atomics). */
+int64_t cyb_blas1_workspace_bytes(void);
+int64_t cyb_blas1_chunk_elems(int dtype);
+/* out[0] + i out[1] = sum_seg sum_e conj?(x[off_x + e]) * y[off_y + e]; seg rows = (off_x, off_y, size).
+ * conj_x bit 0: conjugate x; bit 1: write the real part only (out[1] = 0).
+ * inner (abelian.cpp:2159-2211) and, with x == y, norm^2 (abelian.cpp:2780-2791). */
+int cyb_block_dot(const void* x, const void* y, const int64_t* seg, const int64_t* chunk0, int64_t nseg,
+                  int64_t nchunk, int dtype, int conj_x, double* out, void* work, cyb_stream_t stream);
+/* out = a x + b y + c z per segment; seg rows = (off_x, off_y, off_z, off_out, size); x/y/z may be NULL.
+ * coef = host double[6] (re, im of a, b, c); coef_dev = NULL or host array of 3 device pointers (NULL entries
+ * allowed) to (re, im) factors multiplied onto a, b, c -- a Lanczos step never reads alpha back to the host.
+ * sumsq != NULL: also writes ||out||^2 (fused norm).  `out` may alias an operand when the offsets coincide.
+ * linear_combination / mul (abelian.cpp:2253-2301, 2759-2778), the axpy's of krylov_based.cpp:856-871. */
+int cyb_block_lincomb(const void* x, const void* y, const void* z, void* out, const int64_t* seg,
+                      const int64_t* chunk0, int64_t nseg, int64_t nchunk, int dtype, const double* coef,
+                      const double* const* coef_dev, double* sumsq, void* work, cyb_stream_t stream);
+/* scale_axis (abelian.cpp:3177-3232): out block = in block, viewed as (outer, dleg, inner), times
+ * diag[d_off + r] along the middle axis.  desc (device) int64[nblk][6] = (off_in, off_out, outer, dleg,
+ * inner, d_off); work0[nblk + 1] = running count of 1024-element work items per block. */
+int cyb_scale_axis(const void* in, void* out, const int64_t* desc, const int64_t* work0, int64_t nblk,
+                   int64_t nwork, const void* diag, int dtype, int diag_dtype, cyb_stream_t stream);
+
 /* Keep-mask compaction (apply_mask / _mask_contract, abelian.cpp:2483-2582, 645-673):
  * out_i = in_i[idx, :] (axis 0) or in_i[:, idx] (axis 1).  desc (device) int64[nmat][6] =
  * (m_in, n_in, src_off, dst_off, idx_begin, idx_count); idx (device) concatenated index lists. */

@@ -36,6 +36,8 @@ def _addr(p) -> int:
         return 0
     if isinstance(p, C.c_void_p):
         return p.value or 0
+    if isinstance(p, C.Array):
+        return C.addressof(p)
     return int(p)
 
 
@@ -474,6 +476,70 @@ def cyb_gather_rows_cols(src, dst, desc, idx, nmat, axis, dtype, stream=None):
             _arr(_addr(dst) + isz * int(do), ic * n, dt).reshape(ic, n)[:] = S[ix, :]
         else:
             _arr(_addr(dst) + isz * int(do), m * ic, dt).reshape(m, ic)[:] = S[:, ix]
+    return 0
+
+
+# ---- (f1) Krylov vector operations over whole arenas --------------------------------------------------------
+def cyb_blas1_workspace_bytes():
+    return 64
+
+
+def cyb_blas1_chunk_elems(dtype):
+    return 512 if int(dtype) == 1 else 1024
+
+
+def cyb_block_dot(x, y, seg, chunk0, nseg, nchunk, dtype, conj_x, out, work, stream=None):
+    """inner (abelian.cpp:2159-2211): sum over the common blocks of block_backend.inner = sum conj(a) * b."""
+    dt = _dt(dtype)
+    isz = np.dtype(dt).itemsize
+    o = _arr(out, 2, np.float64)
+    tot = 0.0 + 0.0j
+    for ox, oy, n in _i64(seg, 3 * nseg).reshape(nseg, 3):
+        a = _arr(_addr(x) + isz * int(ox), int(n), dt)
+        b = _arr(_addr(y) + isz * int(oy), int(n), dt)
+        tot += np.sum((np.conj(a) if int(conj_x) & 1 else a) * b)
+    o[0], o[1] = np.real(tot), (0.0 if int(conj_x) & 2 else np.imag(tot))
+    return 0
+
+
+def cyb_block_lincomb(x, y, z, out, seg, chunk0, nseg, nchunk, dtype, coef, coef_dev, sumsq, work, stream=None):
+    """linear_combination / mul (abelian.cpp:2253-2301, 2759-2778): per block a*v + b*w, a*v where w has no such
+    block, b*w where v has none; third operand for the Lanczos three-term recurrence."""
+    dt = _dt(dtype)
+    isz = np.dtype(dt).itemsize
+    k = _arr(coef, 6, np.float64)
+    k = [complex(k[0], k[1]), complex(k[2], k[3]), complex(k[4], k[5])]
+    if _addr(coef_dev):
+        ptrs = _arr(coef_dev, 3, np.uint64)
+        for i in range(3):
+            if int(ptrs[i]):
+                d = _arr(int(ptrs[i]), 2, np.float64)
+                k[i] *= complex(d[0], d[1]) if dt is np.complex128 else d[0]
+    if dt is np.float64:
+        k = [c.real for c in k]
+    ss = 0.0
+    for row in _i64(seg, 5 * nseg).reshape(nseg, 5):
+        n = int(row[4])
+        r = np.zeros(n, dtype=dt)
+        for i, base in enumerate((x, y, z)):
+            if _addr(base) and row[i] >= 0:
+                r = r + k[i] * _arr(_addr(base) + isz * int(row[i]), n, dt)
+        _arr(_addr(out) + isz * int(row[3]), n, dt)[:] = r
+        ss += float(np.sum(np.abs(r) ** 2))
+    if _addr(sumsq):
+        _arr(sumsq, 1, np.float64)[0] = ss
+    return 0
+
+
+def cyb_scale_axis(inp, out, desc, work0, nblk, nwork, diag, dtype, diag_dtype, stream=None):
+    """scale_axis (abelian.cpp:3177-3232): every block times the diagonal block of its sector along one axis."""
+    dt, ddt = _dt(dtype), _dt(diag_dtype)
+    isz, dsz = np.dtype(dt).itemsize, np.dtype(ddt).itemsize
+    for oi, oo, outer, dleg, inner, doff in _i64(desc, 6 * nblk).reshape(nblk, 6):
+        n = int(outer * dleg * inner)
+        a = _arr(_addr(inp) + isz * int(oi), n, dt).reshape(int(outer), int(dleg), int(inner))
+        d = _arr(_addr(diag) + dsz * int(doff), int(dleg), ddt)
+        _arr(_addr(out) + isz * int(oo), n, dt).reshape(a.shape)[:] = a * d[None, :, None]
     return 0
 
 

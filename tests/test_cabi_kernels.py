@@ -442,3 +442,127 @@ def test_blas1_helpers(lib):
     x = lib.up(M.reshape(-1).copy())
     lib.call("cyb_scale_rows_cols", lib.p(x), lib.p(lib.up(dims)), lib.p(lib.up(off)), lib.p(lib.up(d)), lib.p(lib.up(doff)), 1, 1, 0, lib.stream())
     assert np.array_equal(x.cpu().numpy().reshape(6, 9), M * d[None, :])
+
+
+# ---- (f1) Krylov vector operations over whole arenas ------------------------------------------------------------
+def _b1_arena(rng, sizes, dtype):
+    """Blocks at 16-element aligned offsets with NaN padding (the kernels must never read the padding)."""
+    offs, tot = [], 0
+    for s in sizes:
+        offs.append(tot)
+        tot += (s + 15) // 16 * 16
+    a = np.full(max(tot, 16), np.nan, dtype=dtype)
+    for o, s in zip(offs, sizes):
+        a[o:o + s] = rng.standard_normal(s) + (1j * rng.standard_normal(s) if dtype == np.complex128 else 0)
+    return a, np.asarray(offs, np.int64)
+
+
+def _b1_chunks(sizes, chunk):
+    c0 = np.zeros(len(sizes) + 1, np.int64)
+    c0[1:] = np.cumsum((np.asarray(sizes, np.int64) + chunk - 1) // chunk)
+    return c0
+
+
+B1_SIZES = [1, 2, 3, 15, 16, 17, 511, 512, 513, 1023, 1024, 1025, 5000, 70001, 7]
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.complex128])
+@pytest.mark.parametrize("flags", [0, 1, 3])
+def test_block_dot(lib, dtype, flags):
+    rng = np.random.default_rng(31)
+    x, ox = _b1_arena(rng, B1_SIZES, dtype)
+    y, oy = _b1_arena(rng, B1_SIZES[::-1], dtype)
+    oy = oy[::-1].copy()                                   # block t of x pairs with block t of y (other arena order)
+    keep = [t for t in range(len(B1_SIZES)) if t != 4]     # one block without partner
+    seg = np.stack([ox[keep], oy[keep], np.asarray(B1_SIZES, np.int64)[keep]], axis=1)
+    chunk = 512 if dtype == np.complex128 else 1024
+    c0 = _b1_chunks(seg[:, 2], chunk)
+    out = lib.empty(2, torch.float64)
+    work = lib.empty(148 * 8 * 2 + 8, torch.float64)
+    for _ in range(2):                                     # the second call checks that the workspace re-arms itself
+        lib.call("cyb_block_dot", lib.p(lib.up(x)), lib.p(lib.up(y)), lib.p(lib.up(seg)), lib.p(lib.up(c0)), len(seg),
+                 int(c0[-1]), int(dtype == np.complex128), flags, lib.p(out), lib.p(work), lib.stream())
+    ref = sum(np.sum((np.conj(x[a:a + n]) if flags & 1 else x[a:a + n]) * y[b:b + n]) for a, b, n in seg)
+    got = out.cpu().numpy()
+    scale = sum(np.sum(np.abs(x[a:a + n]) * np.abs(y[b:b + n])) for a, b, n in seg)
+    assert abs(got[0] - np.real(ref)) <= 1e-14 * scale
+    assert abs(got[1] - (0.0 if flags & 2 else np.imag(ref))) <= 1e-14 * scale
+
+
+def test_block_dot_empty(lib):
+    out = lib.up(np.ones(2))
+    work = lib.empty(148 * 8 * 2 + 8, torch.float64)
+    z = lib.up(np.zeros(16))
+    lib.call("cyb_block_dot", lib.p(z), lib.p(z), lib.p(lib.up(np.zeros((1, 3), np.int64))), lib.p(lib.up(np.zeros(1, np.int64))),
+             0, 0, 0, 1, lib.p(out), lib.p(work), lib.stream())
+    assert np.array_equal(out.cpu().numpy(), [0.0, 0.0])
+
+
+@pytest.mark.parametrize("dtype", [np.float64, np.complex128])
+@pytest.mark.parametrize("with_dev,with_norm", [(False, False), (True, True)])
+def test_block_lincomb(lib, dtype, with_dev, with_norm):
+    rng = np.random.default_rng(32)
+    cx = dtype == np.complex128
+    x, ox = _b1_arena(rng, B1_SIZES, dtype)
+    y, oy = _b1_arena(rng, B1_SIZES, dtype)
+    z, oz = _b1_arena(rng, B1_SIZES, dtype)
+    o, oo = _b1_arena(rng, B1_SIZES, dtype)
+    sizes = np.asarray(B1_SIZES, np.int64)
+    oy2, oz2 = oy.copy(), oz.copy()
+    oy2[2] = -1                                            # y lacks block 2, z lacks blocks 5 and 6
+    oz2[5:7] = -1
+    seg = np.stack([ox, oy2, oz2, oo, sizes], axis=1)
+    c0 = _b1_chunks(sizes, 512 if cx else 1024)
+    coef = np.asarray([0.7, -0.2 if cx else 0.0, -1.3, 0.4 if cx else 0.0, 2.0, 0.0])
+    dev = lib.up(np.asarray([0.35, 0.9 if cx else 0.0]))
+    ptrs = (C.c_void_p * 3)(None, dev.data_ptr() if with_dev else None, None)
+    d_o = lib.up(o)
+    ss = lib.empty(1, torch.float64)
+    work = lib.empty(148 * 8 * 2 + 8, torch.float64)
+    lib.call("cyb_block_lincomb", lib.p(lib.up(x)), lib.p(lib.up(y)), lib.p(lib.up(z)), lib.p(d_o), lib.p(lib.up(seg)),
+             lib.p(lib.up(c0)), len(seg), int(c0[-1]), int(cx), coef.ctypes.data_as(C.c_void_p), ptrs,
+             lib.p(ss) if with_norm else None, lib.p(work), lib.stream())
+    k = [complex(coef[0], coef[1]), complex(coef[2], coef[3]), complex(coef[4], coef[5])]
+    if with_dev:
+        k[1] *= complex(0.35, 0.9) if cx else 0.35
+    if not cx:
+        k = [c.real for c in k]
+    got = d_o.cpu().numpy()
+    tot = 0.0
+    for t, n in enumerate(sizes):
+        ref = k[0] * x[ox[t]:ox[t] + n]
+        if oy2[t] >= 0:
+            ref = ref + k[1] * y[oy[t]:oy[t] + n]
+        if oz2[t] >= 0:
+            ref = ref + k[2] * z[oz[t]:oz[t] + n]
+        assert np.allclose(got[oo[t]:oo[t] + n], ref, rtol=0, atol=1e-14 * max(1.0, np.abs(ref).max()))
+        pad = got[oo[t] + n:oo[t] + (n + 15) // 16 * 16]
+        assert np.all(np.isnan(pad))                        # the padding of the result arena is not written
+        tot += np.sum(np.abs(ref) ** 2)
+    if with_norm:
+        assert abs(ss.cpu().numpy()[0] - tot) <= 1e-13 * tot
+
+
+@pytest.mark.parametrize("dtype,ddtype", [(np.float64, np.float64), (np.complex128, np.float64), (np.complex128, np.complex128)])
+def test_scale_axis(lib, dtype, ddtype):
+    rng = np.random.default_rng(33)
+    shapes = [(3, 5, 4), (1, 7, 1), (40, 33, 9), (2, 1, 1500), (1, 1, 1), (17, 64, 1)]
+    sizes = [int(np.prod(s)) for s in shapes]
+    x, ox = _b1_arena(rng, sizes, dtype)
+    d, od = _b1_arena(rng, [s[1] for s in shapes], ddtype)
+    oo = ox[::-1].copy()                                  # output blocks in another order
+    order = np.argsort(-np.arange(len(shapes)))
+    out_sizes = [sizes[t] for t in order]
+    _, ooff = _b1_arena(rng, out_sizes, dtype)
+    oo = np.empty(len(shapes), np.int64)
+    oo[order] = ooff
+    desc = np.asarray([(ox[t], oo[t], s[0], s[1], s[2], od[t]) for t, s in enumerate(shapes)], np.int64)
+    w0 = np.zeros(len(shapes) + 1, np.int64)
+    w0[1:] = np.cumsum((np.asarray(sizes) + 1023) // 1024)
+    d_out = lib.empty(sum((s + 15) // 16 * 16 for s in sizes), torch.complex128 if dtype == np.complex128 else torch.float64)
+    lib.call("cyb_scale_axis", lib.p(lib.up(x)), lib.p(d_out), lib.p(lib.up(desc)), lib.p(lib.up(w0)), len(shapes), int(w0[-1]),
+             lib.p(lib.up(d)), int(dtype == np.complex128), int(ddtype == np.complex128), lib.stream())
+    got = d_out.cpu().numpy()
+    for t, s in enumerate(shapes):
+        ref = x[ox[t]:ox[t] + sizes[t]].reshape(s) * d[od[t]:od[t] + s[1]][None, :, None]
+        assert np.allclose(got[oo[t]:oo[t] + sizes[t]].reshape(s), ref, rtol=0, atol=1e-15 * max(1.0, np.abs(ref).max()))

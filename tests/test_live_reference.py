@@ -54,6 +54,12 @@ def _setup(name, dtype, chi, seed):
     return sym, AbelianSymmetry(moduli), A, B
 
 
+def _num(x):
+    """Reference Scalar -> python number."""
+    x = x.to_numpy() if hasattr(x, "to_numpy") else x
+    return complex(x) if np.iscomplexobj(x) else float(x)
+
+
 def _same(ours, ref, tol=0.0):
     """ours (arena tensor) == ref (reference tensor): tables bit-exact, blocks within tol * max|ref|."""
     bi = np.asarray(ref.data.block_inds.to_numpy()).reshape(len(ref.data.blocks), ours.data.block_inds.shape[1])
@@ -117,3 +123,72 @@ def _diag(S, be):
     blocks = [np.diag(b) for b in S.data.to_numpy_blocks()]
     return SymmetricTensor.from_numpy_blocks(blocks, S.data.block_inds, [S.leg], [S.leg], be, labels=["b", "c"],
                                              dtype=S.data.dtype)
+
+
+# ---- (f1) Krylov vector operations and the Lanczos loop against the reference's own ------------------------------------
+@pytest.mark.parametrize("name,dtype,chi", CASES)
+def test_vector_ops(backend, name, dtype, chi):
+    from cyten.testing import randomly_drop_blocks
+    sym, msym, A, B = _setup(name, dtype, chi, 5)
+    B2 = randomly_drop_blocks(1.0 * B, empty_ok=False, max_blocks=max(1, len(B.data.blocks) // 2),
+                              np_random=np.random.default_rng(3))
+    a, b, b2 = (from_reference(T, backend, msym) for T in (A, B, B2))
+    scale = _num(rc.norm(A)) * _num(rc.norm(B))
+    for x, X, y, Y in ((a, A, b, B), (a, A, b2, B2), (b2, B2, a, A)):
+        assert abs(ct.inner(x, y) - _num(rc.inner(X, Y))) <= 1e-14 * scale                 # inner
+    assert abs(ct.norm(a) - _num(rc.norm(A))) <= 1e-14 * _num(rc.norm(A))                     # norm
+    Bd, bd = rc.dagger(B), ct.dagger(b)
+    _same(bd, Bd)                                                                              # dagger: bit-exact
+    assert bd.labels == list(Bd.labels)
+    assert abs(ct.inner(a, bd, do_dagger=False) - _num(rc.inner(A, Bd, do_dagger=False))) <= 1e-14 * scale
+    co = (0.3 - 0.2j, 1.7) if dtype == "complex128" else (0.3, -1.7)
+    lin = rc.tensors.linear_combination
+    _same(ct.linear_combination(co[0], a, co[1], b2), lin(co[0], A, co[1], B2), tol=1e-15)        # union of the blocks
+    _same(ct.linear_combination(co[0], b2, co[1], a), lin(co[0], B2, co[1], A), tol=1e-15)
+    _same(co[0] * a, co[0] * A, tol=1e-15)                                                     # mul
+    _same(a - b, A - B, tol=1e-15)
+
+
+@pytest.mark.parametrize("name,dtype,chi", CASES)
+def test_scale_axis(backend, name, dtype, chi):
+    from cyten_b200.interop import diagonal_from_reference
+    sym, msym, A, B = _setup(name, dtype, chi, 6)
+    U, S, Vh = rc.svd(rc.tdot(A, B, ["vR"], ["vL"]))
+    sd = diagonal_from_reference(S, backend, msym)
+    _same(ct.scale_axis(from_reference(U, backend, msym), sd, 2), rc.scale_axis(U, S, 2), tol=1e-15)
+    _same(ct.scale_axis(from_reference(Vh, backend, msym), sd, 0), rc.scale_axis(Vh, S, 0), tol=1e-15)
+    P = rc.permute_legs(U, [0, 2], [1], bend_right=None)          # the scaled leg in the middle of the block axes
+    _same(ct.scale_axis(from_reference(P, backend, msym), sd, 1), rc.scale_axis(P, S, 1), tol=1e-15)
+
+
+@pytest.mark.parametrize("name,dtype,chi", CASES)
+@pytest.mark.parametrize("opts", [{}, {"N_cache": 3, "N_max": 30}, {"reortho": True, "N_max": 25}])
+def test_lanczos_matches_reference_lanczos(backend, name, dtype, chi, opts):
+    """The same Hermitian operator theta -> K theta + theta K2 and the same start vector through
+    cyten.krylov_based.lanczos and cyten_b200.krylov.lanczos: same number of iterations, same Ritz value, same vector."""
+    from cyten import krylov_based, sparse
+    from cyten_b200.krylov import lanczos
+    sym, msym, A, B = _setup(name, dtype, chi // 4, 7)
+    TH = rc.tdot(A, B, ["vR"], ["vL"])
+    rdt = rc.Dtype.complex128 if dtype == "complex128" else rc.Dtype.float64
+    rb = rc.get_backend("abelian", "numpy")
+    X = rc.SymmetricTensor.from_random_normal(TH.codomain, TH.codomain, backend=rb, dtype=rdt)
+    X2 = rc.SymmetricTensor.from_random_normal(TH.domain, TH.domain, backend=rb, dtype=rdt)
+    K, K2 = X + X.hc, X2 + X2.hc
+
+    class RefOp(sparse.LinearOperator):
+        def matvec(self, t):
+            return rc.compose(K, t) + rc.compose(t, K2)
+
+    class Op:
+        def __init__(self):
+            self.k, self.k2 = from_reference(K, backend, msym), from_reference(K2, backend, msym)
+
+        def matvec(self, t):
+            return ct.compose(self.k, t) + ct.compose(t, self.k2)
+
+    Er, psir, Nr = krylov_based.lanczos(RefOp(), TH, dict(opts))
+    E, psi, N = lanczos(Op(), from_reference(TH, backend, msym), dict(opts))
+    assert N == Nr
+    assert abs(E - _num(Er)) <= 1e-12 * (abs(_num(Er)) + 1.0)
+    assert abs(abs(ct.inner(from_reference(psir, backend, msym), psi)) - 1.0) <= 1e-10

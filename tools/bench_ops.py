@@ -31,7 +31,7 @@ def parse():
     ap.add_argument("--dtype", default="float64", choices=["float64", "complex128"])
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--no-ref", action="store_true")
-    ap.add_argument("--rows", default="permute,combine,split,tdot,svd,tsvd,qr,eigh")
+    ap.add_argument("--rows", default="permute,combine,split,tdot,svd,tsvd,qr,eigh,blas1")
     ap.add_argument("--out", default=None)
     return ap.parse_args()
 
@@ -184,6 +184,58 @@ def main():
         emit("a10 eigh(H[v | v])", ms, eigh_flops(hsect, cx), "TFLOP/s", peak_f64,
              f"{len(hsect)} sectors, largest {max(hsect)}")
 
+    if "blas1" in rows:
+        # (f1) Krylov vector operations.  The kernels take 10-30 us, less than one Python call: 16 calls are captured
+        # into one CUDA graph and the replay is timed; operands cycle through a pool of 8 theta-sized arenas (8 x 45 MB
+        # at chi=4096 > L2), so every call reads from HBM.
+        from cyten_b200.data import AbelianBackendData
+        from cyten_b200.tensors import DiagonalTensor
+
+        def clone(T, scale):
+            d = T.data
+            buf = d.buf.clone()
+            buf *= scale
+            return SymmetricTensor(AbelianBackendData(d.dtype, d.device, buf, d.block_inds, d.offsets, d.shapes, sig=d._sig),
+                                   T.codomain, T.domain, be, T.labels)
+        pool = [clone(TH, 1.0 + 0.1 * i) for i in range(8)]
+        NREP = 16
+
+        def graph_time(body):
+            body(0)
+            body(1)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            keep = []
+            with torch.cuda.graph(g):
+                for i in range(NREP):
+                    keep.append(body(i))
+            best = float("inf")
+            for _ in range(args.reps):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); g.replay(); e1.record(); torch.cuda.synchronize()
+                best = min(best, e0.elapsed_time(e1))
+            return best / NREP
+        nb = float(TH.data.nbytes())
+        scal = torch.zeros(4, dtype=torch.float64, device=dev)
+        ms = graph_time(lambda i: be.inner_dev(pool[(2 * i) % 8].data, pool[(2 * i + 1) % 8].data, True, out=scal[0:2]))
+        emit("f1-inner inner(theta, theta')", ms, 2 * nb, "GB/s", peak_hbm)
+        ms = graph_time(lambda i: be.norm_sq_dev(pool[i % 8].data, out=scal[0:2]))
+        emit("f1-norm norm(theta)", ms, nb, "GB/s", peak_hbm)
+        ms = graph_time(lambda i: be.linear_combination(0.3, pool[(3 * i) % 8].data, -1.7, pool[(3 * i + 1) % 8].data))
+        emit("f1-lincomb linear_combination(a, theta, b, theta')", ms, 3 * nb, "GB/s", peak_hbm)
+        ms = graph_time(lambda i: be.lincomb3_dev([pool[(4 * i) % 8].data, pool[(4 * i + 1) % 8].data, pool[(4 * i + 2) % 8].data],
+                                                  [1.0, -1.0, -0.5], coef_dev=[None, scal[0:2], None], sumsq=scal[2:3],
+                                                  out=pool[(4 * i + 3) % 8].data))
+        emit("f1-lanczos3 w - alpha v - beta v' and its norm (fused, alpha on device)", ms, 4 * nb, "GB/s", peak_hbm)
+        u_, s_, vh_ = ct.svd(TH)
+        touch(u_)
+        upool = [clone(u_, 1.0) for _ in range(8)]
+        ms = graph_time(lambda i: be.scale_axis(upool[i % 8].data, s_.data, 2))
+        emit("f1-scale scale_axis(U, S, -1)", ms, 2.0 * u_.data.nbytes(), "GB/s", peak_hbm)
+        if cx:
+            ms = graph_time(lambda i: be.dagger(pool[i % 8].data))
+            emit("f1-dagger dagger(theta)", ms, 2 * nb, "GB/s", peak_hbm)
+
     # ---- the reference on the host cores, same inputs ----
     ref = {}
     if not args.no_ref and list((ROOT / "oracle" / "_ref" / "cyten").glob("_core*.so")):
@@ -230,6 +282,19 @@ def main():
             "a9": lambda: rc.qr(rA),
             "a10": lambda: rc.eigh(rH, ["a", "b", "c"], False),
         }
+        if "blas1" in rows:
+            rT2 = 1.1 * rT
+            rT3 = 1.2 * rT
+            rU, rS, rVh = rc.svd(rT)
+            lin = rc.tensors.linear_combination
+            calls.update({
+                "f1-inner": lambda: rc.inner(rT, rT2),
+                "f1-norm": lambda: rc.norm(rT),
+                "f1-lincomb": lambda: lin(0.3, rT, -1.7, rT2),
+                "f1-lanczos3": lambda: rc.norm(lin(1.0, lin(1.0, rT, -0.7, rT2), -0.5, rT3)),
+                "f1-scale": lambda: rc.scale_axis(rU, rS, 2),
+                "f1-dagger": lambda: force(rc.dagger(rT)),
+            })
         for o in out:
             key = o["row"].split()[0]
             try:
