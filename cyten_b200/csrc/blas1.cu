@@ -17,28 +17,60 @@ namespace cyb {
 constexpr int B1_THREADS = 256;
 constexpr int B1_CHUNK = 512;        // double2 pairs per chunk: 8 KB per operand, 16 pairs per lane
 constexpr int B1_MAX_GRID = 148 * 8;
+constexpr int B1_BATCH = 8;           // loads issued back to back per operand before the first use
 
 struct B1Seg {                        // device view of the segment table
     const int64_t* seg;               // [nseg][ncol]: operand offsets (elements, -1 = block absent), then size
     const int64_t* chunk0;            // [nseg + 1]: first chunk of every segment
     int nseg, ncol;
     int64_t nchunk;
+    int staged;                       // tables fit the dynamic shared memory of the launch
 };
 
-__device__ __forceinline__ int b1_find(const int64_t* __restrict__ chunk0, int nseg, int64_t c)
+__device__ __forceinline__ int b1_find(const int64_t* chunk0, int nseg, int64_t c)
 {
     int lo = 0, hi = nseg;            // chunk0[lo] <= c < chunk0[hi]
     while (hi - lo > 1) {
         const int mid = (lo + hi) >> 1;
-        if (__ldg(chunk0 + mid) <= c) lo = mid; else hi = mid;
+        if (chunk0[mid] <= c) lo = mid; else hi = mid;
     }
     return lo;
+}
+
+// The tables are read by every warp for every chunk and a binary search is a chain of dependent loads: from global
+// memory that is ~10 L2 round trips (5-8 us on a 20 us kernel).  They are staged in shared memory when they fit.
+constexpr size_t B1_SMEM_MAX = 64 * 1024;
+extern __shared__ int64_t b1_smem[];
+
+__device__ __forceinline__ void b1_stage(const int64_t*& prefix, const int64_t*& rows, int nseg, int ncol, int staged)
+{
+    if (!staged) return;
+    for (int i = threadIdx.x; i <= nseg; i += blockDim.x) b1_smem[i] = prefix[i];
+    for (int i = threadIdx.x; i < nseg * ncol; i += blockDim.x) b1_smem[nseg + 1 + i] = rows[i];
+    __syncthreads();
+    prefix = b1_smem;
+    rows = b1_smem + nseg + 1;
+}
+
+static size_t b1_smem_bytes(int64_t nseg, int ncol)
+{
+    const size_t need = (size_t)(nseg + 1 + nseg * ncol) * sizeof(int64_t);
+    return need <= B1_SMEM_MAX ? need : 0;
 }
 
 __device__ __forceinline__ double2 b1_ld(const double* p, int64_t d, int64_t nd)
 {
     if (d + 1 < nd) return *reinterpret_cast<const double2*>(p + d);
     return make_double2(p[d], 0.0);
+}
+
+// predicated variant: zero beyond the end of the block (a zero contributes nothing to a dot product or a sum)
+__device__ __forceinline__ double2 b1_ldz(const double* p, int64_t d, int64_t nd)
+{
+    double2 r = make_double2(0.0, 0.0);
+    if (d + 1 < nd) r = *reinterpret_cast<const double2*>(p + d);
+    else if (d < nd) r.x = p[d];
+    return r;
 }
 
 __device__ __forceinline__ double2 cmul(double2 a, double2 b) { return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
@@ -97,24 +129,35 @@ __global__ void __launch_bounds__(B1_THREADS) block_dot_kernel(const double* __r
     const int64_t warp0 = (int64_t)blockIdx.x * (B1_THREADS / 32) + (threadIdx.x >> 5);
     const int64_t nwarp = (int64_t)gridDim.x * (B1_THREADS / 32);
     double acc[2] = {0.0, 0.0};
+    const int64_t *chunk0 = T.chunk0, *seg = T.seg;
+    b1_stage(chunk0, seg, T.nseg, T.ncol, T.staged);
     for (int64_t c = warp0; c < T.nchunk; c += nwarp) {
-        const int s = b1_find(T.chunk0, T.nseg, c);
-        const int64_t* row = T.seg + (size_t)s * T.ncol;
-        const int64_t ox = __ldg(row), oy = __ldg(row + 1), nd = __ldg(row + 2) * ES;
+        const int s = b1_find(chunk0, T.nseg, c);
+        const int64_t* row = seg + (size_t)s * T.ncol;
+        const int64_t ox = row[0], oy = row[1], nd = row[2] * ES;
         const double* px = x + ox * ES;
         const double* py = y + oy * ES;
-        const int64_t d0 = (c - __ldg(T.chunk0 + s)) * (2 * B1_CHUNK);
-#pragma unroll 4
-        for (int j = 0; j < B1_CHUNK / 32; ++j) {
-            const int64_t d = d0 + (int64_t)(j * 32 + lane) * 2;
-            if (d >= nd) break;
-            const double2 a = b1_ld(px, d, nd), b = b1_ld(py, d, nd);
-            if (CX) {
-                const double ay = (conj_x & 1) ? -a.y : a.y;
-                acc[0] += a.x * b.x - ay * b.y;
-                acc[1] += a.x * b.y + ay * b.x;
-            } else {
-                acc[0] += a.x * b.x + a.y * b.y;
+        const int64_t d0 = (c - chunk0[s]) * (2 * B1_CHUNK);
+        // all loads of a batch are issued before the first use: 8 x 2 x 16 B in flight per thread
+#pragma unroll
+        for (int j0 = 0; j0 < B1_CHUNK / 32; j0 += B1_BATCH) {
+            if (d0 + (int64_t)(j0 * 32) * 2 >= nd) break;             // warp-uniform
+            double2 a[B1_BATCH], b[B1_BATCH];
+#pragma unroll
+            for (int j = 0; j < B1_BATCH; ++j) {
+                const int64_t d = d0 + (int64_t)((j0 + j) * 32 + lane) * 2;
+                a[j] = b1_ldz(px, d, nd);
+                b[j] = b1_ldz(py, d, nd);
+            }
+#pragma unroll
+            for (int j = 0; j < B1_BATCH; ++j) {
+                if (CX) {
+                    const double ay = (conj_x & 1) ? -a[j].y : a[j].y;
+                    acc[0] += a[j].x * b[j].x - ay * b[j].y;
+                    acc[1] += a[j].x * b[j].y + ay * b[j].x;
+                } else {
+                    acc[0] += a[j].x * b[j].x + a[j].y * b[j].y;
+                }
             }
         }
     }
@@ -148,32 +191,45 @@ __global__ void __launch_bounds__(B1_THREADS) block_lincomb_kernel(const double*
     }
     const double* ops[3] = {x, y, z};
     double acc[1] = {0.0};
+    const int64_t *chunk0 = T.chunk0, *seg = T.seg;
+    b1_stage(chunk0, seg, T.nseg, T.ncol, T.staged);
     for (int64_t c = warp0; c < T.nchunk; c += nwarp) {
-        const int s = b1_find(T.chunk0, T.nseg, c);
-        const int64_t* row = T.seg + (size_t)s * T.ncol;
+        const int s = b1_find(chunk0, T.nseg, c);
+        const int64_t* row = seg + (size_t)s * T.ncol;
         const double* p[3];
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
-            const int64_t off = __ldg(row + i);
+            const int64_t off = row[i];
             p[i] = (ops[i] != nullptr && off >= 0) ? ops[i] + off * ES : nullptr;
         }
-        double* po = o + __ldg(row + 3) * ES;
-        const int64_t nd = __ldg(row + 4) * ES;
-        const int64_t d0 = (c - __ldg(T.chunk0 + s)) * (2 * B1_CHUNK);
-#pragma unroll 4
-        for (int j = 0; j < B1_CHUNK / 32; ++j) {
-            const int64_t d = d0 + (int64_t)(j * 32 + lane) * 2;
-            if (d >= nd) break;
-            double2 r = make_double2(0.0, 0.0);
+        double* po = o + row[3] * ES;
+        const int64_t nd = row[4] * ES;
+        const int64_t d0 = (c - chunk0[s]) * (2 * B1_CHUNK);
+#pragma unroll
+        for (int j0 = 0; j0 < B1_CHUNK / 32; j0 += B1_BATCH / 2) {
+            if (d0 + (int64_t)(j0 * 32) * 2 >= nd) break;             // warp-uniform
+            double2 v[3][B1_BATCH / 2];
 #pragma unroll
             for (int i = 0; i < 3; ++i) {
-                if (p[i] == nullptr) continue;
-                const double2 v = b1_ld(p[i], d, nd);
-                if (CX) { const double2 t = cmul(k[i], v); r.x += t.x; r.y += t.y; }
-                else    { r.x += k[i].x * v.x; r.y += k[i].x * v.y; }
+                if (p[i] == nullptr) continue;                        // warp-uniform
+#pragma unroll
+                for (int j = 0; j < B1_BATCH / 2; ++j)
+                    v[i][j] = b1_ldz(p[i], d0 + (int64_t)((j0 + j) * 32 + lane) * 2, nd);
             }
-            if (d + 1 < nd) *reinterpret_cast<double2*>(po + d) = r; else po[d] = r.x;
-            if (NORM) acc[0] += r.x * r.x + (d + 1 < nd ? r.y * r.y : 0.0);
+#pragma unroll
+            for (int j = 0; j < B1_BATCH / 2; ++j) {
+                const int64_t d = d0 + (int64_t)((j0 + j) * 32 + lane) * 2;
+                if (d >= nd) break;
+                double2 r = make_double2(0.0, 0.0);
+#pragma unroll
+                for (int i = 0; i < 3; ++i) {
+                    if (p[i] == nullptr) continue;
+                    if (CX) { const double2 t = cmul(k[i], v[i][j]); r.x += t.x; r.y += t.y; }
+                    else    { r.x += k[i].x * v[i][j].x; r.y += k[i].x * v[i][j].y; }
+                }
+                if (d + 1 < nd) *reinterpret_cast<double2*>(po + d) = r; else po[d] = r.x;
+                if (NORM) acc[0] += r.x * r.x + (d + 1 < nd ? r.y * r.y : 0.0);
+            }
         }
     }
     if (NORM) b1_finish<1>(acc, partial, counter, sumsq);
@@ -183,19 +239,20 @@ __global__ void __launch_bounds__(B1_THREADS) block_lincomb_kernel(const double*
 // desc int64[nblk][6] = (off_in, off_out, outer, dleg, inner, d_off)
 template <bool CX, bool DCX>
 __global__ void __launch_bounds__(B1_THREADS) scale_axis_kernel(const double* __restrict__ in, double* __restrict__ out,
-                                                                const int64_t* __restrict__ desc, const double* __restrict__ dg,
-                                                                const int64_t* __restrict__ work0, int nblk, int64_t nwork)
+                                                                const int64_t* desc, const double* __restrict__ dg,
+                                                                const int64_t* work0, int nblk, int64_t nwork, int staged)
 {
     constexpr int ES = CX ? 2 : 1;
+    b1_stage(work0, desc, nblk, 6, staged);
     // work item = 1024 consecutive elements of one block
     for (int64_t w = blockIdx.x; w < nwork; w += gridDim.x) {
         const int b = b1_find(work0, nblk, w);
         const int64_t* D = desc + (size_t)b * 6;
-        const int64_t dleg = __ldg(D + 3), inner = __ldg(D + 4), n = __ldg(D + 2) * dleg * inner;
-        const double* pi = in + __ldg(D) * ES;
-        double* po = out + __ldg(D + 1) * ES;
-        const double* pd = dg + __ldg(D + 5) * (DCX ? 2 : 1);
-        const int64_t e0 = (w - __ldg(work0 + b)) * 1024;
+        const int64_t dleg = D[3], inner = D[4], n = D[2] * dleg * inner;
+        const double* pi = in + D[0] * ES;
+        double* po = out + D[1] * ES;
+        const double* pd = dg + D[5] * (DCX ? 2 : 1);
+        const int64_t e0 = (w - work0[b]) * 1024;
 #pragma unroll
         for (int j = 0; j < 1024 / B1_THREADS; ++j) {
             const int64_t e = e0 + j * B1_THREADS + threadIdx.x;
@@ -219,6 +276,24 @@ static int b1_grid(int64_t nchunk)
     return (int)std::max<int64_t>(1, std::min<int64_t>(want, std::min<int64_t>(cap, B1_MAX_GRID)));
 }
 
+// dynamic shared memory above 48 KB is opt-in per kernel; done once per process
+static cudaError_t b1_attr()
+{
+    static cudaError_t done = [] {
+        cudaError_t e = cudaSuccess;
+        auto set = [&](const void* f) {
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)B1_SMEM_MAX);
+        };
+        set((const void*)block_dot_kernel<true>); set((const void*)block_dot_kernel<false>);
+        set((const void*)block_lincomb_kernel<true, true>); set((const void*)block_lincomb_kernel<true, false>);
+        set((const void*)block_lincomb_kernel<false, true>); set((const void*)block_lincomb_kernel<false, false>);
+        set((const void*)scale_axis_kernel<true, true>); set((const void*)scale_axis_kernel<true, false>);
+        set((const void*)scale_axis_kernel<false, false>);
+        return e;
+    }();
+    return done;
+}
+
 }  // namespace cyb
 
 using namespace cyb;
@@ -236,14 +311,16 @@ int cyb_block_dot(const void* x, const void* y, const int64_t* seg, const int64_
     CYB_REQUIRE(out != nullptr && work != nullptr, "block_dot: out / work must not be null");
     cudaStream_t stream = (cudaStream_t)stream_;
     if (nseg == 0 || nchunk == 0) { CYB_CHECK_CUDA(cudaMemsetAsync(out, 0, 2 * sizeof(double), stream)); return CYB_OK; }
-    B1Seg T{seg, chunk0, (int)nseg, 3, nchunk};
+    const size_t smem = b1_smem_bytes(nseg, 3);
+    B1Seg T{seg, chunk0, (int)nseg, 3, nchunk, smem != 0};
     double* partial = static_cast<double*>(work);
     unsigned* counter = reinterpret_cast<unsigned*>(static_cast<char*>(work) + B1_MAX_GRID * 2 * sizeof(double));
     const int grid = b1_grid(nchunk);
+    CYB_CHECK_CUDA(b1_attr());
     if (dtype == CYB_C128)
-        block_dot_kernel<true><<<grid, B1_THREADS, 0, stream>>>((const double*)x, (const double*)y, T, conj_x, partial, counter, out);
+        block_dot_kernel<true><<<grid, B1_THREADS, smem, stream>>>((const double*)x, (const double*)y, T, conj_x, partial, counter, out);
     else
-        block_dot_kernel<false><<<grid, B1_THREADS, 0, stream>>>((const double*)x, (const double*)y, T, conj_x, partial, counter, out);
+        block_dot_kernel<false><<<grid, B1_THREADS, smem, stream>>>((const double*)x, (const double*)y, T, conj_x, partial, counter, out);
     CYB_LAUNCH_CHECK();
     return CYB_OK;
 }
@@ -260,7 +337,9 @@ int cyb_block_lincomb(const void* x, const void* y, const void* z, void* out, co
         if (sumsq) CYB_CHECK_CUDA(cudaMemsetAsync(sumsq, 0, sizeof(double), stream));
         return CYB_OK;
     }
-    B1Seg T{seg, chunk0, (int)nseg, 5, nchunk};
+    const size_t smem = b1_smem_bytes(nseg, 5);
+    B1Seg T{seg, chunk0, (int)nseg, 5, nchunk, smem != 0};
+    CYB_CHECK_CUDA(b1_attr());
     B1Coef K;
     for (int i = 0; i < 3; ++i) {
         K.c[i][0] = coef[2 * i]; K.c[i][1] = coef[2 * i + 1];
@@ -272,10 +351,10 @@ int cyb_block_lincomb(const void* x, const void* y, const void* z, void* out, co
     const double *px = (const double*)x, *py = (const double*)y, *pz = (const double*)z;
     double* po = (double*)out;
     const bool cx = dtype == CYB_C128;
-    if (cx && sumsq)        block_lincomb_kernel<true, true><<<grid, B1_THREADS, 0, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
-    else if (cx)            block_lincomb_kernel<true, false><<<grid, B1_THREADS, 0, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
-    else if (sumsq)         block_lincomb_kernel<false, true><<<grid, B1_THREADS, 0, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
-    else                    block_lincomb_kernel<false, false><<<grid, B1_THREADS, 0, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
+    if (cx && sumsq)        block_lincomb_kernel<true, true><<<grid, B1_THREADS, smem, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
+    else if (cx)            block_lincomb_kernel<true, false><<<grid, B1_THREADS, smem, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
+    else if (sumsq)         block_lincomb_kernel<false, true><<<grid, B1_THREADS, smem, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
+    else                    block_lincomb_kernel<false, false><<<grid, B1_THREADS, smem, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
     CYB_LAUNCH_CHECK();
     return CYB_OK;
 }
@@ -288,14 +367,17 @@ int cyb_scale_axis(const void* in, void* out, const int64_t* desc, const int64_t
     if (nblk == 0 || nwork == 0) return CYB_OK;
     cudaStream_t stream = (cudaStream_t)stream_;
     const int grid = (int)std::min<int64_t>(nwork, (int64_t)sm_count() * 8);
+    const size_t smem = b1_smem_bytes(nblk, 6);
+    const int staged = smem != 0;
+    CYB_CHECK_CUDA(b1_attr());
     const double *pi = (const double*)in, *pd = (const double*)diag;
     double* po = (double*)out;
     if (dtype == CYB_C128 && diag_dtype == CYB_C128)
-        scale_axis_kernel<true, true><<<grid, B1_THREADS, 0, stream>>>(pi, po, desc, pd, work0, (int)nblk, nwork);
+        scale_axis_kernel<true, true><<<grid, B1_THREADS, smem, stream>>>(pi, po, desc, pd, work0, (int)nblk, nwork, staged);
     else if (dtype == CYB_C128)
-        scale_axis_kernel<true, false><<<grid, B1_THREADS, 0, stream>>>(pi, po, desc, pd, work0, (int)nblk, nwork);
+        scale_axis_kernel<true, false><<<grid, B1_THREADS, smem, stream>>>(pi, po, desc, pd, work0, (int)nblk, nwork, staged);
     else
-        scale_axis_kernel<false, false><<<grid, B1_THREADS, 0, stream>>>(pi, po, desc, pd, work0, (int)nblk, nwork);
+        scale_axis_kernel<false, false><<<grid, B1_THREADS, smem, stream>>>(pi, po, desc, pd, work0, (int)nblk, nwork, staged);
     CYB_LAUNCH_CHECK();
     return CYB_OK;
 }

@@ -38,12 +38,22 @@ class GraphedOperator:
     def __init__(self, op, warmup: int = 3):
         self.op, self.warmup, self._steps = op, warmup, {}
 
-    def matvec(self, vec: SymmetricTensor) -> SymmetricTensor:
+    def _step(self, vec: SymmetricTensor) -> CapturedStep:
         step = self._steps.get(vec.data.sig)
         if step is None:
             static = SymmetricTensor(_clone(vec.data), vec.codomain, vec.domain, vec.backend, vec.labels)
             step = self._steps[vec.data.sig] = CapturedStep(self.op.matvec, static, warmup=self.warmup)
-        step.input.data.buf.copy_(vec.data.buf)
+        return step
+
+    def input_like(self, vec: SymmetricTensor) -> SymmetricTensor:
+        """The graph's static input tensor for vectors of this structure: a caller that PRODUCES the vector (the
+        normalisation of a Lanczos step) writes it there directly and saves the copy."""
+        return self._step(vec).input
+
+    def matvec(self, vec: SymmetricTensor) -> SymmetricTensor:
+        step = self._step(vec)
+        if vec is not step.input:
+            step.input.data.buf.copy_(vec.data.buf)
         return step()
 
 
@@ -79,7 +89,7 @@ class LanczosGroundState:
         self.h_krylov = np.zeros((n, n))
         self.Es = np.zeros((self.N_max, self.N_max))
         self._result_krylov = np.ones(1)
-        self._cache: list[SymmetricTensor] = []
+        self._cache: list = []                                   # (u_k, beta_k): v_k = u_k / beta_k
         self.host_syncs = 0
         dev = self.be.device
         self._scal = torch.zeros(4, dtype=torch.float64, device=dev)      # (alpha, 0 | ||u'||^2, 0)
@@ -105,32 +115,45 @@ class LanczosGroundState:
         cannot reach, or new ones) is brought to v's layout + its own extra blocks by one linear_combination."""
         return w if w.data.sig == v.data.sig else linear_combination(1.0, w, 0.0, v)
 
-    def _three_term(self, w, v, v_prev, beta):
-        """alpha = Re<v, w> (device) ; u' = w - alpha v - beta v_prev ; ||u'||^2 -- two launches, no sync."""
+    def _normalised(self, u, b):
+        """v = u / b, written straight into the operator's static input arena when it has one (GraphedOperator)."""
+        static = getattr(self.H, "input_like", None)
+        if static is not None and self.E_shift is None:
+            v = static(u)
+            self.be.lincomb3_dev([u.data, None, None], [1.0 / b, 0.0, 0.0], out=v.data)
+            return v
+        return u if b == 1.0 else scalar_multiply(1.0 / b, u)
+
+    def _three_term(self, w, v, prev, b):
+        """alpha = Re<v, w> (device) ; u' = w - alpha v - b v_prev ; ||u'||^2 -- two launches, no sync.
+        ``prev = (u_prev, b_prev)``: the cache holds the UNNORMALISED vectors, v_prev = u_prev / b_prev."""
         be = self.be
         alpha, ss = self._scal[0:2], self._scal[2:3]
         be.inner_dev(v.data, w.data, True, real_only=True, out=alpha)
-        if w.data.sig == v.data.sig and (v_prev is None or v_prev.data.sig == v.data.sig):
-            ops = [w.data, v.data, None if v_prev is None else v_prev.data]
-            u = be.lincomb3_dev(ops, [1.0, -1.0, -float(beta)], coef_dev=[None, alpha, None], sumsq=ss)
+        same = w.data.sig == v.data.sig and (prev is None or prev[0].data.sig == v.data.sig)
+        if same:
+            ops = [w.data, v.data, None if prev is None else prev[0].data]
+            u = be.lincomb3_dev(ops, [1.0, -1.0, 0.0 if prev is None else -b / prev[1]], coef_dev=[None, alpha, None], sumsq=ss)
             return self._wrap(u, v)
         # general block structures (w gained or lost blocks): reference semantics through linear_combination
         a = float(alpha[0].item())
         self.host_syncs += 1
         u = linear_combination(1.0, w, -a, v)
-        if v_prev is not None:
-            u = linear_combination(1.0, u, -float(beta), v_prev)
+        if prev is not None:
+            u = linear_combination(1.0, u, -b / prev[1], prev[0])
         be.norm_sq_dev(u.data, out=self._scal[2:4])
         return u
 
     def _reorthogonalise(self, u):
+        """u -= <v_i, u> v_i for the cached vectors but the last: <v_i, u> v_i = <u_i, u> u_i / b_i^2, the raw overlap
+        stays on the device."""
         be = self.be
-        for c in self._cache[:-1]:
+        for c, bc in self._cache[:-1]:
             if c.data.sig == u.data.sig:
                 be.inner_dev(c.data, u.data, True, out=self._ov)
-                be.lincomb3_dev([u.data, c.data, None], [1.0, -1.0, 0.0], coef_dev=[None, self._ov, None], out=u.data)
+                be.lincomb3_dev([u.data, c.data, None], [1.0, -1.0 / bc ** 2, 0.0], coef_dev=[None, self._ov, None], out=u.data)
             else:
-                u = linear_combination(1.0, u, -be.inner(c.data, u.data), c)
+                u = linear_combination(1.0, u, -be.inner(c.data, u.data) / bc ** 2, c)
         if self._cache[:-1]:
             be.norm_sq_dev(u.data, out=self._scal[2:4])
         return u
@@ -156,21 +179,21 @@ class LanczosGroundState:
         self.host_syncs += 1
         if beta < self.cutoff:
             raise ValueError(f"Norm of self.psi0 too small: {beta}")
-        self.psi0 = scalar_multiply(1.0 / beta, u)
-        u, beta_prev, performed = self.psi0, 0.0, 0
+        self.psi0 = u = scalar_multiply(1.0 / beta, u)
+        beta, performed = 1.0, 0
         for k in range(self.N_max):
-            v = u if k == 0 else scalar_multiply(1.0 / beta, u)
-            self._to_cache(v)
+            v = self._normalised(u, beta)
+            self._to_cache((u, beta))                              # v_k = u_k / beta_k
             w = self._same_structure(self._matvec(v), v)
-            v_prev = self._cache[-2] if (k > 0 and not self.reortho) else None
-            u = self._three_term(w, v, v_prev, beta if k > 0 else 0.0)
+            prev = self._cache[-2] if (k > 0 and not self.reortho) else None
+            u = self._three_term(w, v, prev, beta)
             if self.reortho:
                 u = self._reorthogonalise(u)
             alpha, _, ss, _ = self._scal.tolist()                  # the one synchronisation of the iteration
             self.host_syncs += 1
             self.h_krylov[k, k] = alpha
             self._calc_result_krylov(k)
-            beta_prev, beta = beta, float(np.sqrt(max(ss, 0.0)))
+            beta = float(np.sqrt(max(ss, 0.0)))
             self.h_krylov[k, k + 1] = self.h_krylov[k + 1, k] = beta
             performed = k + 1
             if abs(beta) < self.cutoff or (k + 1 >= self.N_min and self._converged(k)):
@@ -180,18 +203,18 @@ class LanczosGroundState:
     def _rebuild(self, psif, n_rebuild):
         """Vectors that fell out of the cache are regenerated with the known alpha / beta: no synchronisation."""
         vf = self._result_krylov
-        v, beta = self.psi0, 0.0
+        v, v_prev, beta, vs = self.psi0, None, 0.0, []
         for k in range(n_rebuild):
-            self._to_cache(v)
             w = self._same_structure(self._matvec(v), v)
             u = linear_combination(1.0, w, -self.h_krylov[k, k], v)
             if self.reortho:
-                for c in self._cache[:-1]:
+                for c in vs[-self.N_cache:]:
                     u = linear_combination(1.0, u, -self.be.inner(c.data, u.data), c)
             elif k > 0:
-                u = linear_combination(1.0, u, -beta, self._cache[-2])
+                u = linear_combination(1.0, u, -beta, v_prev)
+            vs.append(v)
             beta = self.h_krylov[k, k + 1]
-            v = scalar_multiply(1.0 / beta, u)
+            v_prev, v = v, scalar_multiply(1.0 / beta, u)
             psif = linear_combination(1.0, psif, vf[k + 1], v)
         return psif
 
@@ -200,7 +223,8 @@ class LanczosGroundState:
         psif = scalar_multiply(vf[0], self.psi0)
         len_cache = len(self._cache)
         for k in range(1, min(len_cache + 1, N)):
-            psif = linear_combination(1.0, psif, vf[N - k], self._cache[len_cache - k])
+            u, b = self._cache[len_cache - k]
+            psif = linear_combination(1.0, psif, vf[N - k] / b, u)
         self._cache = []
         psif = self._rebuild(psif, N - len_cache - 1)
         nrm = norm(psif)
