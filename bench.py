@@ -286,7 +286,9 @@ def run_b200(args):
     pg = sh.attach_process_group(be, dist.group.WORLD if world > 1 else None)
     chi = args.chi
     H, theta_full, host, sp = build_heff(chi, be)
-    SH = sh.ShardedHEffective(H, pg, split_heavy=os.environ.get("CYB_SPLIT_HEAVY", "0") == "1")
+    SH = sh.ShardedHEffective(H, pg, split_heavy=os.environ.get("CYB_SPLIT_HEAVY", "0") == "1",
+                              split_columns=os.environ.get("CYB_SPLIT_COLUMNS", "1") == "1",
+                              column_heavy=float(os.environ.get("CYB_COL_HEAVY", "0.35")))
     # multi-GPU: theta lives sharded along the sectors of vR (LPT by block volume); the matvec chain is
     # rank-local until vR is contracted, then one all_reduce of the (small) result arena
     theta = SH.shard(theta_full) if world > 1 else theta_full

@@ -109,6 +109,94 @@ def take_blocks(T: SymmetricTensor, which) -> SymmetricTensor:
     return SymmetricTensor(res, T.codomain, T.domain, be, T.labels)
 
 
+def slice_leg(T: SymmetricTensor, leg, ranges: dict) -> SymmetricTensor:
+    """T restricted along one leg to the index range ``ranges[sector] = (start, stop)`` of every listed sector
+    (sectors not listed drop out): a tensor on a NARROWER leg (same sectors, smaller multiplicities).  Every
+    operation is linear in each leg, so a tensor cut into such slabs along an open or a contracted leg (with the
+    partner cut the same way) gives partial results that add up -- the finer-than-sector unit of the multi-GPU
+    split.  One strided block-copy launch; the job list is a cached plan."""
+    from .backend import _c_strides
+    from .spaces import ElementarySpace, TensorProduct
+    be = T.backend
+    ax = T.get_leg_idcs([leg])[0]
+    d = T.data
+    key = ("slice", d.sig, ax, tuple(sorted((int(k), int(a), int(b)) for k, (a, b) in ranges.items())))
+    plan = be._plan_get(key)
+    ncod = T.num_codomain_legs
+    old_leg = conventional_leg_order(T.codomain, T.domain)[ax]
+    kept = np.asarray(sorted(int(k) for k in ranges), dtype=np.int64)
+    if plan is None:
+        remap = np.full(old_leg.num_sectors, -1, dtype=np.int64)
+        remap[kept] = np.arange(len(kept))
+        which = np.nonzero(remap[d.block_inds[:, ax]] >= 0)[0]
+        bi = d.block_inds[which].copy()
+        secs = bi[:, ax].copy()
+        bi[:, ax] = remap[secs]
+        start = np.asarray([ranges[int(q)][0] for q in secs], dtype=np.int64)
+        stop = np.asarray([ranges[int(q)][1] for q in secs], dtype=np.int64)
+        old_shapes = d.shapes[which]
+        if np.any(start < 0) or np.any(stop > old_shapes[:, ax]) or np.any(stop <= start):
+            raise ValueError("slice_leg: range outside the sector")
+        shapes = old_shapes.copy()
+        shapes[:, ax] = stop - start
+        res = be._empty(d.dtype, be.device, bi, shapes)
+        st_old = _c_strides(old_shapes)
+        prepared = (0, None)
+        if len(which):
+            prepared = be._prepare_copy(be._make_jobs(d.offsets[which] + start * st_old[:, ax], res.offsets, shapes,
+                                                      st_old, _c_strides(shapes)))
+        plan = dict(bi=res.block_inds, shapes=res.shapes, copy=prepared, sig=res.sig)
+        if not be.dry_run:
+            be._plan_put(key, plan)
+    else:
+        res = be._empty(d.dtype, be.device, plan["bi"], plan["shapes"])
+        res._sig = plan["sig"]
+    be._run_copy(d.buf, res.buf, plan["copy"], d.cyb_dtype)
+    new_leg = ElementarySpace(old_leg.symmetry, old_leg.defining_sectors[kept],
+                              np.asarray([ranges[int(k)][1] - ranges[int(k)][0] for k in kept], dtype=np.int64), old_leg.is_dual)
+    cod, dom = list(T.codomain.factors), list(T.domain.factors)
+    if ax < ncod:
+        cod[ax] = new_leg
+    else:
+        dom[T.num_legs - 1 - ax] = new_leg
+    return SymmetricTensor(res, TensorProduct(cod, symmetry=T.symmetry), TensorProduct(dom, symmetry=T.symmetry), be, T.labels)
+
+
+def column_ranges(costs, mults, world: int, heavy: float = 0.6, align: int = 16):
+    """Work items for a split finer than sectors: a sector whose cost exceeds ``heavy`` x (one rank's share) is cut
+    into equal index ranges (multiples of ``align``), the items go to ranks by LPT, and the parts of one sector
+    that land on the same rank are made adjacent so that every rank holds at most ONE range per sector.
+    Returns ``ranges[rank] = {sector: (start, stop)}``; identical on every rank (integer bookkeeping)."""
+    costs = np.asarray(costs, dtype=np.float64)
+    mults = np.asarray(mults, dtype=np.int64)
+    ideal = float(costs.sum()) / world
+    items = []                                           # (cost, sector, number of align-units)
+    for s, (c, m) in enumerate(zip(costs, mults)):
+        if c <= 0 or m <= 0:
+            continue
+        units = max(1, int(m) // align)
+        nparts = int(min(units, np.ceil(c / (heavy * ideal)))) if c > heavy * ideal else 1
+        base, extra = divmod(units, nparts)
+        for k in range(nparts):
+            u = base + (1 if k < extra else 0)
+            items.append((c * u / units, s, u))
+    owner = lpt_assign(np.asarray([it[0] for it in items]), world)
+    ranges = [dict() for _ in range(world)]
+    for s in sorted({it[1] for it in items}):
+        m = int(mults[s])
+        units_of_rank = np.zeros(world, dtype=np.int64)
+        for (c, ss, u), o in zip(items, owner):
+            if ss == s:
+                units_of_rank[o] += u
+        pos = 0
+        holders = [r for r in range(world) if units_of_rank[r] > 0]
+        for i, r in enumerate(holders):
+            width = int(units_of_rank[r]) * align if i + 1 < len(holders) else m - pos      # the last holder takes the remainder
+            ranges[r][s] = (pos, pos + width)
+            pos += width
+    return ranges
+
+
 def sector_owner_of_leg(T: SymmetricTensor, leg, world: int):
     """LPT owner of every sector of leg ``leg`` (label or index) of T; cost of a sector = number of
     elements in the blocks carrying it (proportional to the flops those blocks cause downstream)."""
@@ -233,9 +321,35 @@ class ShardedHEffective:
     contractions leave ``vR`` open and are rank-local; the last one contracts ``vR`` with RP, so each
     rank holds a partial sum over its ``vR`` sectors and one all_reduce finishes the matvec."""
 
-    def __init__(self, H, pg: ProcessGroup, shard_leg="vR", split_heavy=False):
+    def __init__(self, H, pg: ProcessGroup, shard_leg="vR", split_heavy=False, split_columns=False, column_align=16, column_heavy=0.6):
         self.H, self.pg, self.shard_leg, self.split_heavy = H, pg, shard_leg, split_heavy
+        self.split_columns, self.column_align, self.column_heavy = split_columns, column_align, column_heavy
         self.chains = [(H, None)]
+
+    def shard_columns(self, theta: SymmetricTensor) -> SymmetricTensor:
+        """Split finer than sectors: a heavy ``vR`` sector is cut into INDEX RANGES (``slice_leg``).  theta restricted
+        to a range of vR indices is a tensor on a narrower leg; the first three contractions keep that leg open and
+        the last contracts it with the same rows of RP, so rank r runs the unchanged chain on (theta_r, RP_r) and the
+        partial results add up in the all_reduce.  No flops are duplicated and the GEMMs keep their fat dimensions
+        (only the vR extent shrinks), unlike the row-sector split of ``split_heavy``."""
+        from .workloads import HEffective
+        H, pg = self.H, self.pg
+        costs = flop_costs_of_leg(theta, self.shard_leg, H.matvec)
+        self.costs = costs
+        ax = theta.get_leg_idcs([self.shard_leg])[0]
+        leg = conventional_leg_order(theta.codomain, theta.domain)[ax]
+        self.ranges = column_ranges(costs, leg.multiplicities, pg.world, heavy=self.column_heavy, align=self.column_align)
+        mine = self.ranges[pg.rank]
+        self.slice_of = (self.shard_leg, mine)
+        if not mine:                       # more ranks than work items: this rank contributes zeros
+            self.chains = []
+            self._empty_like = theta
+            return take_blocks(theta, np.zeros(0, np.int64))
+        theta_local = slice_leg(theta, self.shard_leg, mine)
+        rp_ax = 0                          # RP[vR, wR | vR']: its first codomain leg is contracted with theta's vR
+        RP_r = slice_leg(H.RP, rp_ax, mine)
+        self.chains = [(HEffective(H.LP, RP_r, H.W1, H.W2, H.ct), None)]
+        return theta_local
 
     def shard(self, theta: SymmetricTensor) -> SymmetricTensor:
         """Rank-local part of theta.  Work items are the sectors of ``shard_leg`` weighted by the flops each causes
@@ -250,6 +364,8 @@ class ShardedHEffective:
         self.chains = [(self.H, None)]
         if self.pg.world == 1:
             return theta
+        if self.split_columns:
+            return self.shard_columns(theta)
         from .workloads import HEffective
         H, pg = self.H, self.pg
         costs = flop_costs_of_leg(theta, self.shard_leg, H.matvec)
@@ -313,7 +429,7 @@ class ShardedHEffective:
                 with be._ctx():
                     be._call("cyb_axpby", ptr(y.data.buf), ptr(acc.data.buf), n, _lib.CYB_F64, 1.0, 1.0, be._stream())
         if acc is None:      # a rank without work (theta_local has no blocks): zeros on the full layout
-            acc = expand_to_full(self.H.matvec(theta_local))
+            acc = expand_to_full(self.H.matvec(take_blocks(getattr(self, "_empty_like", theta_local), np.zeros(0, np.int64))))
         return acc
 
     def matvec(self, theta_local: SymmetricTensor) -> SymmetricTensor:

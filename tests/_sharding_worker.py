@@ -57,6 +57,24 @@ def worker(rank, world, port, out_dir):
         assert np.allclose(d_got, d_want, rtol=0, atol=1e-12 * np.abs(d_want).max())
         res["matvec_max"] = float(np.abs(d_want).max())
 
+        # ---- the same with the heavy vR sectors cut into index ranges (slice_leg) ----
+        SC = sh.ShardedHEffective(H, pg, split_columns=True, column_align=2, column_heavy=0.25)
+        th_c = SC.shard(theta)
+        cover = torch.tensor([float(th_c.data.sizes.sum())], dtype=torch.float64)
+        dist.all_reduce(cover)
+        assert float(cover.item()) == float(theta.data.sizes.sum())          # every element of theta on exactly one rank
+        be.plan_mkn = []
+        got_c = SC.matvec(th_c)
+        fl = torch.tensor([float(sum(be.plan_mkn))], dtype=torch.float64)
+        be.plan_mkn = None
+        dist.all_reduce(fl)
+        assert float(fl.item()) == fl_full, "the column split must not duplicate flops"
+        assert np.array_equal(got_c.data.block_inds, full_want.data.block_inds)
+        d_c = _dense_of(got_c)
+        assert np.allclose(d_c, d_want, rtol=0, atol=1e-12 * np.abs(d_want).max())
+        nsplit = sum(1 for r in SC.ranges for s, (a, b) in r.items() if (a, b) != (0, int(theta.domain.factors[0].multiplicities[s])))
+        assert nsplit >= 2, "the test must exercise a sector that is cut into ranges"
+
         # ---- tdot with the output blocks partitioned over the ranks ----
         v, p = u1_bond_leg(48, 3, 1.2), u1_phys_leg()
         A, B = mps_tensor(v, p, v, be, seed=1), mps_tensor(v, p, v, be, seed=2)

@@ -13,7 +13,8 @@ if os.environ.get("SHARD"):     # "r/N": the rank-local part of the sharded matv
     r, N = (int(x) for x in os.environ["SHARD"].split("/"))
     pg = sh.ProcessGroup(None)
     pg.rank, pg.world = r, N
-    SH = sh.ShardedHEffective(H, pg, split_heavy=os.environ.get("SPLIT", "0") == "1")
+    SH = sh.ShardedHEffective(H, pg, split_heavy=os.environ.get("SPLIT", "0") == "1",
+                              split_columns=os.environ.get("COLS", "1") == "1")
     theta = SH.shard(theta)    # flop-cost LPT (+ 2-D split of the heavy sectors)
     class _Loc:
         matvec = staticmethod(SH.matvec_local)
