@@ -15,7 +15,7 @@
 namespace cyb {
 
 constexpr int B1_THREADS = 256;
-constexpr int B1_CHUNK = 512;        // double2 pairs per chunk: 8 KB per operand, 16 pairs per lane
+constexpr int B1_CHUNK = 256;        // double2 pairs per chunk: 4 KB per operand, 8 pairs per lane (one batch of loads)
 constexpr int B1_MAX_GRID = 148 * 8;
 constexpr int B1_BATCH = 8;           // loads issued back to back per operand before the first use
 
@@ -253,11 +253,14 @@ __global__ void __launch_bounds__(B1_THREADS) scale_axis_kernel(const double* __
         double* po = out + D[1] * ES;
         const double* pd = dg + D[5] * (DCX ? 2 : 1);
         const int64_t e0 = (w - work0[b]) * 1024;
+        const bool small = n <= 0x7fffffffLL;
 #pragma unroll
         for (int j = 0; j < 1024 / B1_THREADS; ++j) {
             const int64_t e = e0 + j * B1_THREADS + threadIdx.x;
             if (e >= n) break;
-            const int64_t r = (e / inner) % dleg;
+            // 32-bit index arithmetic whenever the block allows it (a 64-bit div + mod per element costs more than
+            // the 16 bytes it moves)
+            const int64_t r = small ? (int64_t)(((uint32_t)e / (uint32_t)inner) % (uint32_t)dleg) : (e / inner) % dleg;
             if (CX) {
                 const double2 v = *reinterpret_cast<const double2*>(pi + 2 * e);
                 const double2 s = DCX ? *reinterpret_cast<const double2*>(pd + 2 * r) : make_double2(__ldg(pd + r), 0.0);
@@ -269,11 +272,16 @@ __global__ void __launch_bounds__(B1_THREADS) scale_axis_kernel(const double* __
     }
 }
 
-static int b1_grid(int64_t nchunk)
+// Persistent grid: as many CTAs as are resident at once (occupancy x SMs), every warp walks the chunks grid-stride,
+// so there is no partial last wave of CTAs; small inputs get one warp per chunk.
+template <class K>
+static int b1_grid(K kernel, size_t smem, int64_t nchunk)
 {
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, B1_THREADS, smem) != cudaSuccess || per_sm < 1) per_sm = 1;
     const int64_t want = (nchunk + B1_THREADS / 32 - 1) / (B1_THREADS / 32);
-    const int64_t cap = (int64_t)sm_count() * 8;
-    return (int)std::max<int64_t>(1, std::min<int64_t>(want, std::min<int64_t>(cap, B1_MAX_GRID)));
+    const int64_t cap = std::min<int64_t>((int64_t)sm_count() * per_sm, B1_MAX_GRID);
+    return (int)std::max<int64_t>(1, std::min<int64_t>(want, cap));
 }
 
 // dynamic shared memory above 48 KB is opt-in per kernel; done once per process
@@ -315,12 +323,13 @@ int cyb_block_dot(const void* x, const void* y, const int64_t* seg, const int64_
     B1Seg T{seg, chunk0, (int)nseg, 3, nchunk, smem != 0};
     double* partial = static_cast<double*>(work);
     unsigned* counter = reinterpret_cast<unsigned*>(static_cast<char*>(work) + B1_MAX_GRID * 2 * sizeof(double));
-    const int grid = b1_grid(nchunk);
     CYB_CHECK_CUDA(b1_attr());
     if (dtype == CYB_C128)
-        block_dot_kernel<true><<<grid, B1_THREADS, smem, stream>>>((const double*)x, (const double*)y, T, conj_x, partial, counter, out);
+        block_dot_kernel<true><<<b1_grid(block_dot_kernel<true>, smem, nchunk), B1_THREADS, smem, stream>>>(
+            (const double*)x, (const double*)y, T, conj_x, partial, counter, out);
     else
-        block_dot_kernel<false><<<grid, B1_THREADS, smem, stream>>>((const double*)x, (const double*)y, T, conj_x, partial, counter, out);
+        block_dot_kernel<false><<<b1_grid(block_dot_kernel<false>, smem, nchunk), B1_THREADS, smem, stream>>>(
+            (const double*)x, (const double*)y, T, conj_x, partial, counter, out);
     CYB_LAUNCH_CHECK();
     return CYB_OK;
 }
@@ -347,14 +356,13 @@ int cyb_block_lincomb(const void* x, const void* y, const void* z, void* out, co
     }
     double* partial = static_cast<double*>(work);
     unsigned* counter = work ? reinterpret_cast<unsigned*>(static_cast<char*>(work) + B1_MAX_GRID * 2 * sizeof(double)) : nullptr;
-    const int grid = b1_grid(nchunk);
     const double *px = (const double*)x, *py = (const double*)y, *pz = (const double*)z;
     double* po = (double*)out;
     const bool cx = dtype == CYB_C128;
-    if (cx && sumsq)        block_lincomb_kernel<true, true><<<grid, B1_THREADS, smem, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
-    else if (cx)            block_lincomb_kernel<true, false><<<grid, B1_THREADS, smem, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
-    else if (sumsq)         block_lincomb_kernel<false, true><<<grid, B1_THREADS, smem, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
-    else                    block_lincomb_kernel<false, false><<<grid, B1_THREADS, smem, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
+    if (cx && sumsq)        block_lincomb_kernel<true, true><<<b1_grid(block_lincomb_kernel<true, true>, smem, nchunk), B1_THREADS, smem, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
+    else if (cx)            block_lincomb_kernel<true, false><<<b1_grid(block_lincomb_kernel<true, false>, smem, nchunk), B1_THREADS, smem, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
+    else if (sumsq)         block_lincomb_kernel<false, true><<<b1_grid(block_lincomb_kernel<false, true>, smem, nchunk), B1_THREADS, smem, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
+    else                    block_lincomb_kernel<false, false><<<b1_grid(block_lincomb_kernel<false, false>, smem, nchunk), B1_THREADS, smem, stream>>>(px, py, pz, po, T, K, partial, counter, sumsq);
     CYB_LAUNCH_CHECK();
     return CYB_OK;
 }

@@ -457,6 +457,13 @@ def _b1_arena(rng, sizes, dtype):
     return a, np.asarray(offs, np.int64)
 
 
+def _b1_chunk_elems(lib, cx):
+    if lib.kind == "cuda":
+        from cyten_b200 import _lib
+        return int(_lib.load().cyb_blas1_chunk_elems(int(cx)))
+    return int(O.cyb_blas1_chunk_elems(int(cx)))
+
+
 def _b1_chunks(sizes, chunk):
     c0 = np.zeros(len(sizes) + 1, np.int64)
     c0[1:] = np.cumsum((np.asarray(sizes, np.int64) + chunk - 1) // chunk)
@@ -475,8 +482,7 @@ def test_block_dot(lib, dtype, flags):
     oy = oy[::-1].copy()                                   # block t of x pairs with block t of y (other arena order)
     keep = [t for t in range(len(B1_SIZES)) if t != 4]     # one block without partner
     seg = np.stack([ox[keep], oy[keep], np.asarray(B1_SIZES, np.int64)[keep]], axis=1)
-    chunk = 512 if dtype == np.complex128 else 1024
-    c0 = _b1_chunks(seg[:, 2], chunk)
+    c0 = _b1_chunks(seg[:, 2], _b1_chunk_elems(lib, dtype == np.complex128))
     out = lib.empty(2, torch.float64)
     work = lib.empty(148 * 8 * 2 + 8, torch.float64)
     for _ in range(2):                                     # the second call checks that the workspace re-arms itself
@@ -512,7 +518,7 @@ def test_block_lincomb(lib, dtype, with_dev, with_norm):
     oy2[2] = -1                                            # y lacks block 2, z lacks blocks 5 and 6
     oz2[5:7] = -1
     seg = np.stack([ox, oy2, oz2, oo, sizes], axis=1)
-    c0 = _b1_chunks(sizes, 512 if cx else 1024)
+    c0 = _b1_chunks(sizes, _b1_chunk_elems(lib, cx))
     coef = np.asarray([0.7, -0.2 if cx else 0.0, -1.3, 0.4 if cx else 0.0, 2.0, 0.0])
     dev = lib.up(np.asarray([0.35, 0.9 if cx else 0.0]))
     ptrs = (C.c_void_p * 3)(None, dev.data_ptr() if with_dev else None, None)
