@@ -119,14 +119,31 @@ def valid_block_inds(codomain: TensorProduct, domain: TensorProduct) -> np.ndarr
     nsecs = [l.num_sectors for l in legs]
     if not legs:
         return np.zeros((1, 0), dtype=np.int64)
-    grid = np.indices(nsecs).reshape(len(legs), -1).T
+    # Sorted merge instead of the reference's brute force over the full product grid:
+    # fuse the codomain grid and the domain grid separately, then join the two lists on the fused charge --
+    # |cod grid| + |dom grid| + |result| rows instead of |cod grid| x |dom grid|.
     ncod = codomain.num_factors
-    qc = (sym.multiple_fusion_broadcast([l.sector_decomposition[grid[:, i]] for i, l in enumerate(legs[:ncod])])
-          if ncod else np.zeros((len(grid), sym.sector_ind_len), np.int64))
-    qd = (sym.multiple_fusion_broadcast([l.sector_decomposition[grid[:, ncod + i]] for i, l in enumerate(legs[ncod:])])
-          if len(legs) > ncod else np.zeros((len(grid), sym.sector_ind_len), np.int64))
-    ok = np.all(qc == qd, axis=1)
-    bi = grid[ok].astype(np.int64)
+    nsym = sym.sector_ind_len
+
+    def side(side_legs):
+        if not side_legs:
+            return np.zeros((1, 0), dtype=np.int64), np.zeros((1, nsym), dtype=np.int64)
+        g = np.indices([l.num_sectors for l in side_legs]).reshape(len(side_legs), -1).T
+        q = sym.multiple_fusion_broadcast([l.sector_decomposition[g[:, i]] for i, l in enumerate(side_legs)])
+        return g, np.asarray(q, dtype=np.int64).reshape(len(g), nsym)
+    gc, qc = side(legs[:ncod])
+    gd, qd = side(legs[ncod:])
+    both, inv = np.unique(np.concatenate([qc, qd]), axis=0, return_inverse=True)
+    inv = np.asarray(inv).reshape(-1)
+    kc, kd = inv[:len(qc)], inv[len(qc):]
+    oc, od = np.argsort(kc, kind="stable"), np.argsort(kd, kind="stable")
+    nc, nd = np.bincount(kc, minlength=len(both)), np.bincount(kd, minlength=len(both))
+    sc, sd = np.concatenate([[0], np.cumsum(nc)]), np.concatenate([[0], np.cumsum(nd)])
+    parts = []
+    for k in np.nonzero((nc > 0) & (nd > 0))[0]:
+        rc, rd = oc[sc[k]:sc[k + 1]], od[sd[k]:sd[k + 1]]
+        parts.append(np.concatenate([np.repeat(gc[rc], len(rd), axis=0), np.tile(gd[rd], (len(rc), 1))], axis=1))
+    bi = (np.concatenate(parts) if parts else np.zeros((0, len(legs)), dtype=np.int64)).astype(np.int64)
     return bi[np.lexsort(bi.T)] if len(bi) else bi
 
 

@@ -52,3 +52,23 @@ def test_partial_chains_add_up(backend):
         loads = [sum(costs[s] * (b - a) / leg.multiplicities[s] for s, (a, b) in r.items()) for r in ranges]
         whole = sh.lpt_imbalance(costs, sh.lpt_assign(costs, world), world)
         assert max(loads) / (sum(loads) / world) <= whole + 0.1                     # (LPT is a heuristic) about as good or better
+
+
+def test_valid_block_inds_join_equals_brute_force():
+    """valid_block_inds joins the codomain and domain grids on the fused charge; the result must
+    be the reference's brute-force list (abelian.cpp:329-399), lexsorted, for U(1) x U(1) and six legs."""
+    from cyten_b200.spaces import TensorProduct
+    from cyten_b200.tensors import valid_block_inds
+    from cyten_b200.workloads import hubbard_bond_leg, hubbard_phys_leg
+    v, p = hubbard_bond_leg(256, Q=3), hubbard_phys_leg()
+    cod, dom = TensorProduct([v, p, p]), TensorProduct([v, p.dual, p.dual])
+    bi = valid_block_inds(cod, dom)
+    legs = list(cod.factors) + list(reversed(dom.factors))
+    sym = cod.symmetry
+    grid = np.indices([l.num_sectors for l in legs]).reshape(len(legs), -1).T
+    qc = sym.multiple_fusion_broadcast([l.sector_decomposition[grid[:, i]] for i, l in enumerate(legs[:3])])
+    qd = sym.multiple_fusion_broadcast([l.sector_decomposition[grid[:, 3 + i]] for i, l in enumerate(legs[3:])])
+    want = grid[np.all(qc == qd, axis=1)]
+    want = want[np.lexsort(want.T)]
+    assert len(bi) > 100 and np.array_equal(bi, want)
+    assert valid_block_inds(TensorProduct([p]), TensorProduct([v], symmetry=sym)).shape[1] == 2
