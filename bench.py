@@ -40,6 +40,7 @@ def parse():
     ap.add_argument("--chi", type=int, default=4096)
     ap.add_argument("--svd-chi", type=int, default=None)
     ap.add_argument("--no-svd", action="store_true")
+    ap.add_argument("--no-lanczos", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel eagerly instead of replaying a CUDA graph")
     ap.add_argument("--cpu-chi", type=int, default=None, help="bond dimension of the bounded CPU sample")
@@ -494,6 +495,30 @@ def run_b200(args):
         svd_info = {"chi": schi, "input": "N(0,1) blocks on [vL,p0 | p1,vR] (full rank)", "kept": kept, "err": err,
                     "sweeps_max": sweeps, "rank_deficient_ms": def_ms, "rank_deficient_kept": def_kept,
                     "rank_deficient_sweeps_max": def_sweeps}
+    # ---- the loop the matvec sits in: 10 Lanczos iterations on this H_eff, graph-replayed matvec,
+    # device-resident alpha, one read-back per iteration.  The random environments are not Hermitian, so the Ritz value
+    # means nothing: a timing; parity of the loop is tests/test_krylov.py and tests/test_live_reference.py.
+    lanczos_info = None
+    if world == 1 and not args.no_lanczos and not args.no_svd:
+        try:
+            from cyten_b200.krylov import GraphedOperator, LanczosGroundState
+            G = GraphedOperator(H)
+            iters = 10
+            lopts = {"N_max": iters, "N_min": iters, "P_tol": 0.0}
+            LanczosGroundState(G, theta_full, dict(lopts)).run()          # warm-up: plans + graph capture
+            best = float("inf")
+            for _ in range(3):
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                lz = LanczosGroundState(G, theta_full, dict(lopts))
+                E0, psi, nit = lz.run()
+                psi.data.buf
+                torch.cuda.synchronize()
+                best = min(best, (time.perf_counter() - t0) * 1e3)
+            lanczos_info = {"iterations": int(nit), "ms": best, "ms_per_iteration": best / nit, "host_syncs": lz.host_syncs,
+                            "what": "LanczosGroundState(GraphedOperator(H_eff), theta): wall time incl. result vector"}
+        except Exception as e:   # noqa: BLE001 -- an extra, must never cost the bench line
+            lanczos_info = {"error": repr(e)}
     clocks = sampler.stop() if rank == 0 else None
 
     if rank == 0:
@@ -532,7 +557,7 @@ def run_b200(args):
                         "mode": "3-stream pipeline (upload | matvec | download), two theta arenas; bytes are per rank",
                         "host_checksum": e2e_check},
                 "gpu_launches": launches, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
-                "svd_ms": svd_ms, "svd": svd_info}
+                "svd_ms": svd_ms, "svd": svd_info, "lanczos": lanczos_info}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
