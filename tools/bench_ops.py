@@ -151,16 +151,55 @@ def main():
         out.append({"row": row, "chi": chi, "dtype": dt, "gpu_ms": ms, "work": work, "rate": rate, "unit": unit,
                     "peak": peak, "frac": rate / peak, "note": note})
 
+    # Kernel-level time of the short rows: one Python call costs more than these kernels run, so besides the eager
+    # call (what a user pays per call) 16 calls are captured into ONE CUDA graph and the replay is timed; operands
+    # cycle through a pool of 8 clones (larger than L2 at chi=4096), so every call reads from HBM.
+    from cyten_b200.data import AbelianBackendData
+    NREP = 16
+
+    def clone(T, scale=1.0):
+        d = T.data
+        buf = d.buf.clone()
+        if scale != 1.0:
+            buf *= scale
+        return SymmetricTensor(AbelianBackendData(d.dtype, d.device, buf, d.block_inds, d.offsets, d.shapes, sig=d._sig),
+                               T.codomain, T.domain, be, T.labels)
+
+    def graph_time(body):
+        touch(body(0))
+        touch(body(1))
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        keep = []
+        with torch.cuda.graph(g):
+            for i in range(NREP):
+                r = body(i)
+                touch(r)
+                keep.append(r)
+        best = float("inf")
+        for _ in range(args.reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); g.replay(); e1.record(); torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        del g, keep
+        return best / NREP
+    pool = [clone(TH, 1.0 + 0.1 * i) for i in range(8)]
+
     be.plan_mkn = None
     if "permute" in rows:
         ms = gpu_time(lambda: ct.permute_legs(TH, ["vR", "p1"], ["vL", "p0"]), args.reps, touch)
         emit("a3 permute_legs(theta -> [vR,p1 | vL,p0])", ms, 2.0 * TH.data.nbytes(), "GB/s", peak_hbm)
+        out[-1]["graph_ms"] = graph_time(lambda i: ct.permute_legs(pool[i % 8], ["vR", "p1"], ["vL", "p0"]))
     if "combine" in rows:
         ms = gpu_time(lambda: ct.combine_legs(TH, [0, 1], [2, 3]), args.reps, touch)
         emit("a4 combine_legs(theta, [vL,p0], [p1,vR])", ms, 2.0 * TH.data.nbytes(), "GB/s", peak_hbm)
+        out[-1]["graph_ms"] = graph_time(lambda i: ct.combine_legs(pool[i % 8], [0, 1], [2, 3]))
     if "split" in rows:
         ms = gpu_time(lambda: ct.split_legs(THc), args.reps, touch)
         emit("a5 split_legs", ms, 2.0 * TH.data.nbytes(), "GB/s", peak_hbm)
+        cpool = [clone(THc) for _ in range(8)]
+        out[-1]["graph_ms"] = graph_time(lambda i: ct.split_legs(cpool[i % 8]))
+        del cpool
     if "tdot" in rows:
         be.plan_mkn = []
         touch(ct.tdot(A, B, [2], [0]))
@@ -168,6 +207,9 @@ def main():
         be.plan_mkn = None
         ms = gpu_time(lambda: ct.tdot(A, B, [2], [0]), args.reps, touch)
         emit("a6 tdot(A, B, vR, vL)", ms, fl, "TFLOP/s", peak_f64)
+        apool, bpool = [clone(A) for _ in range(8)], [clone(B) for _ in range(8)]
+        out[-1]["graph_ms"] = graph_time(lambda i: ct.tdot(apool[i % 8], bpool[i % 8], [2], [0]))
+        del apool, bpool
     if "svd" in rows:
         ms = gpu_time(lambda: ct.svd(TH), max(2, args.reps // 2), touch)
         emit("a7 svd(theta) full rank", ms, svd_flops(sect, cx), "TFLOP/s", peak_f64,
@@ -188,33 +230,6 @@ def main():
         # (f1) Krylov vector operations.  The kernels take 10-30 us, less than one Python call: 16 calls are captured
         # into one CUDA graph and the replay is timed; operands cycle through a pool of 8 theta-sized arenas (8 x 45 MB
         # at chi=4096 > L2), so every call reads from HBM.
-        from cyten_b200.data import AbelianBackendData
-        from cyten_b200.tensors import DiagonalTensor
-
-        def clone(T, scale):
-            d = T.data
-            buf = d.buf.clone()
-            buf *= scale
-            return SymmetricTensor(AbelianBackendData(d.dtype, d.device, buf, d.block_inds, d.offsets, d.shapes, sig=d._sig),
-                                   T.codomain, T.domain, be, T.labels)
-        pool = [clone(TH, 1.0 + 0.1 * i) for i in range(8)]
-        NREP = 16
-
-        def graph_time(body):
-            body(0)
-            body(1)
-            torch.cuda.synchronize()
-            g = torch.cuda.CUDAGraph()
-            keep = []
-            with torch.cuda.graph(g):
-                for i in range(NREP):
-                    keep.append(body(i))
-            best = float("inf")
-            for _ in range(args.reps):
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record(); g.replay(); e1.record(); torch.cuda.synchronize()
-                best = min(best, e0.elapsed_time(e1))
-            return best / NREP
         nb = float(TH.data.nbytes())
         scal = torch.zeros(4, dtype=torch.float64, device=dev)
         ms = graph_time(lambda i: be.inner_dev(pool[(2 * i) % 8].data, pool[(2 * i + 1) % 8].data, True, out=scal[0:2]))
@@ -307,12 +322,16 @@ def main():
         o["cores"] = os.cpu_count()
         if isinstance(o["ref_cpu_ms"], float):
             o["speedup"] = o["ref_cpu_ms"] / o["gpu_ms"]
+        if "graph_ms" in o:
+            o["graph_rate"] = o["work"] / (o["graph_ms"] * 1e-3) / (1e9 if o["unit"] == "GB/s" else 1e12)
+            o["graph_frac"] = o["graph_rate"] / o["peak"]
         print(json.dumps(o))
-    print(f"\n| row | GPU ms | rate | frac of peak | reference CPU ms ({os.cpu_count()} cores) | note |", file=sys.stderr)
-    print("|---|---|---|---|---|---|", file=sys.stderr)
+    print(f"\n| row | GPU ms | rate | frac of peak | in a graph: ms, rate, frac | reference CPU ms ({os.cpu_count()} cores) | note |", file=sys.stderr)
+    print("|---|---|---|---|---|---|---|", file=sys.stderr)
     for o in out:
         r = o["ref_cpu_ms"]
-        print(f"| {o['row']} | {o['gpu_ms']:.3f} | {o['rate']:.1f} {o['unit']} | {o['frac']:.3f} | "
+        g = f"{o['graph_ms']:.3f}, {o['graph_rate']:.1f} {o['unit']}, {o['graph_frac']:.3f}" if "graph_ms" in o else ""
+        print(f"| {o['row']} | {o['gpu_ms']:.3f} | {o['rate']:.1f} {o['unit']} | {o['frac']:.3f} | {g} | "
               f"{r if not isinstance(r, float) else round(r, 1)} | {o['note']} |", file=sys.stderr)
     if args.out:
         Path(args.out).write_text("\n".join(json.dumps(o) for o in out) + "\n")
