@@ -243,7 +243,8 @@ class Blas1Mixin:
                 if d.sizes[dpos[int(a.block_inds[i, leg])]] != sh[leg]:
                     raise ValueError("scale_axis: the diagonal tensor's leg does not match the tensor's leg")
             work0 = np.zeros(len(keep) + 1, dtype=np.int64)
-            work0[1:] = np.cumsum((sizes + 1023) // 1024)
+            chunk = int(self._b1_lib().cyb_blas1_chunk_elems(_lib.CYB_C128 if dt == "complex128" else _lib.CYB_F64))
+            work0[1:] = np.cumsum((sizes + chunk - 1) // chunk)
             with self._ctx():
                 plan = self._plan_put(key, dict(bi=bi, shapes=shapes, sig=None, nblk=len(keep), nwork=int(work0[-1]),
                                                 desc=to_device_i64(desc if len(keep) else np.zeros((1, 6)), self.device),

@@ -237,36 +237,57 @@ __global__ void __launch_bounds__(B1_THREADS) block_lincomb_kernel(const double*
 
 // out block = in block scaled along one axis: block viewed as (outer, dleg, inner); element (a, r, b) *= d[r]
 // desc int64[nblk][6] = (off_in, off_out, outer, dleg, inner, d_off)
+// row index of element e of a block viewed as (outer, dleg, inner); 32-bit arithmetic whenever the block allows it
+// (a 64-bit div + mod per element costs more than the 16 bytes it moves), no division at all for the two common cases
+// (scaled axis last: inner == 1; scaled axis first: outer == 1)
+__device__ __forceinline__ int64_t b1_row(int64_t e, int64_t dleg, int64_t inner, bool small, bool first_axis)
+{
+    if (small) {
+        const uint32_t q = inner == 1 ? (uint32_t)e : (uint32_t)e / (uint32_t)inner;
+        return first_axis ? q : q % (uint32_t)dleg;
+    }
+    const int64_t q = e / inner;
+    return first_axis ? q : q % dleg;
+}
+
 template <bool CX, bool DCX>
 __global__ void __launch_bounds__(B1_THREADS) scale_axis_kernel(const double* __restrict__ in, double* __restrict__ out,
                                                                 const int64_t* desc, const double* __restrict__ dg,
-                                                                const int64_t* work0, int nblk, int64_t nwork, int staged)
+                                                                const int64_t* chunk0, int nblk, int64_t nchunk, int staged)
 {
     constexpr int ES = CX ? 2 : 1;
-    b1_stage(work0, desc, nblk, 6, staged);
-    // work item = 1024 consecutive elements of one block
-    for (int64_t w = blockIdx.x; w < nwork; w += gridDim.x) {
-        const int b = b1_find(work0, nblk, w);
+    b1_stage(chunk0, desc, nblk, 6, staged);
+    const int lane = threadIdx.x & 31;
+    const int64_t warp0 = (int64_t)blockIdx.x * (B1_THREADS / 32) + (threadIdx.x >> 5);
+    const int64_t nwarp = (int64_t)gridDim.x * (B1_THREADS / 32);
+    for (int64_t c = warp0; c < nchunk; c += nwarp) {            // same chunking as the dot / lincomb kernels
+        const int b = b1_find(chunk0, nblk, c);
         const int64_t* D = desc + (size_t)b * 6;
-        const int64_t dleg = D[3], inner = D[4], n = D[2] * dleg * inner;
+        const int64_t outer = D[2], dleg = D[3], inner = D[4], n = outer * dleg * inner, nd = n * ES;
         const double* pi = in + D[0] * ES;
         double* po = out + D[1] * ES;
         const double* pd = dg + D[5] * (DCX ? 2 : 1);
-        const int64_t e0 = (w - work0[b]) * 1024;
-        const bool small = n <= 0x7fffffffLL;
+        const int64_t d0 = (c - chunk0[b]) * (2 * B1_CHUNK);
+        const bool small = n <= 0x7fffffffLL, first_axis = outer == 1;
+        double2 v[B1_BATCH];
 #pragma unroll
-        for (int j = 0; j < 1024 / B1_THREADS; ++j) {
-            const int64_t e = e0 + j * B1_THREADS + threadIdx.x;
-            if (e >= n) break;
-            // 32-bit index arithmetic whenever the block allows it (a 64-bit div + mod per element costs more than
-            // the 16 bytes it moves)
-            const int64_t r = small ? (int64_t)(((uint32_t)e / (uint32_t)inner) % (uint32_t)dleg) : (e / inner) % dleg;
+        for (int j = 0; j < B1_BATCH; ++j) v[j] = b1_ldz(pi, d0 + (int64_t)(j * 32 + lane) * 2, nd);
+#pragma unroll
+        for (int j = 0; j < B1_BATCH; ++j) {
+            const int64_t d = d0 + (int64_t)(j * 32 + lane) * 2;
+            if (d >= nd) break;
             if (CX) {
-                const double2 v = *reinterpret_cast<const double2*>(pi + 2 * e);
+                const int64_t r = b1_row(d >> 1, dleg, inner, small, first_axis);
                 const double2 s = DCX ? *reinterpret_cast<const double2*>(pd + 2 * r) : make_double2(__ldg(pd + r), 0.0);
-                *reinterpret_cast<double2*>(po + 2 * e) = cmul(s, v);
+                *reinterpret_cast<double2*>(po + d) = cmul(s, v[j]);
             } else {
-                po[e] = pi[e] * __ldg(pd + r);
+                const double s0 = __ldg(pd + b1_row(d, dleg, inner, small, first_axis));
+                if (d + 1 < nd) {
+                    const double s1 = __ldg(pd + b1_row(d + 1, dleg, inner, small, first_axis));
+                    *reinterpret_cast<double2*>(po + d) = make_double2(v[j].x * s0, v[j].y * s1);
+                } else {
+                    po[d] = v[j].x * s0;
+                }
             }
         }
     }
@@ -374,18 +395,20 @@ int cyb_scale_axis(const void* in, void* out, const int64_t* desc, const int64_t
     CYB_REQUIRE(!(dtype == CYB_F64 && diag_dtype == CYB_C128), "scale_axis: promote the tensor to complex128 first");
     if (nblk == 0 || nwork == 0) return CYB_OK;
     cudaStream_t stream = (cudaStream_t)stream_;
-    const int grid = (int)std::min<int64_t>(nwork, (int64_t)sm_count() * 8);
     const size_t smem = b1_smem_bytes(nblk, 6);
     const int staged = smem != 0;
     CYB_CHECK_CUDA(b1_attr());
     const double *pi = (const double*)in, *pd = (const double*)diag;
     double* po = (double*)out;
     if (dtype == CYB_C128 && diag_dtype == CYB_C128)
-        scale_axis_kernel<true, true><<<grid, B1_THREADS, smem, stream>>>(pi, po, desc, pd, work0, (int)nblk, nwork, staged);
+        scale_axis_kernel<true, true><<<b1_grid(scale_axis_kernel<true, true>, smem, nwork), B1_THREADS, smem, stream>>>(
+            pi, po, desc, pd, work0, (int)nblk, nwork, staged);
     else if (dtype == CYB_C128)
-        scale_axis_kernel<true, false><<<grid, B1_THREADS, smem, stream>>>(pi, po, desc, pd, work0, (int)nblk, nwork, staged);
+        scale_axis_kernel<true, false><<<b1_grid(scale_axis_kernel<true, false>, smem, nwork), B1_THREADS, smem, stream>>>(
+            pi, po, desc, pd, work0, (int)nblk, nwork, staged);
     else
-        scale_axis_kernel<false, false><<<grid, B1_THREADS, smem, stream>>>(pi, po, desc, pd, work0, (int)nblk, nwork, staged);
+        scale_axis_kernel<false, false><<<b1_grid(scale_axis_kernel<false, false>, smem, nwork), B1_THREADS, smem, stream>>>(
+            pi, po, desc, pd, work0, (int)nblk, nwork, staged);
     CYB_LAUNCH_CHECK();
     return CYB_OK;
 }

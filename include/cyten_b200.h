@@ -240,7 +240,8 @@ int cyb_block_lincomb(const void* x, const void* y, const void* z, void* out, co
                       const double* const* coef_dev, double* sumsq, void* work, cyb_stream_t stream);
 /* scale_axis (abelian.cpp:3177-3232): out block = in block, viewed as (outer, dleg, inner), times
  * diag[d_off + r] along the middle axis.  desc (device) int64[nblk][6] = (off_in, off_out, outer, dleg,
- * inner, d_off); work0[nblk + 1] = running count of 1024-element work items per block. */
+ * inner, d_off); work0[nblk + 1] = running count of chunks of cyb_blas1_chunk_elems(dtype) elements per block
+ * (ceil), nwork = work0[nblk]. */
 int cyb_scale_axis(const void* in, void* out, const int64_t* desc, const int64_t* work0, int64_t nblk,
                    int64_t nwork, const void* diag, int dtype, int diag_dtype, cyb_stream_t stream);
 

@@ -564,7 +564,8 @@ def test_scale_axis(lib, dtype, ddtype):
     oo[order] = ooff
     desc = np.asarray([(ox[t], oo[t], s[0], s[1], s[2], od[t]) for t, s in enumerate(shapes)], np.int64)
     w0 = np.zeros(len(shapes) + 1, np.int64)
-    w0[1:] = np.cumsum((np.asarray(sizes) + 1023) // 1024)
+    chunk = _b1_chunk_elems(lib, dtype == np.complex128)
+    w0[1:] = np.cumsum((np.asarray(sizes) + chunk - 1) // chunk)
     d_out = lib.empty(sum((s + 15) // 16 * 16 for s in sizes), torch.complex128 if dtype == np.complex128 else torch.float64)
     lib.call("cyb_scale_axis", lib.p(lib.up(x)), lib.p(d_out), lib.p(lib.up(desc)), lib.p(lib.up(w0)), len(shapes), int(w0[-1]),
              lib.p(lib.up(d)), int(dtype == np.complex128), int(ddtype == np.complex128), lib.stream())
