@@ -91,6 +91,7 @@ class LanczosGroundState:
         self._result_krylov = np.ones(1)
         self._cache: list = []                                   # (u_k, beta_k): v_k = u_k / beta_k
         self.host_syncs = 0
+        self._psi0_norm = None
         dev = self.be.device
         self._scal = torch.zeros(4, dtype=torch.float64, device=dev)      # (alpha, 0 | ||u'||^2, 0)
         self._ov = torch.zeros(2, dtype=torch.float64, device=dev)
@@ -180,6 +181,8 @@ class LanczosGroundState:
         if beta < self.cutoff:
             raise ValueError(f"Norm of self.psi0 too small: {beta}")
         self.psi0 = u = scalar_multiply(1.0 / beta, u)
+        if self._psi0_norm is None:
+            self._psi0_norm = beta                                  # only needed by LanczosEvolution
         beta, performed = 1.0, 0
         for k in range(self.N_max):
             v = self._normalised(u, beta)
@@ -239,6 +242,50 @@ class LanczosGroundState:
         if N == 1:
             return E0, self.psi0, N
         return E0, self._calc_result_full(N), N
+
+
+class LanczosEvolution(LanczosGroundState):
+    """``psi(t) = exp(delta H) psi0`` in the Krylov space (krylov_based.cpp:948-1024): the same recurrence and vector
+    operations; only the small host algebra differs (exp of the tridiagonal matrix instead of its lowest eigenvector,
+    convergence = weight of the last Krylov vector below ``P_tol``).  ``run(delta, normalize=None)`` returns
+    ``(psi, N)``; ``normalize`` defaults to True for purely imaginary ``delta`` (real time).  For a real ``delta`` the
+    coefficients are real and the result keeps the dtype of ``psi0``."""
+
+    def __init__(self, H, psi0, options=None):
+        super().__init__(H, psi0, options)
+        self._result_norm = 1.0
+        self.delta = None
+
+    def run(self, delta, normalize=None):
+        self.delta = complex(delta)
+        self._cache = []
+        self.h_krylov[:] = 0.0
+        self.Es[:] = 0.0
+        N = self._build_krylov()
+        psi = scalar_multiply(self._coef(self._result_krylov[0]), self.psi0) if N == 1 else self._calc_result_full(N)
+        if normalize if normalize is not None else (self.delta.real == 0.0):
+            return psi, N
+        return scalar_multiply(self._psi0_norm * self._result_norm, psi), N
+
+    def _coef(self, c):
+        return float(np.real(c)) if self.delta.imag == 0.0 else complex(c)
+
+    def _calc_result_krylov(self, k):
+        if k == 0:
+            e = np.exp(self.delta * self.h_krylov[0, 0])
+            self._result_norm = abs(e)
+            self._result_krylov = np.asarray([e / self._result_norm])
+        else:
+            E, V = np.linalg.eigh(self.h_krylov[:k + 1, :k + 1])
+            self.Es[k, :k + 1] = E
+            x = V @ (np.exp(E * self.delta) * np.conj(V[0]))
+            self._result_norm = float(np.linalg.norm(x))
+            self._result_krylov = x / self._result_norm
+        if self.delta.imag == 0.0:
+            self._result_krylov = np.real(self._result_krylov)
+
+    def _converged(self, k) -> bool:
+        return abs(self._result_krylov[k]) < self.P_tol
 
 
 def lanczos(H, psi, options=None):

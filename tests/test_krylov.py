@@ -125,3 +125,27 @@ def test_lanczos_graph_replay_matches_eager(cuda_backend):
     E1, psi1, N1 = lanczos(GraphedOperator(H), th, {"N_max": 12})
     assert N == N1 and E0 == E1
     assert np.array_equal(psi.to_dense(), psi1.to_dense())
+
+
+@pytest.mark.parametrize("dtype", ["float64", "complex128"])
+@pytest.mark.parametrize("delta", [-0.2j, -0.15, 0.05 - 0.1j])
+def test_lanczos_evolution_against_dense_expm(backend, dtype, delta):
+    from scipy.linalg import expm
+    from cyten_b200.krylov import LanczosEvolution
+    th, _, K, _ = _problem(backend, 12, dtype)
+    K = 0.1 * K
+
+    class Op:
+        def matvec(self, t):
+            return ct.compose(K, t)
+
+    psi, N = LanczosEvolution(Op(), th, {"N_max": 40, "P_tol": 1e-15}).run(delta, normalize=False)
+    Kd, T = K.to_dense(), th.to_dense()
+    n = Kd.shape[0] * Kd.shape[1]
+    M = Kd.transpose(0, 1, 3, 2).reshape(n, n)                 # block axes are [vL, p0, p0', vL']
+    want = (expm(delta * M) @ T.reshape(n, -1)).reshape(T.shape)
+    assert N < 40
+    assert psi.dtype == ("float64" if (dtype == "float64" and np.imag(delta) == 0) else "complex128")
+    assert np.allclose(psi.to_dense(), want, rtol=0, atol=1e-10 * np.abs(want).max())
+    unit, _ = LanczosEvolution(Op(), th, {"N_max": 40, "P_tol": 1e-15}).run(delta, normalize=True)
+    assert abs(ct.norm(unit) - 1.0) < 1e-12

@@ -192,3 +192,35 @@ def test_lanczos_matches_reference_lanczos(backend, name, dtype, chi, opts):
     assert N == Nr
     assert abs(E - _num(Er)) <= 1e-12 * (abs(_num(Er)) + 1.0)
     assert abs(abs(ct.inner(from_reference(psir, backend, msym), psi)) - 1.0) <= 1e-10
+
+
+@pytest.mark.parametrize("name,dtype,chi", CASES[:2])
+@pytest.mark.parametrize("delta", [-0.05j, -0.1, 0.03 - 0.02j])
+def test_lanczos_evolution_matches_reference(backend, name, dtype, chi, delta):
+    """exp(delta H) psi through cyten.krylov_based.LanczosEvolution and cyten_b200.krylov.LanczosEvolution."""
+    from cyten import krylov_based, sparse
+    from cyten_b200.krylov import LanczosEvolution
+    sym, msym, A, B = _setup(name, dtype, chi // 4, 8)
+    TH = rc.tdot(A, B, ["vR"], ["vL"])
+    rdt = rc.Dtype.complex128 if dtype == "complex128" else rc.Dtype.float64
+    rb = rc.get_backend("abelian", "numpy")
+    X = rc.SymmetricTensor.from_random_normal(TH.codomain, TH.codomain, backend=rb, dtype=rdt)
+    K = 0.2 * (X + X.hc)
+
+    class RefOp(sparse.LinearOperator):
+        def matvec(self, t):
+            return rc.compose(K, t)
+
+    class Op:
+        def __init__(self):
+            self.k = from_reference(K, backend, msym)
+
+        def matvec(self, t):
+            return ct.compose(self.k, t)
+
+    psir, Nr = krylov_based.LanczosEvolution(RefOp(), TH, {"N_max": 30}).run(delta)
+    psi, N = LanczosEvolution(Op(), from_reference(TH, backend, msym), {"N_max": 30}).run(delta)
+    assert N == Nr
+    ref = from_reference(psir, backend, msym)
+    diff = ct.norm(ct.linear_combination(1.0, psi, -1.0, ref))
+    assert diff <= 1e-10 * max(1.0, ct.norm(ref)), diff
