@@ -529,7 +529,7 @@ class B200AbelianBackend(Blas1Mixin):
         B: AbelianBackendData = b.data
         a_keep, ncontr, b_keep = a.codomain.num_factors, a.domain.num_factors, b.domain.num_factors
         if ncontr == 0:
-            raise NotImplementedError("compose without contracted legs (outer product)")
+            return self._compose_no_contraction(a, b)
         res_dtype = "complex128" if "complex128" in (A.dtype, B.dtype) else "float64"
         rr = a_keep + b_keep
         if A.num_blocks == 0 or B.num_blocks == 0:
@@ -577,6 +577,24 @@ class B200AbelianBackend(Blas1Mixin):
         self._run_gemm(A.buf, b_buf, res, plan)
         res._dev_tables["offsets"] = plan["d_off"][:plan["n_out"]]
         return res
+
+    def _compose_no_contraction(self, a, b) -> AbelianBackendData:
+        """abelian.cpp:1518-1565: a has no domain, b no codomain -- every pair of blocks gives an outer product.
+        That is the ordinary compose over ONE extra leg holding only the trivial sector with multiplicity 1 (K = 1):
+        the tables get one more column, the arenas are shared, the planner and the grouped GEMM run unchanged."""
+        sym = a.codomain.symmetry
+        triv = ElementarySpace(sym, np.zeros((1, sym.sector_ind_len), dtype=np.int64), np.ones(1, dtype=np.int64), False)
+
+        def with_leg(data, front):
+            z, o = np.zeros((data.num_blocks, 1), np.int64), np.ones((data.num_blocks, 1), np.int64)
+            bi = np.concatenate([z, data.block_inds] if front else [data.block_inds, z], axis=1)
+            shapes = np.concatenate([o, data.shapes] if front else [data.shapes, o], axis=1)
+            return AbelianBackendData(data.dtype, self.device, data.buf, bi, data.offsets, shapes)
+        a2 = _Retyped(a, with_leg(a.data, False))
+        a2.domain = TensorProduct([triv], symmetry=sym)
+        b2 = _Retyped(b, with_leg(b.data, True))
+        b2.codomain = TensorProduct([triv], symmetry=sym)
+        return self.compose(a2, b2)
 
     def _compose_operand_b(self, B: AbelianBackendData, ncontr: int, b_keep: int) -> torch.Tensor:
         """Arena with every block of B re-laid-out to axes ``[reversed(contracted), kept]`` (same block
@@ -661,8 +679,14 @@ class B200AbelianBackend(Blas1Mixin):
     def _sorted_data(self, dtype, block_inds, shapes):
         """Allocates an arena for the given blocks in lexsorted order; returns (data, position of
         every input row in the arena)."""
-        block_inds = np.asarray(block_inds, dtype=np.int64).reshape(len(shapes), -1)
-        shapes = np.asarray(shapes, dtype=np.int64).reshape(len(block_inds), -1)
+        block_inds, shapes = np.asarray(block_inds, dtype=np.int64), np.asarray(shapes, dtype=np.int64)
+        if len(shapes) == 0:                       # no matched sector at all: tensors without blocks
+            ncol = block_inds.shape[1] if block_inds.ndim == 2 else 2
+            block_inds = np.zeros((0, ncol), np.int64)
+            shapes = np.zeros((0, shapes.shape[1] if shapes.ndim == 2 else ncol), np.int64)
+        else:
+            block_inds = block_inds.reshape(len(shapes), -1)
+            shapes = shapes.reshape(len(block_inds), -1)
         order = self.lexsort(block_inds) if len(block_inds) else np.zeros(0, np.int64)
         inv = np.empty(len(order), dtype=np.int64)
         inv[order] = np.arange(len(order))

@@ -19,7 +19,7 @@ from .spaces import AbelianLegPipe, ElementarySpace, TensorProduct
 
 __all__ = ["SymmetricTensor", "DiagonalTensor", "permute_legs", "combine_legs", "split_legs",
            "compose", "tdot", "svd", "truncated_svd", "qr", "eigh", "norm", "inner", "linear_combination",
-           "scalar_multiply", "dagger", "scale_axis"]
+           "scalar_multiply", "dagger", "scale_axis", "outer", "partial_compose", "lq"]
 
 
 class SymmetricTensor:
@@ -263,6 +263,67 @@ def compose(A: SymmetricTensor, B: SymmetricTensor):
                            A.labels[:A.num_codomain_legs] + B.labels[B.num_codomain_legs:])
 
 
+def outer(A: SymmetricTensor, B: SymmetricTensor):
+    """Tensor product without contraction (ops_algebra.cpp:1097-1178 -> ``_compose_no_contraction``,
+    abelian.cpp:1518-1565): legs ``[*A.legs, *B.legs]``, ``A``'s legs bent into the codomain and ``B``'s into the
+    domain for the product, then codomain ``A.codomain + B.codomain`` and domain ``A.domain + B.domain`` (the
+    reference's convention)."""
+    nA, nB = A.num_legs, B.num_legs
+    A2 = permute_legs(A, codomain=list(range(nA)), domain=[])
+    B2 = permute_legs(B, codomain=[], domain=list(reversed(range(nB))))
+    R = compose(A2, B2)                       # legs [*A.legs, *B.legs]
+    cA, cB = A.num_codomain_legs, B.num_codomain_legs
+    cod = list(range(cA)) + [nA + i for i in range(cB)]
+    dom = [nA - 1 - j for j in range(A.num_domain_legs)] + [nA + nB - 1 - j for j in range(B.num_domain_legs)]
+    return permute_legs(R, cod, dom)
+
+
+def partial_compose(T1: SymmetricTensor, T2: SymmetricTensor, first_leg):
+    """Applies ``T2`` to a consecutive part of ``T1``'s codomain (``T2.domain`` is contracted, ``T2.codomain`` takes
+    its place) or of its domain (``T2.codomain`` is contracted, ``T2.domain`` takes its place), starting at leg
+    ``first_leg`` of ``T1``; ops_algebra.cpp:1180-1370 -> abelian.cpp:2853-2951.  Here: one ``tdot`` (the
+    permutations are deferred and folded into the GEMM operand re-layout) and one deferred permutation back."""
+    n1, c1, d1 = T1.num_legs, T1.num_codomain_legs, T1.num_domain_legs
+    n2, c2, d2 = T2.num_legs, T2.num_codomain_legs, T2.num_domain_legs
+    f = T1.get_leg_idcs([first_leg])[0]
+    if f < c1:
+        num, last = d2, f + d2 - 1
+        if num == 0:
+            raise ValueError("Use compose or outer when no legs are to be contracted")
+        if last >= c1:
+            raise ValueError("Not all legs to be contracted are in the (co)domain")
+        if num >= c1:
+            raise ValueError("Use compose for contracting the full (co)domain")
+        if list(T1.codomain.factors[f:last + 1]) != list(T2.domain.factors):
+            raise ValueError("partial_compose: incompatible legs")
+        R = tdot(T2, T1, [n2 - 1 - j for j in range(num)], [f + j for j in range(num)])   # [T2.codomain, T1 open legs]
+
+        def pos(i):
+            return c2 + (i if i < f else i - num)
+        cod = [pos(i) for i in range(f)] + list(range(c2)) + [pos(i) for i in range(last + 1, c1)]
+        dom = [pos(n1 - 1 - j) for j in range(d1)]
+        return permute_legs(R, cod, dom)
+    num, last = c2, f + c2 - 1
+    if num == 0:
+        raise ValueError("Use compose or outer when no legs are to be contracted")
+    if last >= n1:
+        raise ValueError("Not all legs to be contracted are in the (co)domain")
+    if num >= d1:
+        raise ValueError("Use compose for contracting the full (co)domain")
+    df, dl = n1 - 1 - last, n1 - 1 - f
+    if list(T1.domain.factors[df:dl + 1]) != list(T2.codomain.factors):
+        raise ValueError("partial_compose: incompatible legs")
+    R = tdot(T1, T2, [n1 - 1 - (df + j) for j in range(num)], list(range(num)))          # [T1 open legs, reversed(T2.domain)]
+
+    def pos1(i):
+        return i if i < f else i - num
+    m = n1 - num
+    cod = [pos1(i) for i in range(c1)]
+    dom = ([pos1(n1 - 1 - j) for j in range(df)] + [m + (d2 - 1 - j) for j in range(d2)]
+           + [pos1(n1 - 1 - j) for j in range(dl + 1, d1)])
+    return permute_legs(R, cod, dom)
+
+
 def tdot(A: SymmetricTensor, B: SymmetricTensor, legs1, legs2):
     """Like ``cyten.tdot`` (ops_algebra.cpp:1908-1917)."""
     l1 = A.get_leg_idcs(legs1 if isinstance(legs1, (list, tuple)) else [legs1])
@@ -345,6 +406,15 @@ def qr(T: SymmetricTensor, new_labels=("a", "b"), new_leg_dual=False):
     if cd:
         R = split_legs(R, [1])
     return Q, R
+
+
+def lq(T: SymmetricTensor, new_labels=("a", "b"), new_leg_dual=False):
+    """``T = L Q`` with ``Q`` an isometry from the right (``Q Q^dagger = 1``); decompositions.cpp / abelian.cpp:2304-2382.
+    Computed as the QR decomposition of ``T^dagger`` (``T^dagger = Q^dagger L^dagger``): the two daggers are block
+    copies, the factorisation is the batched blocked Householder kernel."""
+    Qd, Rd = qr(dagger(T), new_labels=(_dual_label(new_labels[1]) if new_labels[1] else None,
+                                       _dual_label(new_labels[0]) if new_labels[0] else None), new_leg_dual=new_leg_dual)
+    return dagger(Rd), dagger(Qd)
 
 
 def eigh(T: SymmetricTensor, new_labels=("a", "b", "c"), new_leg_dual=False, sort=None):

@@ -149,3 +149,30 @@ def test_lanczos_evolution_against_dense_expm(backend, dtype, delta):
     assert np.allclose(psi.to_dense(), want, rtol=0, atol=1e-10 * np.abs(want).max())
     unit, _ = LanczosEvolution(Op(), th, {"N_max": 40, "P_tol": 1e-15}).run(delta, normalize=True)
     assert abs(ct.norm(unit) - 1.0) < 1e-12
+
+
+def test_outer_partial_compose_lq_against_dense(backend):
+    """Self-contained versions of the live-reference checks (dense numpy)."""
+    from cyten_b200.spaces import TensorProduct
+    th = _theta(backend, 24, "float64", 4)
+    A, T = None, th.to_dense()
+    p0 = th.codomain.factors[1]
+    op = random_tensor([p0], [p0], backend, seed=8, labels=["q", "q*"])
+    r = ct.partial_compose(th, op, 1)
+    assert r.labels == ["vL", "q", "p1", "vR"]
+    assert np.allclose(r.to_dense(), np.einsum("qp,apcd->aqcd", op.to_dense(), T), rtol=0, atol=1e-13)
+    dl = th.domain.factors[1]                                  # legs order [vL, p0, p1, vR]: domain = [vR, p1]
+    op2 = random_tensor([dl], [dl], backend, seed=9, labels=["r", "r*"])
+    r2 = ct.partial_compose(th, op2, 2)
+    assert np.allclose(r2.to_dense(), np.einsum("abcd,cr->abrd", T, op2.to_dense()), rtol=0, atol=1e-13)
+    o = ct.outer(op, op2)
+    assert o.num_codomain_legs == 2 and o.num_domain_legs == 2
+    assert np.allclose(o.to_dense(), np.einsum("ab,cd->acdb", op.to_dense(), op2.to_dense()), rtol=0, atol=1e-14)
+    l, q = ct.lq(th)
+    assert np.allclose(ct.compose(l, q).to_dense(), T, rtol=0, atol=1e-12 * np.abs(T).max())
+    qq = ct.compose(q, ct.dagger(q)).to_dense()
+    assert np.allclose(qq, np.eye(qq.shape[0]), rtol=0, atol=1e-12)
+    empty = TensorProduct([], symmetry=th.symmetry)
+    a = random_tensor(th.codomain.factors, empty, backend, seed=3)
+    b = random_tensor(empty, th.codomain.factors, backend, seed=4)
+    assert np.allclose(ct.compose(a, b).to_dense(), np.multiply.outer(a.to_dense(), b.to_dense()), rtol=0, atol=1e-14)

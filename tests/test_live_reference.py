@@ -224,3 +224,44 @@ def test_lanczos_evolution_matches_reference(backend, name, dtype, chi, delta):
     ref = from_reference(psir, backend, msym)
     diff = ct.norm(ct.linear_combination(1.0, psi, -1.0, ref))
     assert diff <= 1e-10 * max(1.0, ct.norm(ref)), diff
+
+
+def _ref_bi(T, ncol):
+    return np.asarray(T.data.block_inds.to_numpy()).reshape(len(T.data.blocks), ncol)
+
+
+@pytest.mark.parametrize("name,dtype,chi", CASES)
+def test_partial_compose_outer_lq(backend, name, dtype, chi):
+    """The remaining members of SURVEY rows a6 / a9: partial_compose (abelian.cpp:2853-2951), the product without
+    contracted legs (_compose_no_contraction, :1518-1565, through outer) and lq (:2304-2382)."""
+    sym, msym, A, B = _setup(name, dtype, chi // 3, 9)
+    TH = rc.tdot(A, B, ["vR"], ["vL"])                       # [vL, p0 | p1, vR]
+    th = from_reference(TH, backend, msym)
+    rdt = rc.Dtype.complex128 if dtype == "complex128" else rc.Dtype.float64
+    rb = rc.get_backend("abelian", "numpy")
+    p = TH.codomain[1]
+    Op = rc.SymmetricTensor.from_random_normal([p], [p], backend=rb, dtype=rdt, labels=["q", "q*"])
+    R, r = rc.tensors.partial_compose(TH, Op, 1), ct.partial_compose(th, from_reference(Op, backend, msym), 1)
+    assert list(R.labels) == r.labels
+    _same(r, R, tol=1e-13)                                   # an operator applied to a codomain leg
+    dleg = TH.domain[1]
+    Op2 = rc.SymmetricTensor.from_random_normal([dleg], [dleg], backend=rb, dtype=rdt, labels=["r", "r*"])
+    first = TH.num_legs - 2                                  # leg index of domain factor 1
+    R, r = rc.tensors.partial_compose(TH, Op2, first), ct.partial_compose(th, from_reference(Op2, backend, msym), first)
+    assert list(R.labels) == r.labels
+    _same(r, R, tol=1e-13)                                   # ... and to a domain leg
+    with pytest.raises(ValueError):                          # the full codomain is compose's job
+        full = rc.SymmetricTensor.from_random_normal(TH.codomain, TH.codomain, backend=rb, dtype=rdt)
+        ct.partial_compose(th, from_reference(full, backend, msym), 0)
+    Bl = rc.SymmetricTensor.from_random_normal([p], [p], backend=rb, dtype=rdt, labels=["x", "y"])
+    O, o = rc.outer(A, Bl), ct.outer(from_reference(A, backend, msym), from_reference(Bl, backend, msym))
+    assert list(O.labels) == o.labels
+    _same(o, O, tol=1e-14)                                   # no contracted leg: every pair of blocks
+    Lr, Qr = rc.lq(TH)
+    l, q = ct.lq(th)
+    assert np.array_equal(l.data.block_inds, _ref_bi(Lr, 3)) and np.array_equal(q.data.block_inds, _ref_bi(Qr, 3))
+    _same(ct.compose(l, q), TH, tol=1e-12)                   # L Q = theta (the factors: gauge)
+    if q.data.num_blocks:
+        qq = ct.compose(q, ct.dagger(q)).to_dense()
+        n = qq.shape[0]
+        assert np.allclose(qq.reshape(n, n), np.eye(n), rtol=0, atol=1e-12)      # Q Q^dagger = 1 on the new leg
