@@ -432,6 +432,27 @@ class ShardedHEffective:
             acc = expand_to_full(self.H.matvec(take_blocks(getattr(self, "_empty_like", theta_local), np.zeros(0, np.int64))))
         return acc
 
+    def local_part(self, theta: SymmetricTensor) -> SymmetricTensor:
+        """This rank's shard of a REPLICATED theta with the structure ``shard`` was called on (cached plans: one
+        block-copy launch)."""
+        if self.pg.world == 1:
+            return theta
+        if self.split_columns:
+            mine = self.ranges[self.pg.rank]
+            return slice_leg(theta, self.shard_leg, mine) if mine else take_blocks(theta, np.zeros(0, np.int64))
+        ax = theta.get_leg_idcs([self.shard_leg])[0]
+        my_secs = sorted({it[1] for it, o in zip(self.items, self.item_owner) if o == self.pg.rank})
+        return take_blocks(theta, np.nonzero(np.isin(theta.data.block_inds[:, ax], my_secs))[0])
+
+    def matvec_replicated(self, theta: SymmetricTensor) -> SymmetricTensor:
+        """``H_eff . theta`` for a replicated theta, replicated result: the operator a Krylov solver sees
+        (``cyten_b200.krylov.lanczos(SimpleNamespace(matvec=SH.matvec_replicated), theta)``).  Every rank runs the
+        cheap vector operations on the full vectors redundantly (identical arithmetic, identical alpha/beta, no
+        further collective); the matvec is the sharded chain + one all_reduce."""
+        if self.pg.world == 1:
+            return self.H.matvec(theta)
+        return self.matvec(self.local_part(theta))
+
     def matvec(self, theta_local: SymmetricTensor) -> SymmetricTensor:
         """Replicated ``H_eff . theta`` from the rank-local shard of theta: one all_reduce of the result arena."""
         full = self.matvec_local(theta_local)

@@ -75,6 +75,17 @@ def worker(rank, world, port, out_dir):
         nsplit = sum(1 for r in SC.ranges for s, (a, b) in r.items() if (a, b) != (0, int(theta.domain.factors[0].multiplicities[s])))
         assert nsplit >= 2, "the test must exercise a sector that is cut into ranges"
 
+        # ---- the Krylov loop on top of the sharded matvec: same iterations, same Ritz value as single process ----
+        from types import SimpleNamespace
+        from cyten_b200.krylov import lanczos
+        opts = {"N_max": 6, "N_min": 6, "P_tol": 0.0}
+        E1, psi1, N1 = lanczos(H, theta, dict(opts))
+        for SX in (SC, SH):
+            E2, psi2, N2 = lanczos(SimpleNamespace(matvec=SX.matvec_replicated), theta, dict(opts))
+            assert N1 == N2 and abs(E1 - E2) <= 1e-10 * (abs(E1) + 1.0)
+            full1, full2 = sh.expand_to_full(psi1), sh.expand_to_full(psi2)
+            assert np.allclose(_dense_of(full2), _dense_of(full1), rtol=0, atol=1e-9)
+
         # ---- tdot with the output blocks partitioned over the ranks ----
         v, p = u1_bond_leg(48, 3, 1.2), u1_phys_leg()
         A, B = mps_tensor(v, p, v, be, seed=1), mps_tensor(v, p, v, be, seed=2)
