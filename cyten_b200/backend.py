@@ -22,8 +22,7 @@ import torch
 from . import _lib
 from .blas1 import Blas1Mixin
 from .data import AbelianBackendData, aligned_offsets, ptr, stream_ptr, to_device_i64, ALIGN
-from .spaces import (AbelianLegPipe, ElementarySpace, TensorProduct, find_row_differences,
-                     make_stride)
+from .spaces import AbelianLegPipe, ElementarySpace, TensorProduct
 
 MAX_RANK = _lib.MAX_RANK
 
