@@ -225,9 +225,26 @@ def run_reference(args):
     svd_ms = None
     if not args.no_svd:
         svd_ms = cpu_svd_time(args.svd_chi or chi, kind) * 1e3
+    lanczos_info = None
+    if kind == "reference" and not args.no_lanczos and not args.no_svd:
+        # the loop the matvec sits in: the reference's own Lanczos, same operator, same 10 forced iterations as the
+        # b200 arm's `lanczos` key
+        try:
+            from cyten import krylov_based, sparse
+
+            class RefOp(sparse.LinearOperator):
+                def matvec(self, t):
+                    return H.matvec(t)
+            t0 = time.perf_counter()
+            _, _, nit = krylov_based.lanczos(RefOp(), theta, {"N_max": 10, "N_min": 10, "P_tol": 0.0})
+            ms = (time.perf_counter() - t0) * 1e3
+            lanczos_info = {"iterations": int(nit), "ms": ms, "ms_per_iteration": ms / int(nit),
+                            "what": "cyten.krylov_based.lanczos on the host cores"}
+        except Exception as e:   # noqa: BLE001
+            lanczos_info = {"error": repr(e)}
     line = {"metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": min(args.warmup, 1),
             "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "impl": "reference",
+            "data": "synthetic", "impl": "reference", "lanczos": lanczos_info,
             "config": {"workload": f"U(1) DMRG two-site H_eff matvec (4 tdot + 5 permute_legs), chi={chi}, D=5, d=2, float64"},
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind,
                              "sample": f"{steps} matvec(s) at chi={chi} on the host cores"},
