@@ -184,8 +184,9 @@ class LanczosGroundState:
         if self._psi0_norm is None:
             self._psi0_norm = beta                                  # only needed by LanczosEvolution
         beta, performed = 1.0, 0
+        v_next = None
         for k in range(self.N_max):
-            v = self._normalised(u, beta)
+            v = v_next if v_next is not None else self._normalised(u, beta)
             self._to_cache((u, beta))                              # v_k = u_k / beta_k
             w = self._same_structure(self._matvec(v), v)
             prev = self._cache[-2] if (k > 0 and not self.reortho) else None
@@ -194,9 +195,12 @@ class LanczosGroundState:
                 u = self._reorthogonalise(u)
             alpha, _, ss, _ = self._scal.tolist()                  # the one synchronisation of the iteration
             self.host_syncs += 1
+            beta = float(np.sqrt(max(ss, 0.0)))
+            # the next normalisation is enqueued BEFORE the host-side convergence test (eigh of the tridiagonal matrix),
+            # so the GPU is not idle during it; if the test then stops the loop the kernel was wasted, nothing else
+            v_next = self._normalised(u, beta) if (abs(beta) >= self.cutoff and k + 1 < self.N_max) else None
             self.h_krylov[k, k] = alpha
             self._calc_result_krylov(k)
-            beta = float(np.sqrt(max(ss, 0.0)))
             self.h_krylov[k, k + 1] = self.h_krylov[k + 1, k] = beta
             performed = k + 1
             if abs(beta) < self.cutoff or (k + 1 >= self.N_min and self._converged(k)):
