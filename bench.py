@@ -22,6 +22,21 @@ import threading
 import time
 from pathlib import Path
 
+
+def _host_cores() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+# The CPU legs (``--impl reference`` and the ``cpu_baseline`` of the b200 arm) use every host core the process may
+# run on.  torch.distributed.run exports OMP_NUM_THREADS=1 to its workers, and OpenBLAS reads the variable when numpy
+# is imported: so the override has to happen HERE, before the first ``import numpy``.
+if "reference" in sys.argv[1:] or any(a.startswith("--impl=reference") for a in sys.argv[1:]):
+    for _v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[_v] = str(_host_cores())
+
 import numpy as np
 
 ROOT = Path(__file__).resolve().parent
@@ -193,6 +208,18 @@ def cpu_svd_time(chi, kind):
     return time.perf_counter() - t0
 
 
+def blas_threads(want: int) -> int:
+    """Sets the BLAS/OpenMP pools of this process to ``want`` threads (works after numpy was imported, unlike the
+    environment variables) and returns the number of threads the BLAS behind numpy really uses."""
+    try:
+        import threadpoolctl
+        threadpoolctl.threadpool_limits(limits=want)
+        pools = [p.get("num_threads", 1) for p in threadpoolctl.threadpool_info() if p.get("user_api") == "blas"]
+        return int(max(pools)) if pools else want
+    except Exception:   # noqa: BLE001
+        return want
+
+
 def reference_available():
     return bool(list((ROOT / "oracle" / "_ref" / "cyten").glob("_core*.so")))
 
@@ -203,9 +230,7 @@ def run_reference(args):
         return
     kind = "reference" if reference_available() else "port"
     chi = args.chi
-    cores = os.cpu_count() or 1
-    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
-    os.environ.setdefault("OPENBLAS_NUM_THREADS", str(cores))
+    cores = blas_threads(_host_cores())
     flops = flops_of_matvec(chi)
     if kind == "reference":
         H, theta, _ = build_reference_heff(chi)
@@ -214,9 +239,10 @@ def run_reference(args):
         from cyten_b200.workloads import build_heff
         from oracle import cabi_numpy
         H, theta, _, _ = build_heff(chi, B200AbelianBackend("cpu", _library=cabi_numpy))
-    for _ in range(min(args.warmup, 1)):
+    warm = max(1, min(args.warmup, 5))
+    for _ in range(warm):
         H.matvec(theta)
-    steps = max(1, min(args.steps, 3))
+    steps = max(1, min(args.steps, 100))     # 0.3 s per matvec at chi=4096 on 16 cores: K steps stay within minutes
     t0 = time.perf_counter()
     for _ in range(steps):
         H.matvec(theta)
@@ -242,7 +268,7 @@ def run_reference(args):
                             "what": "cyten.krylov_based.lanczos on the host cores"}
         except Exception as e:   # noqa: BLE001
             lanczos_info = {"error": repr(e)}
-    line = {"metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": min(args.warmup, 1),
+    line = {"metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warm,
             "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "impl": "reference", "lanczos": lanczos_info,
             "config": {"workload": f"U(1) DMRG two-site H_eff matvec (4 tdot + 5 permute_legs), chi={chi}, D=5, d=2, float64"},
@@ -304,8 +330,7 @@ def run_b200(args):
     pg = sh.attach_process_group(be, dist.group.WORLD if world > 1 else None)
     chi = args.chi
     H, theta_full, host, sp = build_heff(chi, be)
-    SH = sh.ShardedHEffective(H, pg, split_heavy=os.environ.get("CYB_SPLIT_HEAVY", "0") == "1",
-                              split_columns=os.environ.get("CYB_SPLIT_COLUMNS", "1") == "1",
+    SH = sh.ShardedHEffective(H, pg, split_columns=os.environ.get("CYB_SPLIT_COLUMNS", "1") == "1",
                               column_heavy=float(os.environ.get("CYB_COL_HEAVY", "0.35")))
     # multi-GPU: theta lives sharded along the sectors of vR (LPT by block volume); the matvec chain is
     # rank-local until vR is contracted, then one all_reduce of the (small) result arena
@@ -558,7 +583,7 @@ def run_b200(args):
         cpu = None
         if not args.no_cpu_baseline and world == 1:
             cpu = cpu_baseline(args)
-        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3) + 1,
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic",
                 "config": {"workload": f"U(1) DMRG two-site H_eff matvec (4 tdot + 5 permute_legs), chi={chi}, D=5, d=2, float64",
@@ -600,7 +625,7 @@ def fp64_peak_tflops(dev):
 
 
 def cpu_baseline(args):
-    cores = os.cpu_count() or 1
+    cores = blas_threads(_host_cores())
     kind = "reference" if reference_available() else "port"
     chi = args.cpu_chi or min(args.chi, 4096)
     try:

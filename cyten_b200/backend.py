@@ -853,6 +853,8 @@ class B200AbelianBackend(Blas1Mixin):
                        ptr(keep), ptr(result), self._stream())
             keep_h = keep[:n].cpu().numpy().astype(bool)
             res_h = result.cpu().numpy()
+        if res_h[2] < 0:
+            raise _lib.CytenB200Error("truncate_singular_values: the singular values contain non-finite entries")
         mults, secs = [], []
         for bi_large in range(leg.num_sectors):
             b0, b1 = leg.slices[bi_large]

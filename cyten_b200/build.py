@@ -30,7 +30,8 @@ def _stale(target: Path, deps: list[Path]) -> bool:
 
 def build(force: bool = False, verbose: bool = False) -> Path:
     OBJ.mkdir(exist_ok=True)
-    common = [CSRC / "common.cuh", HERE.parent / "include" / "cyten_b200.h"]
+    # every header any source may include: editing block_jacobi.cuh must rebuild factorize.o
+    common = [*sorted(CSRC.glob("*.cuh")), HERE.parent / "include" / "cyten_b200.h"]
     jobs = []
     for name in SOURCES:
         src, obj = CSRC / f"{name}.cu", OBJ / f"{name}.o"

@@ -58,6 +58,21 @@ struct Scratch {
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// One-time work PER DEVICE at a call site (cudaFuncSetAttribute is a per-device setting): ``static PerDeviceOnce once;
+// if (once.first()) { ... }``.  Repeating the guarded work is harmless, so no lock.
+struct PerDeviceOnce {
+    unsigned long long done = 0ull;
+    bool first()
+    {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess) return true;
+        const unsigned long long bit = 1ull << (dev & 63);
+        if (done & bit) return false;
+        done |= bit;
+        return true;
+    }
+};
+
 // ---- device helpers -----------------------------------------------------------------------
 #ifdef __CUDACC__
 

@@ -745,12 +745,11 @@ static int run_block_jacobi(const void* a, void* o0, double* s_out, void* o2, vo
 {
     constexpr int CM = CX ? 2 : 1;
     constexpr size_t SMEM_ROT = CX ? BJ_SMEM_ROT_CX : BJ_SMEM_ROT, SMEM_APPLY = CX ? BJ_SMEM_APPLY_CX : BJ_SMEM_APPLY;
-    static bool configured = false;
-    if (!configured) {
+    static PerDeviceOnce configured;
+    if (configured.first()) {
         CYB_CHECK_CUDA(cudaFuncSetAttribute(bj_gram_kernel<CX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BJ_SMEM_GRAM));
         CYB_CHECK_CUDA(cudaFuncSetAttribute(bj_rotate_kernel<CX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_ROT));
         CYB_CHECK_CUDA(cudaFuncSetAttribute(bj_apply_kernel<CX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_APPLY));
-        configured = true;
     }
     const int nbig = (int)big.size();
     const size_t nmat = descs.size();

@@ -753,41 +753,18 @@ __global__ void __launch_bounds__(SK_THREADS, 3) skinny_gemm_kernel(const double
     }
 }
 
-using CfgR = GemmCfg<false, 128, 128, 16, 4, 2, 4>;   // 8 warps, 4 x 8 interleaved 8x8 groups per warp, 4-stage pipeline
-// tuning variants (same 128 x 128 tile grid, so one schedule serves all); selected with CYB_GEMM_VARIANT
-using CfgR0 = GemmCfg<false, 128, 128, 16, 2, 4, 4, false, false, false>;  // round-1 baseline layout
-using CfgR2 = GemmCfg<false, 128, 128, 16, 2, 4, 4, false, false, true>;   // baseline layout + edge skipping
-using CfgR3 = GemmCfg<false, 128, 128, 32, 2, 4, 3, false, false, true>;   // BK = 32, 3 stages
-using CfgR4 = GemmCfg<false, 128, 128, 8, 2, 4, 6, false, false, true>;    // BK = 8, 6 stages
-using CfgR5 = GemmCfg<false, 128, 128, 16, 2, 4, 4, true, false, true>;    // interleaved, wm slow
-using CfgR6 = GemmCfg<false, 128, 128, 32, 4, 2, 3>;                       // current layout, BK = 32
-using CfgR7 = GemmCfg<false, 128, 64, 16, 4, 2, 3, true, true, true, 2>;   // 128 x 64 tiles, two CTAs per SM
-using CfgR8 = GemmCfg<false, 128, 64, 16, 4, 2, 3, false, false, false, 2>;
-using CfgR9 = GemmCfg<false, 64, 128, 16, 2, 4, 3, false, false, false, 2>;
-using CfgR10 = GemmCfg<false, 64, 64, 16, 2, 2, 3, false, false, false, 4>;   // 4 warps, 4 CTAs per SM
-using CfgR11 = GemmCfg<false, 128, 64, 8, 4, 2, 4, false, false, false, 2>;   // BK = 8, 4 stages
-using CfgR12 = GemmCfg<false, 64, 64, 32, 2, 2, 3, false, false, false, 3>;   // 64 x 64, BK = 32
-using CfgR13 = GemmCfg<false, 64, 64, 16, 2, 2, 3, true, true, true, 4>;      // 64 x 64, interleaved groups + edge skipping
-using CfgR14 = GemmCfg<false, 64, 64, 16, 2, 2, 3, false, false, true, 4>;    // 64 x 64, contiguous groups + edge skipping
-using CfgR15 = GemmCfg<false, 64, 64, 16, 2, 2, 4, false, false, true, 4>;    // ... 4 stages
-
-static int gemm_variant()
-{
-    // default: 64 x 64 tiles, 4 warps, four CTAs per SM (22.8 TFLOP/s on the chi = 4096 H_eff GEMMs; the
-    // 128 x 128 / one-CTA-per-SM layout of the first version reached 18.5) -- profiles/r1b
-    static const int v = [] { const char* e = getenv("CYB_GEMM_VARIANT"); return e ? atoi(e) : 10; }();
-    return v;
-}
+// float64: 64 x 64 tiles, 4 warps, four CTAs per SM (22.8 TFLOP/s on the chi = 4096 H_eff GEMMs; the 128 x 128 /
+// one-CTA-per-SM layout of the first version reached 18.5, and 13 further tile / pipeline variants measured within
+// -2 ... -20 % of this one -- profiles/r1b, profiles/r1c)
+using CfgR = GemmCfg<false, 64, 64, 16, 2, 2, 3, false, false, false, 4>;
 using CfgC = GemmCfg<true, 128, 64, 8, 4, 2, 4>;      // 8 warps, 4 x 4 interleaved groups per warp, complex
 
 template <class Cfg>
 static int launch_gemm(const void* a, const void* b, void* c, GemmTables T, cudaStream_t stream)
 {
-    static bool configured = false;
-    if (!configured) {
+    static PerDeviceOnce configured;
+    if (configured.first())
         CYB_CHECK_CUDA(cudaFuncSetAttribute(grouped_gemm_kernel<Cfg>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
-        configured = true;
-    }
     grouped_gemm_kernel<Cfg><<<sm_count() * Cfg::MINB, Cfg::THREADS, Cfg::SMEM, stream>>>(
         static_cast<const double*>(a), static_cast<const double*>(b), static_cast<double*>(c), T);
     CYB_LAUNCH_CHECK();
@@ -836,17 +813,9 @@ int cyb_grouped_gemm_prepare(int dtype, const int64_t* out_mn, const int64_t* ou
     double* cost[2];
     gemm_tables(T, cost, out_mn, nullptr, out_pair_ptr, pairs, nblocks, workspace);
     // streaming kernel: aim at SK_UNITS_PER_SLOT work units per resident CTA (3 per SM)
-    static const int ups = [] { const char* e = getenv("CYB_SK_UNITS_PER_SLOT"); return e ? atoi(e) : 8; }();
+    const int ups = 8;
     const int64_t sk_target = (int64_t)sm_count() * 3 * ups;
     if (dtype == CYB_F64) {
-        const int v = gemm_variant();
-        if (v == 10 || v == 12 || v == 13 || v == 14 || v == 15)
-            gemm_schedule_kernel<64, 64, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket, 0);
-        else if (v == 7 || v == 8 || v == 11)
-            gemm_schedule_kernel<128, 64, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket, 0);
-        else if (v == 9)
-            gemm_schedule_kernel<64, 128, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket, 0);
-        else
         gemm_schedule_kernel<CfgR::BM, CfgR::BN, false><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[0], (int64_t*)T[0].order, (int64_t*)T[0].tile_start, T[0].ticket, 0);
         gemm_schedule_kernel<CfgR::BM, CfgR::BN, true><<<1, 1024, 0, stream>>>(out_mn, out_pair_ptr, pairs, block_subset, nblocks, cost[1], (int64_t*)T[1].order, (int64_t*)T[1].tile_start, T[1].ticket, sk_target);
     } else {
@@ -875,34 +844,16 @@ int cyb_grouped_gemm_run(const void* a, const void* b, void* c, int dtype, const
     const double* A = static_cast<const double*>(a);
     const double* B = static_cast<const double*>(b);
     double* C = static_cast<double*>(c);
-    static bool sk_configured = false;
-    if (!sk_configured) {
+    static PerDeviceOnce sk_configured;
+    if (sk_configured.first()) {
         CYB_CHECK_CUDA(cudaFuncSetAttribute(skinny_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SK_SMEM_RING));
         CYB_CHECK_CUDA(cudaFuncSetAttribute(skinny_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SK_SMEM_RING));
-        sk_configured = true;
     }
     const int sk_grid = sm_count() * 3;   // resident CTAs; units are drawn from an atomic ticket
     if (dtype == CYB_F64) {
         skinny_gemm_kernel<false><<<sk_grid, SK_THREADS, SK_SMEM_RING, stream>>>(A, B, C, T[1]);
         CYB_LAUNCH_CHECK();
-        switch (gemm_variant()) {
-            case 0: return launch_gemm<CfgR0>(a, b, c, T[0], stream);
-            case 2: return launch_gemm<CfgR2>(a, b, c, T[0], stream);
-            case 3: return launch_gemm<CfgR3>(a, b, c, T[0], stream);
-            case 4: return launch_gemm<CfgR4>(a, b, c, T[0], stream);
-            case 5: return launch_gemm<CfgR5>(a, b, c, T[0], stream);
-            case 6: return launch_gemm<CfgR6>(a, b, c, T[0], stream);
-            case 7: return launch_gemm<CfgR7>(a, b, c, T[0], stream);
-            case 8: return launch_gemm<CfgR8>(a, b, c, T[0], stream);
-            case 9: return launch_gemm<CfgR9>(a, b, c, T[0], stream);
-            case 10: return launch_gemm<CfgR10>(a, b, c, T[0], stream);
-            case 11: return launch_gemm<CfgR11>(a, b, c, T[0], stream);
-            case 12: return launch_gemm<CfgR12>(a, b, c, T[0], stream);
-            case 13: return launch_gemm<CfgR13>(a, b, c, T[0], stream);
-            case 14: return launch_gemm<CfgR14>(a, b, c, T[0], stream);
-            case 15: return launch_gemm<CfgR15>(a, b, c, T[0], stream);
-            default: return launch_gemm<CfgR>(a, b, c, T[0], stream);
-        }
+        return launch_gemm<CfgR>(a, b, c, T[0], stream);
     }
     skinny_gemm_kernel<true><<<sk_grid, SK_THREADS, SK_SMEM_RING, stream>>>(A, B, C, T[1]);
     CYB_LAUNCH_CHECK();

@@ -8,6 +8,7 @@
 // n <= d*chi values: one CTA, everything stays in L1/L2.  A constraint that would leave no
 // admissible cut is ignored, like combine_constraints in the reference.
 #include "common.cuh"
+#include <math_constants.h>
 
 namespace cyb {
 
@@ -52,13 +53,15 @@ __global__ void __launch_bounds__(TR_RANK_THREADS) truncate_rank_kernel(TruncArg
     __shared__ double s_e[TR_RANK_THREADS];
     const int64_t n = P.n;
     const int64_t i = (int64_t)blockIdx.x * TR_RANK_THREADS + threadIdx.x;
-    const double si = i < n ? P.s[i] : 0.0, ei = si * si;
+    // NaN compares false with everything: ranks would collide and slots of piv[] stay unwritten (an out-of-bounds
+    // scatter later).  The sort key maps NaN to +inf so the order is total; the select kernel reports non-finite input.
+    const double si = i < n ? P.s[i] : 0.0, ei = (si != si) ? CUDART_INF : si * si;
     int64_t rank = 0;
     for (int64_t base = 0; base < n; base += TR_RANK_THREADS) {
         const int64_t j = base + threadIdx.x;
         const double sj = j < n ? P.s[j] : 0.0;
         __syncthreads();
-        s_e[threadIdx.x] = sj * sj;
+        s_e[threadIdx.x] = (sj != sj) ? CUDART_INF : sj * sj;
         __syncthreads();
         const int cnt = (int)min((int64_t)TR_RANK_THREADS, n - base);
         for (int t = 0; t < cnt; ++t) {
@@ -78,8 +81,22 @@ __global__ void __launch_bounds__(TR_THREADS) truncate_select_kernel(TruncArgs P
 {
     __shared__ double s_scan[33];
     __shared__ long long s_cut;
+    __shared__ int s_bad;
     const int tid = threadIdx.x;
     const int64_t n = P.n;
+    if (tid == 0) s_bad = 0;
+    __syncthreads();
+    {
+        int bad = 0;
+        for (int64_t i = tid; i < n; i += TR_THREADS) bad |= !isfinite(P.ssort[i]);
+        if (bad) atomicOr(&s_bad, 1);
+    }
+    __syncthreads();
+    if (s_bad) {     // unconverged / overflowed factorisation upstream: no selection, the host raises
+        for (int64_t i = tid; i < n; i += TR_THREADS) P.keep[i] = 0;
+        if (tid == 0) { P.result[0] = 0.0; P.result[1] = 0.0; P.result[2] = -1.0; P.result[3] = 0.0; }
+        return;
+    }
     // inclusive cumulative sum (sequential order of additions per chunk differs from np.cumsum
     // only in rounding; used for the trunc_cut test and err/new_norm)
     {

@@ -321,8 +321,8 @@ class ShardedHEffective:
     contractions leave ``vR`` open and are rank-local; the last one contracts ``vR`` with RP, so each
     rank holds a partial sum over its ``vR`` sectors and one all_reduce finishes the matvec."""
 
-    def __init__(self, H, pg: ProcessGroup, shard_leg="vR", split_heavy=False, split_columns=False, column_align=16, column_heavy=0.6):
-        self.H, self.pg, self.shard_leg, self.split_heavy = H, pg, shard_leg, split_heavy
+    def __init__(self, H, pg: ProcessGroup, shard_leg="vR", split_columns=False, column_align=16, column_heavy=0.6):
+        self.H, self.pg, self.shard_leg = H, pg, shard_leg
         self.split_columns, self.column_align, self.column_heavy = split_columns, column_align, column_heavy
         self.chains = [(H, None)]
 
@@ -331,7 +331,7 @@ class ShardedHEffective:
         to a range of vR indices is a tensor on a narrower leg; the first three contractions keep that leg open and
         the last contracts it with the same rows of RP, so rank r runs the unchanged chain on (theta_r, RP_r) and the
         partial results add up in the all_reduce.  No flops are duplicated and the GEMMs keep their fat dimensions
-        (only the vR extent shrinks), unlike the row-sector split of ``split_heavy``."""
+        (only the vR extent shrinks)."""
         from .workloads import HEffective
         H, pg = self.H, self.pg
         costs = flop_costs_of_leg(theta, self.shard_leg, H.matvec)
@@ -353,67 +353,22 @@ class ShardedHEffective:
 
     def shard(self, theta: SymmetricTensor) -> SymmetricTensor:
         """Rank-local part of theta.  Work items are the sectors of ``shard_leg`` weighted by the flops each causes
-        in the matvec chain; a sector heavier than ~one rank's share (the central sectors: 20 % of the flops sit
-        on q = 0 at chi = 4096) is split further along the OUTPUT sectors ``vL'`` of LP -- LP restricted to a subset
-        of its row sectors is again just a block subset, every later contraction keeps ``vL'`` open, so the parts
-        stay disjoint in work and their results add up.  Items go to ranks by LPT; identical on every rank
-        (pure integer bookkeeping).  The split is OFF by default (``split_heavy``): measured at chi = 4096 / 8 ranks
-        (profiles/r1c/README.md) every extra chain pays the fixed cost of 11 more small kernels and the GEMM rate
-        of the pieces drops to 5-8 TFLOP/s, so the balanced parts run slower (0.9-1.4 ms per rank, graph replay)
-        than the unbalanced whole sectors (0.41-0.68 ms)."""
+        in the matvec chain (plan-only passes); items go to ranks by LPT, identical on every rank (pure integer
+        bookkeeping).  With ``split_columns`` the heavy sectors are cut into index ranges first (``shard_columns``)."""
         self.chains = [(self.H, None)]
         if self.pg.world == 1:
             return theta
         if self.split_columns:
             return self.shard_columns(theta)
-        from .workloads import HEffective
         H, pg = self.H, self.pg
         costs = flop_costs_of_leg(theta, self.shard_leg, H.matvec)
         self.costs = costs
-        ideal = float(costs.sum()) / pg.world
         ax = theta.get_leg_idcs([self.shard_leg])[0]
-        lp = H.LP.data
-        w_rows = np.bincount(lp.block_inds[:, 0], weights=lp.sizes.astype(np.float64),
-                             minlength=H.LP.codomain.factors[0].num_sectors)
-        items = []          # (cost, vR sector, vL' sectors of LP or None)
-        for sec, c in enumerate(costs):
-            if c <= 0:
-                continue
-            nparts = int(np.ceil(c / (0.5 * ideal))) if (self.split_heavy and c > 0.9 * ideal) else 1
-            nparts = min(nparts, int(np.count_nonzero(w_rows)))
-            if nparts <= 1:
-                items.append((float(c), sec, None))
-                continue
-            # exact flops of (this vR sector) x (each row sector of LP): one more plan-only pass per row sector
-            th_sec = take_blocks(theta, np.nonzero(theta.data.block_inds[:, ax] == sec)[0])
-            w_sec = np.zeros(len(w_rows))
-            for a in np.nonzero(w_rows > 0)[0]:
-                LP_a = take_blocks(H.LP, np.nonzero(lp.block_inds[:, 0] == a)[0])
-                w_sec[a] = flop_costs_total(th_sec, HEffective(LP_a, H.RP, H.W1, H.W2, H.ct).matvec)
-            part_of_row = lpt_assign(w_sec, nparts)
-            for k in range(nparts):
-                rows = np.nonzero((part_of_row == k) & (w_sec > 0))[0]
-                if len(rows):
-                    items.append((float(w_sec[rows].sum()), sec, rows))
+        items = [(float(c), sec) for sec, c in enumerate(costs) if c > 0]
         owner = lpt_assign(np.asarray([it[0] for it in items]), pg.world)
-        mine = [it for it, o in zip(items, owner) if o == pg.rank]
         self.items, self.item_owner = items, owner
-        my_secs = sorted({it[1] for it in mine})
-        bi_ax = theta.data.block_inds[:, ax]
-        theta_local = take_blocks(theta, np.nonzero(np.isin(bi_ax, my_secs))[0])
-        loc_ax = theta_local.data.block_inds[:, ax]
-        chains = []
-        full_secs = [it[1] for it in mine if it[2] is None]
-        if full_secs:
-            idx = np.nonzero(np.isin(loc_ax, full_secs))[0]
-            chains.append((H, None if len(idx) == theta_local.data.num_blocks else idx))
-        for _, sec, rows in mine:
-            if rows is None:
-                continue
-            LP_A = take_blocks(H.LP, np.nonzero(np.isin(lp.block_inds[:, 0], rows))[0])
-            chains.append((HEffective(LP_A, H.RP, H.W1, H.W2, H.ct), np.nonzero(loc_ax == sec)[0]))
-        self.chains = chains
-        return theta_local
+        my_secs = sorted({it[1] for it, o in zip(items, owner) if o == pg.rank})
+        return take_blocks(theta, np.nonzero(np.isin(theta.data.block_inds[:, ax], my_secs))[0])
 
     def matvec_local(self, theta_local: SymmetricTensor) -> SymmetricTensor:
         """This rank's partial sum of ``H_eff . theta`` on the shared all-blocks layout (sum over its chains)."""

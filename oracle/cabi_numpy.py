@@ -428,6 +428,10 @@ def truncate_selection(S, chi_max=None, chi_min=1, degeneracy_tol=0.0, trunc_cut
 def cyb_truncate_select(s, n, chi_max, chi_min, degeneracy_tol, trunc_cut, svd_min, minimize_error,
                         keep, result, stream=None):
     S = _arr(s, n, np.float64)
+    if not np.all(np.isfinite(S)):          # same contract as the CUDA kernel: no selection, result[2] = -1
+        _arr(keep, n, np.uint8)[:] = 0
+        _arr(result, 4, np.float64)[:] = (0.0, 0.0, -1.0, 0.0)
+        return 0
     mask, err, new_norm = truncate_selection(S, None if chi_max < 0 else int(chi_max), int(chi_min),
                                              float(degeneracy_tol), float(trunc_cut),
                                              None if svd_min < 0 else float(svd_min), bool(minimize_error))

@@ -1,5 +1,6 @@
-"""Worker of tests/test_sharding.py: one process per (virtual) GPU, gloo backend, the host logic of
-cyten_b200 over the numpy oracle of the C-ABI."""
+"""Worker of tests/test_sharding.py: one process per (virtual) GPU.  ``mode="gloo"``: gloo backend, the host logic of
+cyten_b200 over the numpy oracle of the C-ABI (CPU suite).  ``mode="nccl"``: one rank per real GPU, NCCL, the CUDA
+library -- the sharded results are compared with the UNSHARDED result computed on the same GPU."""
 import os
 import sys
 from pathlib import Path
@@ -15,36 +16,49 @@ def _dense_of(T):
     return T.to_dense()
 
 
-def worker(rank, world, port, out_dir):
+def worker(rank, world, port, out_dir, mode="gloo", chi=64):
     import torch
     import torch.distributed as dist
     from cyten_b200 import sharding as sh
     from cyten_b200 import tensors as ct
     from cyten_b200.backend import B200AbelianBackend
-    from cyten_b200.workloads import build_heff, mps_tensor, u1_bond_leg, u1_phys_leg
-    from oracle import cabi_numpy
+    from cyten_b200.workloads import CONFIG_LEGS, build_heff, mps_tensor, u1_bond_leg, u1_phys_leg
 
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
-    dist.init_process_group("gloo", rank=rank, world_size=world)
+    if mode == "nccl":
+        torch.cuda.set_device(rank)
+        dev = torch.device(f"cuda:{rank}")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    else:
+        dev = torch.device("cpu")
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+
+    def tt(x, dtype=None):      # scalars for the collectives live where the process group wants them
+        return torch.tensor(x, dtype=dtype, device=dev)
     try:
-        be = B200AbelianBackend("cpu", _library=cabi_numpy)
+        if mode == "nccl":
+            be = B200AbelianBackend(dev)
+        else:
+            from oracle import cabi_numpy
+            be = B200AbelianBackend("cpu", _library=cabi_numpy)
         pg = sh.attach_process_group(be, dist.group.WORLD)
         assert (pg.rank, pg.world) == (rank, world)
         res = {}
 
         # ---- H_eff matvec: sharded chain + one all_reduce == unsharded ----
-        H, theta, _, _ = build_heff(64, be, Q=3, sigma=1.2)
+        Q, sigma = CONFIG_LEGS.get(chi, (3, 1.2))
+        H, theta, _, _ = build_heff(chi, be, Q=Q, sigma=sigma)
         want = H.matvec(theta)
-        SH = sh.ShardedHEffective(H, pg, split_heavy=True)     # also exercises the 2-D split of heavy sectors (world 3)
+        SH = sh.ShardedHEffective(H, pg)                       # whole vR sectors by flop-cost LPT
         th_loc = SH.shard(theta)
-        nblk = torch.tensor([th_loc.data.num_blocks])
+        nblk = tt([th_loc.data.num_blocks])
         dist.all_reduce(nblk)
         assert int(nblk.item()) >= theta.data.num_blocks          # cover (a heavy sector may live on several ranks,
         #                                                            each with a disjoint part of LP's rows)
         be.plan_mkn = []
         got = SH.matvec(th_loc)
-        fl = torch.tensor([float(sum(be.plan_mkn))], dtype=torch.float64)
+        fl = tt([float(sum(be.plan_mkn))], dtype=torch.float64)
         be.plan_mkn = []
         H.matvec(theta)
         fl_full = float(sum(be.plan_mkn))
@@ -58,14 +72,14 @@ def worker(rank, world, port, out_dir):
         res["matvec_max"] = float(np.abs(d_want).max())
 
         # ---- the same with the heavy vR sectors cut into index ranges (slice_leg) ----
-        SC = sh.ShardedHEffective(H, pg, split_columns=True, column_align=2, column_heavy=0.25)
+        SC = sh.ShardedHEffective(H, pg, split_columns=True, column_align=2 if chi <= 64 else 16, column_heavy=0.25)
         th_c = SC.shard(theta)
-        cover = torch.tensor([float(th_c.data.sizes.sum())], dtype=torch.float64)
+        cover = tt([float(th_c.data.sizes.sum())], dtype=torch.float64)
         dist.all_reduce(cover)
         assert float(cover.item()) == float(theta.data.sizes.sum())          # every element of theta on exactly one rank
         be.plan_mkn = []
         got_c = SC.matvec(th_c)
-        fl = torch.tensor([float(sum(be.plan_mkn))], dtype=torch.float64)
+        fl = tt([float(sum(be.plan_mkn))], dtype=torch.float64)
         be.plan_mkn = None
         dist.all_reduce(fl)
         assert float(fl.item()) == fl_full, "the column split must not duplicate flops"
@@ -87,18 +101,18 @@ def worker(rank, world, port, out_dir):
             assert np.allclose(_dense_of(full2), _dense_of(full1), rtol=0, atol=1e-9)
 
         # ---- tdot with the output blocks partitioned over the ranks ----
-        v, p = u1_bond_leg(48, 3, 1.2), u1_phys_leg()
+        v, p = (u1_bond_leg(48, 3, 1.2) if chi <= 64 else u1_bond_leg(chi, Q, sigma)), u1_phys_leg()
         A, B = mps_tensor(v, p, v, be, seed=1), mps_tensor(v, p, v, be, seed=2)
         th = ct.tdot(A, B, [2], [0])
         th_loc = sh.tdot_sharded(A, B, [2], [0], pg)
-        nb = torch.tensor([th_loc.data.num_blocks])
+        nb = tt([th_loc.data.num_blocks])
         dist.all_reduce(nb)
         assert int(nb.item()) == th.data.num_blocks               # every output block computed exactly once
         th_rep = sh.all_gather_blocks(th_loc, pg)
         assert np.array_equal(_dense_of(th_rep), _dense_of(th))   # same kernels, same order: bit-exact
 
         # ---- truncated SVD with the sectors LPT-partitioned, global cut via all_gather of S ----
-        for chi_max in (30, 48):
+        for chi_max in ((30, 48) if chi <= 64 else (chi // 2, chi)):
             U1, S1, V1, err1, ren1 = ct.truncated_svd(th, chi_max=chi_max, svd_min=1e-12)
             U, S, Vh, err, ren, owner = sh.truncated_svd_sharded(th, pg, chi_max=chi_max, svd_min=1e-12)
             assert abs(err - err1) <= 1e-14 and ren == ren1
@@ -107,7 +121,7 @@ def worker(rank, world, port, out_dir):
             s_un = {int(r[0]): b for r, b in zip(S1.data.block_inds, S1.data.to_numpy_blocks())}
             for r, b in zip(S.data.block_inds, S.data.to_numpy_blocks()):
                 assert np.array_equal(b, s_un[int(r[0])])
-            kept = torch.tensor([int(S.data.shapes.sum())])
+            kept = tt([int(S.data.shapes.sum())])
             dist.all_reduce(kept)
             assert int(kept.item()) == int(S1.data.shapes.sum())
             Ur, Vr = sh.all_gather_blocks(U, pg), sh.all_gather_blocks(Vh, pg)

@@ -412,6 +412,33 @@ def test_truncate_select_golden(lib):
         assert abs(res[1] - float(z[f"t{t}/new_norm"])) <= 1e-14, t
 
 
+@pytest.mark.parametrize("bad", [np.nan, np.inf])
+def test_truncate_select_rejects_non_finite_input(lib, bad):
+    """A NaN (unconverged / overflowed sector upstream) must not corrupt the rank sort: the kernel keeps nothing and
+    flags the input (result[2] = -1); the host layer raises (next test)."""
+    rng = np.random.default_rng(3)
+    for n in (5, 300, 5000):
+        S = np.abs(rng.standard_normal(n))
+        S[rng.integers(0, n, size=max(1, n // 50))] = bad
+        d_keep, d_res = lib.up(np.ones(n, np.uint8)), lib.empty(4, torch.float64)
+        lib.call("cyb_truncate_select", lib.p(lib.up(S)), n, n // 2, 1, 0.0, 0.0, 1e-12, 1, lib.p(d_keep), lib.p(d_res), lib.stream())
+        assert d_res.cpu().numpy()[2] == -1.0
+        assert not d_keep.cpu().numpy()[:n].any()
+
+
+def test_truncate_singular_values_raises_on_nan(backend):
+    from cyten_b200._lib import CytenB200Error
+    from cyten_b200.data import AbelianBackendData
+    from cyten_b200.spaces import ElementarySpace, u1_symmetry
+    leg = ElementarySpace(u1_symmetry, [[-1], [0], [2]], [3, 4, 2], False)
+    bi = np.asarray([[0, 0], [1, 1], [2, 2]])
+    blocks = [np.asarray([3.0, 2.0, 1.0]), np.asarray([5.0, np.nan, 1.0, 0.5]), np.asarray([2.5, 0.1])]
+    S = AbelianBackendData.from_numpy_blocks(blocks, bi[:, :1], backend.device, dtype="float64", is_sorted=True)
+    S.block_inds = bi
+    with pytest.raises(CytenB200Error, match="non-finite"):
+        backend.truncate_singular_values(S, leg, chi_max=4, svd_min=1e-12)
+
+
 def test_blas1_helpers(lib):
     rng = np.random.default_rng(9)
     for dt, code in ((np.float64, 0), (np.complex128, 1)):

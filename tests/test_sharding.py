@@ -35,3 +35,18 @@ def test_sharded_ops_match_single_process(tmp_path, world):
     from _sharding_worker import worker
     mp.spawn(worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
     assert len(list(tmp_path.glob("rank*.npy"))) == world
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("chi", [64, 1024])
+def test_sharded_ops_match_unsharded_on_gpus_nccl(tmp_path, chi):
+    """The same checks with one rank per real GPU over NCCL and the CUDA library (column-split matvec, sharded tdot,
+    sharded truncated SVD against the unsharded result of the same GPU).  Needs >= 2 GPUs (gpurun --gpus 2)."""
+    import torch
+    import torch.multiprocessing as mp
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs at least 2 GPUs")
+    from _sharding_worker import worker
+    world = 2
+    mp.spawn(worker, args=(world, _free_port(), str(tmp_path), "nccl", chi), nprocs=world, join=True)
+    assert len(list(tmp_path.glob("rank*.npy"))) == world

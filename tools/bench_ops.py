@@ -31,6 +31,9 @@ def parse():
     ap.add_argument("--dtype", default="float64", choices=["float64", "complex128"])
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--no-ref", action="store_true")
+    ap.add_argument("--ref-torch", action="store_true",
+                    help="also time the reference's own GPU path (AbelianBackend + TorchBlockBackend on cuda: torch.matmul per "
+                         "block pair, cuSOLVER per sector; src/block_backend/torch.cpp:1341-1394, 898-911) on the same inputs")
     ap.add_argument("--rows", default="permute,combine,split,tdot,svd,tsvd,qr,eigh,blas1")
     ap.add_argument("--out", default=None)
     return ap.parse_args()
@@ -316,9 +319,77 @@ def main():
                 ref[key] = cpu_time(calls[key], 1 if key in ("a7", "a7+a8", "a9", "a10") else 2)
             except Exception as e:   # noqa: BLE001
                 ref[key] = f"failed: {e!r}"
+    # ---- the reference's GPU path on the same box (comparator only, never the product) ----
+    ref_t, ref_t_kind = {}, None
+    if args.ref_torch and not args.no_ref and list((ROOT / "oracle" / "_ref" / "cyten").glob("_core*.so")):
+        def dev_time(fn, reps=2):
+            fn()
+            torch.cuda.synchronize()
+            best = float("inf")
+            for _ in range(reps):
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                fn()
+                torch.cuda.synchronize()
+                best = min(best, time.perf_counter() - t0)
+            return best * 1e3
+        try:
+            tbe = rc.get_backend("abelian", "torch")
+
+            def mv(T):
+                T2 = T.to_backend(tbe)
+                T2.move_to_device("cuda")
+                return T2
+            tA, tB, tT, tH = mv(rA), mv(rB), mv(rT), mv(rH)
+            tTc = rc.combine_legs(tT, [0, 1], [2, 3])
+            tcalls = {
+                "a3": lambda: rc.permute_legs(tT, ["vR", "p1"], ["vL", "p0"], bend_right=None),
+                "a4": lambda: rc.combine_legs(tT, [0, 1], [2, 3]),
+                "a5": lambda: rc.split_legs(tTc),
+                "a6": lambda: rc.tdot(tA, tB, ["vR"], ["vL"]),
+                "a7": lambda: rc.svd(tT),
+                "a7+a8": lambda: rc.truncated_svd(tT, chi_max=chi, svd_min=1e-14),
+                "a9": lambda: rc.qr(tA),
+                "a10": lambda: rc.eigh(tH, ["a", "b", "c"], False),
+            }
+            ref_t_kind = "reference AbelianBackend+TorchBlockBackend on cuda"
+            for o in out:
+                key = o["row"].split()[0]
+                if key in tcalls:
+                    try:
+                        ref_t[key] = dev_time(tcalls[key], 1 if key in ("a7", "a7+a8") else 2)
+                    except Exception as e:   # noqa: BLE001
+                        ref_t[key] = f"failed: {e!r}"
+        except Exception as e:   # noqa: BLE001
+            ref_t_kind = f"reference torch backend unusable on cuda ({e!r}); per-sector torch.linalg loop instead"
+        # the same library calls without the reference's host layer: torch.linalg.* per sector, torch.matmul per sector
+        tdt = torch.complex128 if cx else torch.float64
+        smats = [torch.randn(m, n, dtype=tdt, device=dev) for m, n in sect]
+        qmats = [torch.randn(m, n, dtype=tdt, device=dev) for m, n in qsect]
+        hmats = [torch.as_tensor(b, device=dev) for b in hb]
+        loops = {
+            "a7": lambda: [torch.linalg.svd(x, full_matrices=False) for x in smats],
+            "a7-gesvdj": lambda: [torch.linalg.svd(x, full_matrices=False, driver="gesvdj") for x in smats],
+            "a7-gesvda": lambda: [torch.linalg.svd(x, full_matrices=False, driver="gesvda") for x in smats],
+            "a9": lambda: [torch.linalg.qr(x, mode="reduced") for x in qmats],
+            "a10": lambda: [torch.linalg.eigh(x) for x in hmats],
+        }
+        loop_ms = {}
+        for k, fn in loops.items():
+            try:
+                loop_ms[k] = dev_time(fn, 2)
+            except Exception as e:   # noqa: BLE001
+                loop_ms[k] = f"failed: {e!r}"
+        print(json.dumps({"row": "cusolver per-sector loops (torch.linalg, same sector shapes)", "chi": chi, "dtype": dt,
+                          "ms": loop_ms, "reference_torch_backend": ref_t_kind}))
+        for o in out:
+            key = o["row"].split()[0]
+            o["cusolver_loop_ms"] = loop_ms.get(key)
     for o in out:
         key = o["row"].split()[0]
         o["ref_cpu_ms"] = ref.get(key)
+        if ref_t:
+            o["ref_torch_cuda_ms"] = ref_t.get(key)
         o["cores"] = os.cpu_count()
         if isinstance(o["ref_cpu_ms"], float):
             o["speedup"] = o["ref_cpu_ms"] / o["gpu_ms"]
