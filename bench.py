@@ -122,8 +122,12 @@ def measured_peaks():
 
 
 # ---- reference arm: the UNMODIFIED reference (oracle/_ref) on the host cores ------------------------------
-def build_reference_heff(chi):
-    sys.path.insert(0, str(ROOT / "oracle" / "_ref"))
+def build_reference_heff(chi, plugin=None):
+    """H_eff and theta as REFERENCE tensors (cyten's own SymmetricTensor / permute_legs / compose) from the same host
+    blocks as the native arm.  ``plugin``: a ``CytenB200Backend`` -- the tensors are then moved onto it, so the very same
+    cyten calls run on the B200 kernels (the ``e2e_plugin`` leg)."""
+    if str(ROOT / "oracle" / "_ref") not in sys.path:
+        sys.path.insert(0, str(ROOT / "oracle" / "_ref"))
     import cyten as ct
     from cyten_b200.workloads import HEFF_LABELS, HEFF_SEEDS, HEffective, heff_spaces, random_blocks
     be = ct.get_backend("abelian", "numpy")
@@ -140,6 +144,11 @@ def build_reference_heff(chi):
                                               is_sorted=True)
         T[name] = ct.SymmetricTensor(data, [conv(l) for l in cod], [conv(l) for l in dom], backend=be,
                                      labels=HEFF_LABELS[name])
+        if plugin is not None:
+            if str(ROOT / "integration") not in sys.path:
+                sys.path.insert(0, str(ROOT / "integration"))
+            from cyten_plugin import to_plugin
+            T[name] = to_plugin(T[name], plugin)
 
     class Ops:
         permute_legs = staticmethod(lambda t, codomain=None, domain=None: ct.permute_legs(t, codomain, domain, bend_right=None))

@@ -26,6 +26,12 @@ from .spaces import AbelianLegPipe, ElementarySpace, TensorProduct
 
 MAX_RANK = _lib.MAX_RANK
 
+# eigh(sort=...): BlockBackend::argsort (block_backend.cpp:759-781) applied to REAL eigenvalues that the kernels
+# deliver in ascending order.  None / '<' / 'SR' / 'SA' leave them as they are; the imaginary-part orders sort all-zero
+# keys; '>' reverses; 'm<' / 'm>' sort by magnitude.
+_EIGH_SORTS = {None: None, "<": None, "SR": None, "SA": None, "SI": "zero", "LI": "-zero",
+               ">": "rev", "LR": "rev", "LA": "rev", "m<": "abs", "SM": "abs", "m>": "-abs", "LM": "-abs"}
+
 
 def conventional_leg_order(codomain: TensorProduct, domain: TensorProduct):
     """``[*codomain, *reversed(domain)]``: the axis order of every block."""
@@ -78,6 +84,7 @@ class B200AbelianBackend(Blas1Mixin):
         self.gemm_events = None     # bench hook: list of (start, end) CUDA events around the GEMM launch
         self.gemm_event_flops = []
         self.shard = None           # multi-GPU hook, see cyten_b200.sharding
+        self.check_convergence = True   # raise when a Jacobi factorisation hits its sweep limit
 
     def _empty(self, dtype, device, block_inds, shapes, zero=False):
         if self.dry_run:
@@ -740,6 +747,7 @@ class B200AbelianBackend(Blas1Mixin):
                 self._call("cyb_batched_svd", ptr(A.buf), ptr(U.buf), ptr(S.buf), ptr(Vh.buf),
                            desc.ctypes.data_as(C.c_void_p), len(present), A.cyb_dtype, ptr(info), self._stream())
         self.last_info = info
+        self._check_converged(info, "svd")
         return U, S, Vh
 
     def qr(self, a, new_co_domain: TensorProduct):
@@ -772,8 +780,8 @@ class B200AbelianBackend(Blas1Mixin):
     def eigh(self, a, new_leg_dual: bool, sort=None):
         """abelian.cpp:1759-1788: per-sector Hermitian eigendecomposition; V starts as eye_data
         (abelian.cpp:1790-1826) and is overwritten where ``a`` has blocks.  Returns (W, V, new_leg)."""
-        if sort not in (None, "<"):
-            raise NotImplementedError("eigh: only ascending eigenvalue order (sort=None or '<')")
+        if sort not in _EIGH_SORTS:
+            raise ValueError(f"Unknown sort option: '{sort}'")      # BlockBackend::argsort, block_backend.cpp:759-781
         A: AbelianBackendData = a.data
         dom0 = a.domain.factors[0]
         new_leg = a.domain.as_ElementarySpace(new_leg_dual)
@@ -797,7 +805,56 @@ class B200AbelianBackend(Blas1Mixin):
                 self._call("cyb_batched_eigh", ptr(A.buf), ptr(W.buf), ptr(V.buf),
                            desc.ctypes.data_as(C.c_void_p), A.num_blocks, A.cyb_dtype, ptr(info), self._stream())
         self.last_info = info
+        self._check_converged(info, "eigh")
+        if _EIGH_SORTS[sort] is not None and A.num_blocks:
+            W, V = self._eigh_reorder(A, W, V, _EIGH_SORTS[sort])
         return W, V, new_leg
+
+    def _eigh_reorder(self, A, W, V, mode):
+        """``perm = argsort(w, sort); w = take(w, perm); v = take(v, perm, axis=1)`` per sector
+        (NumpyBlockBackend::eigh, numpy.cpp:658-680).  The kernels deliver ascending eigenvalues: descending order
+        is a reversal (no read-back); the two by-magnitude orders read the eigenvalues back once (dim(leg) doubles)
+        to build the index lists.  The reordering itself is one gather launch for W and one for V."""
+        nb = A.num_blocks
+        dims = A.shapes[:, 0]
+        if mode == "rev":
+            idx_lists = [np.arange(int(d) - 1, -1, -1, dtype=np.int64) for d in dims]
+        elif mode in ("zero", "-zero"):      # keys = imag(w) = 0: whatever numpy's argsort makes of equal keys
+            idx_lists = [np.argsort(np.zeros(int(d)) * (1.0 if mode == "zero" else -1.0)).astype(np.int64) for d in dims]
+        else:
+            w_host = W.buf.cpu().numpy()
+            idx_lists = []
+            for i in range(nb):
+                w = np.abs(w_host[W.offsets[i]:W.offsets[i] + dims[i]])
+                idx_lists.append(np.argsort(w if mode == "abs" else -w).astype(np.int64))
+        idx_ptr = np.concatenate([[0], np.cumsum(dims)]).astype(np.int64)
+        W2 = AbelianBackendData(W.dtype, self.device, self._new_buf(W.dtype, W.buf.numel()), W.block_inds, W.offsets,
+                                W.shapes, sig=W._sig)
+        V2 = AbelianBackendData(V.dtype, self.device, V.buf.clone(), V.block_inds, V.offsets, V.shapes, sig=V._sig)
+        dw = np.zeros((nb, 6), dtype=np.int64)
+        dv = np.zeros((nb, 6), dtype=np.int64)
+        for i in range(nb):
+            vo = V.offsets[A.block_inds[i, 0]]
+            dw[i] = (dims[i], 1, W.offsets[i], W.offsets[i], idx_ptr[i], dims[i])
+            dv[i] = (dims[i], dims[i], vo, vo, idx_ptr[i], dims[i])
+        with self._ctx():
+            d_idx = to_device_i64(np.concatenate(idx_lists), self.device)
+            self._call("cyb_gather_rows_cols", ptr(W.buf), ptr(W2.buf), ptr(to_device_i64(dw, self.device)), ptr(d_idx),
+                       nb, 0, W.cyb_dtype, self._stream())
+            self._call("cyb_gather_rows_cols", ptr(V.buf), ptr(V2.buf), ptr(to_device_i64(dv, self.device)), ptr(d_idx),
+                       nb, 1, V.cyb_dtype, self._stream())
+        return W2, V2
+
+    def _check_converged(self, info, what: str):
+        """A negative ``info`` entry = the Jacobi sweeps of that sector hit the sweep limit (factorize.cu); the
+        reference's LAPACK path raises ``LinAlgError`` there, so this raises instead of returning unconverged
+        factors.  One read-back of nsectors int64 (the factorisation has synchronised already)."""
+        if info is None or not self.check_convergence or self.dry_run:
+            return
+        bad = (info < 0).nonzero().flatten().cpu().numpy() if hasattr(info, "nonzero") else np.nonzero(np.asarray(info) < 0)[0]
+        if len(bad):
+            raise _lib.CytenB200Error(f"{what}: Jacobi sweeps did not converge for sector(s) {bad.tolist()} "
+                                      f"(CYB_ERR_NOCONV)")
 
     # ------------------------------------------------------------------------------------------
     # (a8) truncation

@@ -65,13 +65,14 @@ class _Unwrap:
 class ArenaBlock:
     """One dense block.  ``owner``/``index``: the arena data object and block number this block is a view of (or
     ``None`` for blocks produced by cold-path arithmetic)."""
-    __slots__ = ("_tensor", "owner", "index", "__weakref__")
+    __slots__ = ("_tensor", "owner", "index", "host", "__weakref__")
     __array_priority__ = 1000
 
     def __init__(self, tensor=None, owner=None, index=-1):
         self._tensor = tensor
         self.owner = owner
         self.index = index
+        self.host = None      # optional host copy of a small block (keep masks), spares a device read-back
 
     # -- the torch view (lazy for arena blocks) -------------------------------------------------------------------
     @property
@@ -135,7 +136,7 @@ class ArenaBlock:
         return bool(self.t.item())
 
     def __repr__(self):
-        return f"ArenaBlock({self.t!r})"
+        return repr(np.asarray(self))         # like the numpy blocks of the reference (its reprs embed this)
 
     # -- indexing -------------------------------------------------------------------------------------------------
     @staticmethod
@@ -266,7 +267,7 @@ class _Linalg:
 
     @staticmethod
     def trace(a):
-        return ArenaBlock(torch.trace(_t(a)))
+        return ArenaBlock(torch.diagonal(_t(a), dim1=-2, dim2=-1).sum(-1))      # batched over leading axes (Array API)
 
     @staticmethod
     def qr(a, mode="reduced"):
@@ -435,3 +436,90 @@ class TorchNamespace:
 
 
 NAMESPACE = TorchNamespace
+
+
+def make_block_backend(cyten, device: str):
+    """``ArrayApiBlockBackend`` over :class:`TorchNamespace`, with the handful of block operations the reference's
+    generic Array API backend leaves unimplemented (src/block_backend/array_api.cpp:678, 782, 788, 838, 934, 956, 1002,
+    1111) or implements as an endless ``mul`` <-> ``Block::operator*`` recursion (block_backend.cpp:153-156, 694-697:
+    ``BlockBackend::mul(Scalar, Block)`` calls ``Block * Scalar``, which calls ``get_backend()->mul`` again; the numpy and
+    torch backends override ``mul``, the Array API one does not).  The trampoline ``PyArrayApiBlockBackend``
+    (pybind/block_backend/py_trampolines.hpp:496-862) makes these Python overrides visible to the C++ callers.
+    Cold-path glue only."""
+    base = cyten.block_backends.ArrayApiBlockBackend
+    t2d = {torch.float32: cyten.Dtype.float32, torch.float64: cyten.Dtype.float64, torch.complex64: cyten.Dtype.complex64,
+           torch.complex128: cyten.Dtype.complex128, torch.bool: cyten.Dtype.bool, torch.int64: cyten.Dtype.int64}
+    d2t = {v: k for k, v in t2d.items()}
+
+    class ArenaBlockBackend(base):
+        def _w(self, t: torch.Tensor):
+            """torch tensor -> Block of this backend, keeping its dtype."""
+            return self.as_block(ArenaBlock(t), t2d.get(t.dtype))
+
+        @staticmethod
+        def _t(block) -> torch.Tensor:
+            return unwrap_block(block).t
+
+        @staticmethod
+        def _num(a):
+            if hasattr(a, "to_numpy"):
+                a = a.to_numpy()
+            if isinstance(a, np.ndarray):
+                a = a.item()
+            if isinstance(a, np.generic):
+                a = a.item()
+            return a
+
+        def mul(self, a, b):
+            return self._w(torch.mul(self._t(b), self._num(a)))
+
+        def angle(self, a):
+            return self._w(torch.angle(self._t(a)))
+
+        def sqrt(self, a):
+            return self._w(torch.sqrt(self._t(a)))
+
+        def kron(self, a, b):
+            return self._w(torch.kron(self._t(a), self._t(b)))
+
+        def matrix_exp(self, matrix):
+            return self._w(torch.linalg.matrix_exp(self._t(matrix)))
+
+        def real_if_close(self, a, tol):
+            t = self._t(a)
+            if t.is_complex():
+                eps = torch.finfo(t.real.dtype).eps
+                if bool((t.imag.abs() <= tol * eps).all()):          # numpy: tol > 1 is in units of machine epsilon
+                    t = t.real.clone()
+            return self._w(t)
+
+        def tile(self, a, repeats):
+            t = self._t(a)
+            return self._w(t.repeat(*([int(repeats)] if t.ndim <= 1 else [1] * (t.ndim - 1) + [int(repeats)])))
+
+        def trace_partial(self, a, idcs1, idcs2, remaining_idcs):
+            # the generic implementation flattens the remaining axes (array_api.cpp:1070-1086); the numpy / torch
+            # backends keep them (numpy.cpp:1167-1195)
+            t = self._t(a)
+            rem = [int(i) % t.ndim for i in remaining_idcs]
+            i1, i2 = [int(i) % t.ndim for i in idcs1], [int(i) % t.ndim for i in idcs2]
+            t = t.permute(*rem, *i1, *i2)
+            keep = list(t.shape[:len(rem)])
+            d = 1
+            for s_ in t.shape[len(rem):len(rem) + len(i1)]:
+                d *= int(s_)
+            t = t.reshape(*keep, d, d)
+            return self._w(torch.diagonal(t, dim1=-2, dim2=-1).sum(-1))
+
+        def block_from_diagonal(self, diag):
+            return self._w(torch.diag(self._t(diag)))
+
+        def block_from_mask(self, mask, dtype):
+            m = self._t(mask).to(torch.bool)
+            (M,) = m.shape
+            cols = torch.nonzero(m).flatten()
+            res = torch.zeros((len(cols), M), dtype=d2t[dtype], device=m.device)
+            res[torch.arange(len(cols), device=m.device), cols] = 1
+            return self._w(res)
+
+    return ArenaBlockBackend(TorchNamespace(device), device)

@@ -69,12 +69,18 @@ def _stage_python_package() -> None:
         "__version__ = '0.0.1+ref'\n__version_tuple__ = (0, 0, 1)\n__commit_id__ = 'reference'\n"
         "version = __version__\nversion_tuple = __version_tuple__\ncommit_id = __commit_id__\n"
     )
-    # reference helpers needed to drive its own tests / toy codes
-    for name in ("toycodes",):
+    # reference helpers needed to drive its own tests / toy codes (the GPU box has no /root/reference: the reference's
+    # pytest suite travels with the built artefact so that it can be run THROUGH the plugin there, see
+    # integration/pytest_cyten_b200.py and tests/test_plugin.py)
+    for name in ("toycodes", "tests/python_tests"):
         if (REF / name).exists():
             if (OUT / name).exists():
                 shutil.rmtree(OUT / name)
+            (OUT / name).parent.mkdir(parents=True, exist_ok=True)
             shutil.copytree(REF / name, OUT / name)
+    for name in ("conftest.py", "pyproject.toml"):
+        if (REF / name).exists():
+            shutil.copy(REF / name, OUT / name)
 
 
 def main() -> int:
