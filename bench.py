@@ -56,6 +56,7 @@ def parse():
     ap.add_argument("--svd-chi", type=int, default=None)
     ap.add_argument("--no-svd", action="store_true")
     ap.add_argument("--no-lanczos", action="store_true")
+    ap.add_argument("--no-plugin", action="store_true", help="skip the e2e_plugin leg (cyten API through the plugin)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel eagerly instead of replaying a CUDA graph")
     ap.add_argument("--cpu-chi", type=int, default=None, help="bond dimension of the bounded CPU sample")
@@ -508,6 +509,16 @@ def run_b200(args):
     e2e_val = flops / e2e_s / 1e9
     e2e_check = float(out_host[(pipe_steps - 1) & 1][:8].abs().sum())   # the result really arrived on the host
 
+    # ---- the same step through the reference-facing plugin: cyten.permute_legs / cyten.compose on tensors that live on
+    # CytenB200Backend (integration/cyten_plugin.py), theta uploaded from pinned host memory and the result downloaded
+    # every step, serial (no pipelining, no CUDA graph: what a cyten user gets by switching the backend) ----
+    plugin_info = None
+    if world == 1 and not args.no_plugin and reference_available():
+        try:
+            plugin_info = e2e_plugin(args, chi, dev, flops, y)
+        except Exception as e:   # noqa: BLE001 -- an extra, must never cost the bench line
+            plugin_info = {"error": repr(e)}
+
     # ---- truncated SVD of the two-site theta at chi (BASELINE config 3) ----
     # theta[vL, p0 | p1, vR] with N(0,1) blocks (the synthetic input of SURVEY 8(d)); the rank-chi theta = tdot(A, B)
     # of two MPS tensors (half of every sector's singular values are numerically zero, the slow case for a Jacobi
@@ -608,10 +619,57 @@ def run_b200(args):
                         "mode": "3-stream pipeline (upload | matvec | download), two theta arenas; bytes are per rank",
                         "host_checksum": e2e_check},
                 "gpu_launches": launches, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
-                "svd_ms": svd_ms, "svd": svd_info, "lanczos": lanczos_info}
+                "e2e_plugin": plugin_info, "svd_ms": svd_ms, "svd": svd_info, "lanczos": lanczos_info}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def e2e_plugin(args, chi, dev, flops, y_native):
+    """One H_eff matvec per step written with cyten's OWN calls (toycodes/tenpy_toycodes/d_dmrg.py:70-88) on tensors of
+    the plugin backend; every step uploads theta from pinned host memory, runs the 5 permute_legs + 4 compose virtuals
+    (each one: reference C++ -> trampoline -> plugin -> cyb:: kernels) and downloads the result."""
+    import torch
+    if str(ROOT / "oracle" / "_ref") not in sys.path:
+        sys.path.insert(0, str(ROOT / "oracle" / "_ref"))
+    if str(ROOT / "integration") not in sys.path:
+        sys.path.insert(0, str(ROOT / "integration"))
+    from cyten_plugin import install
+    plugin = install(str(dev), key="b200-bench")
+    H, theta, ct = build_reference_heff(chi, plugin=plugin)
+    arena = plugin._arena(theta.data, theta.num_legs)          # theta's device arena (its blocks are views into it)
+    nel = arena.buf.numel()
+    pinned = torch.empty(nel, dtype=torch.float64).pin_memory()
+    pinned.copy_(arena.buf)
+    y = H.matvec(theta)
+    ya = plugin._arena(y.data, y.num_legs)
+    out = torch.empty(ya.buf.numel(), dtype=torch.float64).pin_memory()
+    # same host blocks, same kernels, same plans as the native arm: the results must agree
+    yn = y_native.data
+    same = bool(ya.num_blocks == yn.num_blocks and np.array_equal(ya.block_inds, yn.block_inds) and
+                all(torch.allclose(ya.block(i), yn.block(i), rtol=0, atol=1e-10 * float(yn.block(i).abs().max()))
+                    for i in range(yn.num_blocks)))
+    for _ in range(2):
+        H.matvec(theta)
+    for c in (plugin.hot_calls, plugin.cold_calls, plugin.fallbacks):
+        c.clear()
+    plugin.fast.launches = 0
+    steps = max(3, min(args.steps, 10))
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        arena.buf.copy_(pinned, non_blocking=True)
+        y = H.matvec(theta)
+        out.copy_(plugin._arena(y.data, y.num_legs).buf, non_blocking=True)
+        torch.cuda.synchronize()
+    dt = (time.perf_counter() - t0) / steps
+    return {"value": flops / dt / 1e9, "unit": UNIT, "ms_per_step": dt * 1e3, "steps": steps,
+            "h2d_bytes_per_step": nel * 8, "d2h_bytes_per_step": out.numel() * 8,
+            "api": "cyten.permute_legs / cyten.compose on CytenB200Backend tensors (get_backend('abelian', 'b200-bench'))",
+            "hot_calls_per_step": {k: v / steps for k, v in plugin.hot_calls.items()},
+            "fallbacks": dict(plugin.fallbacks), "cold_calls_per_step": {k: v / steps for k, v in plugin.cold_calls.items()},
+            "kernel_launching_calls_per_step": plugin.fast.launches / steps, "matches_native_arm": same,
+            "host_checksum": float(out[:8].abs().sum())}
 
 
 def fp64_peak_tflops(dev):

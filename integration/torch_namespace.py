@@ -53,6 +53,9 @@ def _tt(x, like=None):
     return x
 
 
+_LAST_SHAPE_READ = [None]
+
+
 class _Unwrap:
     """Key for ``block[key]``: the reference forwards unknown keys to ``obj.__getitem__`` (array_api.cpp:181-189), which
     deposits the wrapped object here."""
@@ -64,15 +67,27 @@ class _Unwrap:
 
 class ArenaBlock:
     """One dense block.  ``owner``/``index``: the arena data object and block number this block is a view of (or
-    ``None`` for blocks produced by cold-path arithmetic)."""
-    __slots__ = ("_tensor", "owner", "index", "host", "__weakref__")
+    ``None`` for blocks produced by cold-path arithmetic).  ``device`` / ``dtype`` are plain attributes (the reference
+    reads them several times per block when it wraps the object, array_api.cpp:112-122)."""
+    __slots__ = ("_tensor", "owner", "index", "host", "device", "dtype", "__weakref__")
     __array_priority__ = 1000
 
-    def __init__(self, tensor=None, owner=None, index=-1):
+    def __init__(self, tensor=None, owner=None, index=-1, device=None, dtype=None):
         self._tensor = tensor
         self.owner = owner
         self.index = index
         self.host = None      # optional host copy of a small block (keep masks), spares a device read-back
+        if tensor is not None:
+            self.device = str(tensor.device)
+            self.dtype = tensor.dtype
+        else:
+            self.device = device if device is not None else str(owner.device)
+            self.dtype = dtype if dtype is not None else (torch.complex128 if owner.dtype == "complex128" else torch.float64)
+
+    def rebind(self, owner, index):
+        """Points this block at block ``index`` of the arena ``owner`` (same values, see CytenB200Backend._arena)."""
+        self._tensor, self.owner, self.index = None, owner, index
+        self.device = str(owner.device)
 
     # -- the torch view (lazy for arena blocks) -------------------------------------------------------------------
     @property
@@ -84,6 +99,7 @@ class ArenaBlock:
     # -- array attributes the reference reads ---------------------------------------------------------------------
     @property
     def shape(self):
+        _LAST_SHAPE_READ[0] = self        # see unwrap_block
         if self._tensor is None:
             return tuple(int(s) for s in self.owner.shapes[self.index])
         return tuple(self._tensor.shape)
@@ -91,17 +107,6 @@ class ArenaBlock:
     @property
     def ndim(self):
         return len(self.shape)
-
-    @property
-    def dtype(self):
-        if self._tensor is None:
-            return torch.complex128 if self.owner.dtype == "complex128" else torch.float64
-        return self._tensor.dtype
-
-    @property
-    def device(self):
-        d = self.owner.device if self._tensor is None else self._tensor.device
-        return str(d)
 
     @property
     def size(self):
@@ -196,7 +201,7 @@ class ArenaBlock:
     def __rmul__(self, o):
         # ``1.0 * block`` is how ArrayApiBlockBackend::as_block forces a float dtype (array_api.cpp:594-595): for a
         # block that already is float64 / complex128 the same object comes back -- zero copy
-        if type(o) is float and o == 1.0 and self.dtype in (torch.float64, torch.complex128):
+        if o == 1.0 and type(o) is float and (self.dtype is torch.float64 or self.dtype is torch.complex128):
             return self
         return self._bin(o, torch.mul, True)
 
@@ -243,7 +248,16 @@ class ArenaBlock:
 
 
 def unwrap_block(block) -> ArenaBlock:
-    """The ``ArenaBlock`` inside a reference ``ArrayApiBlockBackend.BlockCls``."""
+    """The ``ArenaBlock`` inside a reference ``ArrayApiBlockBackend.BlockCls``.  The reference exposes no accessor for
+    the wrapped object, but ``block.shape`` is answered by reading ``obj.shape`` (array_api.cpp Block::shape), so the
+    wrapped object announces itself there; ``block[key]`` with a sentinel key (forwarded to ``obj.__getitem__``,
+    array_api.cpp:181-189) is the slower fallback."""
+    _LAST_SHAPE_READ[0] = None
+    block.shape
+    obj = _LAST_SHAPE_READ[0]
+    if obj is not None:
+        _LAST_SHAPE_READ[0] = None
+        return obj
     key = _Unwrap()
     block[key]
     if key.obj is None:
@@ -295,6 +309,8 @@ class TorchNamespace:
 
     # -- creation -----------------------------------------------------------------------------------------------------
     def asarray(self, obj, dtype=None, device=None, copy=None):
+        if type(obj) is ArenaBlock and dtype is None and device is None and not copy:
+            return obj                                           # the hot case: as_block of an arena view
         if isinstance(obj, ArenaBlock):
             same_dtype = dtype is None or obj.dtype == dtype
             same_dev = device is None or torch.device(device) == torch.device(obj.device)
