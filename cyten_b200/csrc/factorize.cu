@@ -23,6 +23,7 @@
 #include <vector>
 #include <cmath>
 #include <algorithm>
+#include <cstdlib>
 
 namespace cyb {
 
@@ -391,13 +392,18 @@ jacobi_svd_kernel(const void* __restrict__ a_, void* __restrict__ o0_, double* _
 
 }  // namespace cyb
 #include "block_jacobi.cuh"
+#include "qr_blocked.cuh"
 namespace cyb {
 
 // ---- QR ---------------------------------------------------------------------------------------
 // Working copy Wt = A^T (n x m): row i of Wt is column i of A.  Hermitian Householder reflectors
 // H_j = I - tau_j u_j u_j^H (tau real), u_j stored in Wt[j][j+1:m] with its head in uhead[j].
-template <bool CX, int G>
-__global__ void __launch_bounds__(FZ_THREADS, 1)
+// BLK (large real sectors): two-level blocking.  An outer panel of QB_NBO = 32 columns is factored by CTA 0 of the team
+// (inner panels of QR_NB reflectors, applied only inside the outer panel); the trailing matrix and, in the second phase,
+// Q take the 32 reflectors at once as compact-WY GEMMs on the FP64 tensor pipe, split over the CTAs of the team
+// (qr_blocked.cuh).
+template <bool CX, int G, bool BLK>
+__global__ void __launch_bounds__(BLK ? QB_THREADS : FZ_THREADS, 1)
 householder_qr_kernel(const void* __restrict__ a_, void* __restrict__ q_, void* __restrict__ r_,
                       void* __restrict__ ws_, double* __restrict__ aux_, FzDesc* __restrict__ descs,
                       const int64_t* __restrict__ sel, int use_smem)
@@ -416,16 +422,30 @@ householder_qr_kernel(const void* __restrict__ a_, void* __restrict__ q_, void* 
     double* tau = aux_ + D.aux_off + 2 * k;              // k
     T* Q = static_cast<T*>(q_) + D.o0_off;      // m x k
     T* R = static_cast<T*>(r_) + D.o1_off;      // k x n
+    constexpr int NT = BLK ? QB_THREADS : FZ_THREADS, NW = NT / 32;   // threads / warps per CTA
     const unsigned trank = Team<G>::rank();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int64_t gthreads = (int64_t)G * FZ_THREADS, gtid = (int64_t)trank * FZ_THREADS + tid;
-    const int64_t gwarps = (int64_t)G * FZ_WARPS, gwarp = (int64_t)trank * FZ_WARPS + warp;
+    const int64_t gthreads = (int64_t)G * NT, gtid = (int64_t)trank * NT + tid;
+    const int64_t gwarps = (int64_t)G * NW, gwarp = (int64_t)trank * NW + warp;
+    // CYB_QR_PROFILE=1: wall time of the phases as seen by thread 0 of CTA 0 of every team (device printf at the end)
+    const bool prof = (use_smem & 2) != 0;
+    use_smem &= 1;
+    unsigned long long pt[13] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, pl = 0;
+    auto tick = [&](int slot) {
+        if (!prof) return;
+        unsigned long long now;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (slot >= 0) pt[slot] += now - pl;
+        pl = now;
+    };
+    tick(-1);
 
     for (int64_t e = gtid; e < n * m; e += gthreads) {
         const int64_t i = e / m, q = e % m;
         E::stcg(&Wt[e], A[q * n + i]);
     }
     Team<G>::sync();
+    tick(0);
 
     // Blocked Householder (compact WY, panels of QR_NB reflectors): H_j0 ... H_j0+nb-1 = I - U T U^H.
     // The panel is factored by CTA 0 of the team (unblocked, on the nb panel rows only); every trailing row
@@ -444,7 +464,7 @@ householder_qr_kernel(const void* __restrict__ a_, void* __restrict__ q_, void* 
         cur_j0 = j0;
         if (!use_smem) return;
         __syncthreads();
-        for (int64_t e = tid; e < (int64_t)nb * m; e += FZ_THREADS) {
+        for (int64_t e = tid; e < (int64_t)nb * m; e += NT) {
             const int64_t j = j0 + e / m, q = e % m;
             s_U[e] = q > j ? E::ldcg(Wt + j * m + q) : (q == j ? E::ldcg(&uhead[j]) : E::zero());
         }
@@ -452,7 +472,7 @@ householder_qr_kernel(const void* __restrict__ a_, void* __restrict__ q_, void* 
     };
     // T of the panel [j0, j0 + nb) into s_T (every CTA builds its own copy): z[b][a] = u_b^H u_a, b < a
     auto build_T = [&](int64_t j0, int nb) {
-        for (int pr = warp; pr < nb * nb; pr += FZ_WARPS) {
+        for (int pr = warp; pr < nb * nb; pr += NW) {
             const int bb = pr / nb, aa = pr % nb;
             if (bb >= aa) continue;
             T dot = E::zero();
@@ -511,12 +531,12 @@ householder_qr_kernel(const void* __restrict__ a_, void* __restrict__ q_, void* 
         }
     };
 
-    for (int64_t j0 = 0; j0 < k; j0 += QR_NB) {
-        const int nb = (int)((k - j0) < QR_NB ? (k - j0) : QR_NB);
-        if (trank == 0 && use_smem) {
+    // unblocked factorisation of the nb panel rows [j0, j0 + nb) by the calling CTA
+    auto factor_panel = [&](int64_t j0, int nb) {
+        if (use_smem) {
             // the nb panel rows are factored in shared memory: one coalesced load, no L2 round trip per step
             __syncthreads();
-            for (int64_t e = tid; e < (int64_t)nb * m; e += FZ_THREADS) s_U[e] = E::ldcg(Wt + j0 * m + e);
+            for (int64_t e = tid; e < (int64_t)nb * m; e += NT) s_U[e] = E::ldcg(Wt + j0 * m + e);
             __syncthreads();
             for (int aa = 0; aa < nb; ++aa) {
                 const int64_t j = j0 + aa;
@@ -538,7 +558,7 @@ householder_qr_kernel(const void* __restrict__ a_, void* __restrict__ q_, void* 
                     uhead[j] = u0;
                     x[j] = tj != 0.0 ? alpha : x0;
                 }
-                for (int i = aa + 1 + warp; i < nb; i += FZ_WARPS) {
+                for (int i = aa + 1 + warp; i < nb; i += NW) {
                     T* y = s_U + (int64_t)i * m;
                     T dot = (lane == 0) ? E::mul(E::conj(u0), y[j]) : E::zero();
                     for (int64_t q = j + 1 + lane; q < m; q += 32) dot = E::add(dot, E::mul(E::conj(x[q]), y[q]));
@@ -549,10 +569,10 @@ householder_qr_kernel(const void* __restrict__ a_, void* __restrict__ q_, void* 
                 }
                 __syncthreads();
             }
-            for (int64_t e = tid; e < (int64_t)nb * m; e += FZ_THREADS)
+            for (int64_t e = tid; e < (int64_t)nb * m; e += NT)
                 if (e % m >= j0) E::stcg(Wt + j0 * m + e, s_U[e]);
             __threadfence();
-        } else if (trank == 0) {
+        } else {
             for (int aa = 0; aa < nb; ++aa) {
                 const int64_t j = j0 + aa;
                 // reflector from x = Wt[j][j:m]; every warp computes the scalars redundantly from the same data
@@ -575,7 +595,7 @@ householder_qr_kernel(const void* __restrict__ a_, void* __restrict__ q_, void* 
                     E::stcg(x + j, tj != 0.0 ? alpha : x0);
                 }
                 // H_j on the remaining panel rows
-                for (int64_t i = j + 1 + warp; i < j0 + nb; i += FZ_WARPS) {
+                for (int64_t i = j + 1 + warp; i < j0 + nb; i += NW) {
                     T* y = Wt + i * m;
                     T dot = (lane == 0) ? E::mul(E::conj(u0), E::ldcg(y + j)) : E::zero();
                     for (int64_t q = j + 1 + lane; q < m; q += 32) dot = E::add(dot, E::mul(E::conj(E::ldcg(x + q)), E::ldcg(y + q)));
@@ -588,6 +608,51 @@ householder_qr_kernel(const void* __restrict__ a_, void* __restrict__ q_, void* 
                 __syncthreads();
             }
         }
+    };
+    // BLK: outer panel width = what fits shared memory next to nothing else (the staging buffers of the block apply
+    // alias it), at most QB_NBO; below 8 rows (m > 3200) the panel stays in global memory (the old inner loop)
+    int nbo_max = QB_NBO;
+    bool panel_in_smem = false;
+    if constexpr (BLK) {
+        const int64_t cap = (int64_t)(QB_SMEM_LIMIT / sizeof(double)) / m - QB_NBI;   // + QB_NBI rows of explicit reflectors
+        panel_in_smem = cap >= 8;
+        if (panel_in_smem && cap < QB_NBO) nbo_max = (int)(cap / QB_NBI) * QB_NBI;
+    }
+    if constexpr (BLK) {
+        double* qb_smem = reinterpret_cast<double*>(qr_smem);
+        for (int64_t J0 = 0; J0 < k; J0 += nbo_max) {
+            const int nbo = (int)((k - J0) < nbo_max ? (k - J0) : nbo_max);
+            const int64_t Jend = J0 + nbo;
+            if (trank == 0 && panel_in_smem) {
+                qr_factor_outer_panel(reinterpret_cast<double*>(Wt), reinterpret_cast<double*>(uhead), tau, J0, nbo, nbo_max, m, qb_smem, prof ? pt : nullptr);
+                tick(1);
+            } else if (trank == 0) {
+                for (int64_t j0 = J0; j0 < Jend; j0 += QR_NB) {
+                    const int nb = (int)((Jend - j0) < QR_NB ? (Jend - j0) : QR_NB);
+                    factor_panel(j0, nb);
+                    __syncthreads();
+                    tick(1);
+                    if (j0 + nb < Jend) {           // the rest of the OUTER panel only
+                        load_panel(j0, nb);
+                        build_T(j0, nb);
+                        for (int64_t i = j0 + nb + warp; i < Jend; i += NW) apply_panel(Wt + i * m, j0, nb, true);
+                        __threadfence();
+                        __syncthreads();
+                    }
+                    tick(2);
+                }
+            }
+            Team<G>::sync();
+            tick(2);
+            if (Jend < n) qr_block_apply(reinterpret_cast<double*>(Wt), Jend, n, reinterpret_cast<const double*>(Wt),
+                                         reinterpret_cast<const double*>(uhead), tau, J0, nbo, m, true, qb_smem, trank, G, prof ? pt : nullptr);
+            Team<G>::sync();
+            tick(3);
+        }
+    } else {
+    for (int64_t j0 = 0; j0 < k; j0 += QR_NB) {
+        const int nb = (int)((k - j0) < QR_NB ? (k - j0) : QR_NB);
+        if (trank == 0) factor_panel(j0, nb);
         Team<G>::sync();
         if (j0 + nb < n) {
             load_panel(j0, nb);
@@ -595,6 +660,7 @@ householder_qr_kernel(const void* __restrict__ a_, void* __restrict__ q_, void* 
             for (int64_t i = j0 + nb + gwarp; i < n; i += gwarps) apply_panel(Wt + i * m, j0, nb, true);
         }
         Team<G>::sync();
+    }
     }
     // R[j][i] = Wt[i][j] for i >= j, 0 below the diagonal
     for (int64_t e = gtid; e < k * n; e += gthreads) {
@@ -604,6 +670,16 @@ householder_qr_kernel(const void* __restrict__ a_, void* __restrict__ q_, void* 
     // Qt = [I_k 0] (k x m), then Q <- H_0 ... H_{k-1} [I;0] by backward accumulation
     for (int64_t e = gtid; e < k * m; e += gthreads) E::stcg(&Qt[e], (e / m == e % m) ? E::one() : E::zero());
     Team<G>::sync();
+    if constexpr (BLK) {
+        double* qb_smem = reinterpret_cast<double*>(qr_smem);
+        for (int64_t J0 = ((k - 1) / nbo_max) * nbo_max; J0 >= 0; J0 -= nbo_max) {
+            const int nbo = (int)((k - J0) < nbo_max ? (k - J0) : nbo_max);
+            // rows c < J0 of Qt are still unit vectors e_c, orthogonal to every u of this panel
+            qr_block_apply(reinterpret_cast<double*>(Qt), J0, k, reinterpret_cast<const double*>(Wt),
+                           reinterpret_cast<const double*>(uhead), tau, J0, nbo, m, false, qb_smem, trank, G, prof ? pt : nullptr);
+            Team<G>::sync();
+        }
+    } else {
     for (int64_t j0 = ((k - 1) / QR_NB) * QR_NB; j0 >= 0; j0 -= QR_NB) {
         const int nb = (int)((k - j0) < QR_NB ? (k - j0) : QR_NB);
         load_panel(j0, nb);
@@ -612,10 +688,19 @@ householder_qr_kernel(const void* __restrict__ a_, void* __restrict__ q_, void* 
         for (int64_t cidx = j0 + gwarp; cidx < k; cidx += gwarps) apply_panel(Qt + cidx * m, j0, nb, false);
         Team<G>::sync();
     }
+    }
+    tick(4);
     for (int64_t e = gtid; e < m * k; e += gthreads) {
         const int64_t q = e / k, cidx = e % k;
         Q[e] = E::ldcg(Qt + cidx * m + q);
     }
+    tick(5);
+    if (prof && tid == 0 && trank == 0)
+        printf("qr team %u m=%lld n=%lld us: load %.1f factor %.1f inner-apply %.1f trailing %.1f form-Q %.1f store %.1f\n",
+               Team<G>::id(), (long long)m, (long long)n, pt[0] * 1e-3, pt[1] * 1e-3, pt[2] * 1e-3, pt[3] * 1e-3, pt[4] * 1e-3, pt[5] * 1e-3);
+    if (prof && tid == 0 && trank == 0)
+        printf("   panel: load %.1f columns %.1f inner-apply %.1f store %.1f | block apply (both phases): pass1 %.1f solve %.1f pass2 %.1f\n",
+               pt[6] * 1e-3, pt[7] * 1e-3, pt[8] * 1e-3, pt[9] * 1e-3, pt[10] * 1e-3, pt[11] * 1e-3, pt[12] * 1e-3);
 }
 
 template <bool CX>
@@ -636,7 +721,16 @@ __global__ void fill_eye_kernel(void* __restrict__ dst_, const int64_t* __restri
 enum FzKind { FZ_SVD = 0, FZ_EIGH = 1, FZ_QR = 2 };
 
 template <class K, class... Args>
+static cudaError_t launch_team_smem_nt(K kernel, int G, int nteams, size_t smem, int nthreads, cudaStream_t stream, Args... args);
+
+template <class K, class... Args>
 static cudaError_t launch_team_smem(K kernel, int G, int nteams, size_t smem, cudaStream_t stream, Args... args)
+{
+    return launch_team_smem_nt(kernel, G, nteams, smem, FZ_THREADS, stream, args...);
+}
+
+template <class K, class... Args>
+static cudaError_t launch_team_smem_nt(K kernel, int G, int nteams, size_t smem, int nthreads, cudaStream_t stream, Args... args)
 {
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -644,7 +738,7 @@ static cudaError_t launch_team_smem(K kernel, int G, int nteams, size_t smem, cu
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(nteams * G), 1, 1);
-    cfg.blockDim = dim3(FZ_THREADS, 1, 1);
+    cfg.blockDim = dim3((unsigned)nthreads, 1, 1);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
@@ -938,6 +1032,8 @@ static int run_factorize(FzKind kind, const void* a, void* o0, double* o1d, void
     do { if ((NT) > 0) { err = launch_team_smem(KERN, G, (int)(NT), SMEM, stream, __VA_ARGS__); if (err != cudaSuccess) { set_error("factorize launch failed: %s", cudaGetErrorString(err)); return CYB_ERR_CUDA; } } } while (0)
     // QR: the QR_NB x m panel lives in shared memory when it fits (else the kernels work through L2)
     size_t qr_smem_small = 0, qr_smem_big = 0;
+    bool qr_panel_big = false;
+    const int qr_prof = (kind == FZ_QR && getenv("CYB_QR_PROFILE")) ? 2 : 0;
     if (kind == FZ_QR) {
         int64_t m_small = 0, m_big = 0;
         for (int64_t i : small) m_small = std::max(m_small, descs[(size_t)i].m);
@@ -947,6 +1043,14 @@ static int run_factorize(FzKind kind, const void* a, void* o0, double* o1d, void
         qr_smem_big = (size_t)QR_NB * (size_t)m_big * esz;
         if (qr_smem_small > lim) qr_smem_small = 0;
         if (qr_smem_big > lim) qr_smem_big = 0;
+        qr_panel_big = qr_smem_big > 0;
+        // real large sectors: the outer panel (factored in shared memory) and the operand staging area of the DMMA block
+        // apply share one region of QB_SMEM_LIMIT bytes; the QR_NB x m inner panel of the global-memory fallback too
+        if (!cx) {
+            static_assert(QB_SMEM_DOUBLES * sizeof(double) <= QB_SMEM_LIMIT, "block apply staging exceeds the shared-memory budget");
+            qr_panel_big = (size_t)QR_NB * (size_t)m_big * esz <= QB_SMEM_LIMIT;
+            qr_smem_big = QB_SMEM_LIMIT;
+        }
     }
     if (kind != FZ_QR && !big.empty()) {
         // large sectors: block Jacobi (block_jacobi.cuh) between the load and the output phases
@@ -976,11 +1080,15 @@ static int run_factorize(FzKind kind, const void* a, void* o0, double* o1d, void
         }
     } else {
         if (cx) {
-            FZ_LAUNCH_SMEM((householder_qr_kernel<true, 1>), 1, small.size(), qr_smem_small, a, o0, o1, d_ws, d_aux, d_desc, sel_small, (int)(qr_smem_small > 0));
-            FZ_LAUNCH_SMEM((householder_qr_kernel<true, FZ_BIG_G>), FZ_BIG_G, big.size(), qr_smem_big, a, o0, o1, d_ws, d_aux, d_desc, sel_big, (int)(qr_smem_big > 0));
+            FZ_LAUNCH_SMEM((householder_qr_kernel<true, 1, false>), 1, small.size(), qr_smem_small, a, o0, o1, d_ws, d_aux, d_desc, sel_small, (int)(qr_smem_small > 0));
+            FZ_LAUNCH_SMEM((householder_qr_kernel<true, FZ_BIG_G, false>), FZ_BIG_G, big.size(), qr_smem_big, a, o0, o1, d_ws, d_aux, d_desc, sel_big, (int)qr_panel_big | qr_prof);
         } else {
-            FZ_LAUNCH_SMEM((householder_qr_kernel<false, 1>), 1, small.size(), qr_smem_small, a, o0, o1, d_ws, d_aux, d_desc, sel_small, (int)(qr_smem_small > 0));
-            FZ_LAUNCH_SMEM((householder_qr_kernel<false, FZ_BIG_G>), FZ_BIG_G, big.size(), qr_smem_big, a, o0, o1, d_ws, d_aux, d_desc, sel_big, (int)(qr_smem_big > 0));
+            FZ_LAUNCH_SMEM((householder_qr_kernel<false, 1, false>), 1, small.size(), qr_smem_small, a, o0, o1, d_ws, d_aux, d_desc, sel_small, (int)(qr_smem_small > 0));
+            if (!big.empty()) {
+                err = launch_team_smem_nt(householder_qr_kernel<false, FZ_BIG_G, true>, FZ_BIG_G, (int)big.size(), qr_smem_big, QB_THREADS,
+                                          stream, a, o0, o1, d_ws, d_aux, d_desc, sel_big, (int)qr_panel_big | qr_prof);
+                if (err != cudaSuccess) { set_error("factorize launch failed: %s", cudaGetErrorString(err)); return CYB_ERR_CUDA; }
+            }
         }
     }
 #undef FZ_LAUNCH
