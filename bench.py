@@ -56,6 +56,7 @@ def parse():
     ap.add_argument("--svd-chi", type=int, default=None)
     ap.add_argument("--no-svd", action="store_true")
     ap.add_argument("--no-lanczos", action="store_true")
+    ap.add_argument("--no-sweep", action="store_true", help="skip the sweep-step leg (BASELINE config 5)")
     ap.add_argument("--no-plugin", action="store_true", help="skip the e2e_plugin leg (cyten API through the plugin)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel eagerly instead of replaying a CUDA graph")
@@ -155,6 +156,65 @@ def build_reference_heff(chi, plugin=None):
         permute_legs = staticmethod(lambda t, codomain=None, domain=None: ct.permute_legs(t, codomain, domain, bend_right=None))
         compose = staticmethod(ct.compose)
     return HEffective(T["LP"], T["RP"], T["W1"], T["W2"], Ops), T["theta"], ct
+
+
+class ReferenceOps:
+    """The ``SweepStep`` operation interface (cyten_b200.workloads.NativeOps) over the reference's own functions."""
+
+    def __init__(self, ct):
+        self.ct = ct
+
+    @staticmethod
+    def relabel(T, mapping):
+        T = T.copy(deep=False)
+        T.relabel({k: v for k, v in mapping.items() if k in T.labels})
+        return T
+
+    def permute_legs(self, T, codomain=None, domain=None):
+        return self.ct.permute_legs(T, codomain, domain, bend_right=None)
+
+    def compose(self, A, B, relabel1=None, relabel2=None):
+        return self.ct.compose(A, B, relabel1=relabel1, relabel2=relabel2)
+
+    def truncated_svd(self, theta, new_labels, chi_max, svd_min):
+        U, S, Vh, err, _ = self.ct.truncated_svd(theta, new_labels, chi_max=chi_max, svd_min=svd_min)
+        return U, S, Vh, err
+
+    def scale_axis(self, T, D, leg):
+        return self.ct.scale_axis(T, D, leg=leg)
+
+    def pinv(self, D, cutoff):
+        return self.ct.pinv(D, cutoff=cutoff)
+
+    def hc(self, T):
+        return T.hc
+
+    def norm(self, T):
+        x = self.ct.norm(T)
+        return float(x.to_numpy()) if hasattr(x, "to_numpy") else float(x)
+
+    def scale(self, T, a):
+        return a * T
+
+
+def build_reference_sweep_step(chi, plugin=None, nmv=1, chi_max=None, eps=1e-14, sync=None):
+    """``SweepStep`` (BASELINE config 5) on reference tensors -- numpy backend, or the plugin if given -- from the same
+    host blocks and Schmidt values as cyten_b200.workloads.build_sweep_step."""
+    from cyten_b200.workloads import SweepStep, heff_spaces, schmidt_values
+    H, theta, ct = build_reference_heff(chi, plugin=plugin)
+    o = ReferenceOps(ct)
+    LP = o.permute_legs(H.LP, ["vL"], ["vL*", "wL*"])
+    RP = o.permute_legs(H.RP, ["vR"], ["wR*", "vR*"])
+    W = o.permute_legs(o.relabel(H.W1, {"p0": "p", "p0*": "p*", "wC": "wR"}), ["wL", "p"], ["p*", "wR"])
+    leg = theta.codomain.factors[0]
+    vals = schmidt_values(heff_spaces(chi)["theta"][0][0])
+    be = theta.backend
+    S = ct.DiagonalTensor.from_diag_block(be.block_backend.as_block(np.ascontiguousarray(vals)), leg, backend=be, labels=["vL", "vR"])
+    if plugin is not None:
+        from cyten_plugin import to_plugin
+        S = to_plugin(ct.DiagonalTensor.from_diag_block(ct.get_backend("abelian", "numpy").block_backend.as_block(
+            np.ascontiguousarray(vals)), leg, backend=ct.get_backend("abelian", "numpy"), labels=["vL", "vR"]), plugin)
+    return SweepStep(o, LP, RP, W, S, chi_max or chi, eps, nmv, sync), theta, ct
 
 
 def cpu_matvec_time(chi, kind, repeats=1):
@@ -519,6 +579,14 @@ def run_b200(args):
         except Exception as e:   # noqa: BLE001 -- an extra, must never cost the bench line
             plugin_info = {"error": repr(e)}
 
+    # ---- BASELINE config 5: one bond update of a DMRG sweep (matvec + truncated_svd + scale_axis/pinv + update_LP/RP) ----
+    sweep_info = None
+    if world == 1 and not args.no_sweep and not args.no_svd:
+        try:
+            sweep_info = sweep_bench(chi, be)
+        except Exception as e:   # noqa: BLE001 -- an extra, must never cost the bench line
+            sweep_info = {"error": repr(e)}
+
     # ---- truncated SVD of the two-site theta at chi (BASELINE config 3) ----
     # theta[vL, p0 | p1, vR] with N(0,1) blocks (the synthetic input of SURVEY 8(d)); the rank-chi theta = tdot(A, B)
     # of two MPS tensors (half of every sector's singular values are numerically zero, the slow case for a Jacobi
@@ -619,10 +687,38 @@ def run_b200(args):
                         "mode": "3-stream pipeline (upload | matvec | download), two theta arenas; bytes are per rank",
                         "host_checksum": e2e_check},
                 "gpu_launches": launches, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
-                "e2e_plugin": plugin_info, "svd_ms": svd_ms, "svd": svd_info, "lanczos": lanczos_info}
+                "e2e_plugin": plugin_info, "sweep": sweep_info, "svd_ms": svd_ms, "svd": svd_info, "lanczos": lanczos_info}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def sweep_bench(chi, be, reps=3):
+    """One ``update_bond`` of the reference's toy DMRG (cyten_b200.workloads.SweepStep; d_dmrg.py:217-274) on the chi legs:
+    device time of the whole step (CUDA events, best of ``reps``) and the share of each part (wall clock with a
+    synchronisation after every part, second pass)."""
+    import torch
+    from cyten_b200.workloads import build_sweep_step
+    st, th = build_sweep_step(chi, be)
+    st.update_bond(th)                       # plans
+    best = float("inf")
+    for _ in range(reps):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        r = st.update_bond(th)
+        r["LP"].data.buf, r["RP"].data.buf   # materialise the final (deferred) permutations
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    st.sync = torch.cuda.synchronize
+    st.timings = {}
+    st.update_bond(th)
+    tot = sum(st.timings.values())
+    return {"chi": chi, "ms": best, "parts_ms": {k: v * 1e3 for k, v in st.timings.items()},
+            "share": {k: v / tot for k, v in st.timings.items()}, "kept": int(r["S"].data.shapes.sum()), "err": r["err"],
+            "what": "update_bond: 4 bends + 1 H_eff matvec + normalise, truncated_svd(chi_max=chi, svd_min=1e-14), "
+                    "scale_axis/pinv, update_LP, update_RP"}
 
 
 def e2e_plugin(args, chi, dev, flops, y_native):

@@ -185,7 +185,9 @@ class B200AbelianBackend(Blas1Mixin):
     def _new_buf(self, dtype: str, total: int) -> torch.Tensor:
         tdt = torch.complex128 if dtype == "complex128" else torch.float64
         if self.dry_run:
-            return torch.empty(ALIGN, dtype=tdt)
+            t = torch.empty(ALIGN, dtype=tdt)
+            t._cyb_dummy = True        # must never be cached as a tensor's arena (AbelianBackendData.buf)
+            return t
         return torch.empty(max(int(total), ALIGN), dtype=tdt, device=self.device)
 
     @staticmethod
@@ -894,6 +896,20 @@ class B200AbelianBackend(Blas1Mixin):
             if S_norm > 0:
                 self._call("cyb_axpby", ptr(dense), ptr(dense), n, _lib.CYB_F64, 1.0 / S_norm, 0.0, self._stream())
         return (*self._select(dense, leg, chi_max, chi_min, degeneracy_tol, trunc_cut, svd_min, minimize_error), S_norm)
+
+    def cutoff_inverse(self, d: AbelianBackendData, cutoff: float) -> AbelianBackendData:
+        """Pseudo-inverse of a real diagonal tensor: ``1/x`` where ``|x| >= cutoff``, else 0 (cyten.pinv of a
+        DiagonalTensor, ops_algebra.cpp:1514-1515 -> BlockBackend::cutoff_inverse, numpy.cpp:645-656).  One launch over
+        the whole arena (the padding between blocks is never read back)."""
+        if d.dtype != "float64":
+            raise _lib.CytenB200Error("cutoff_inverse: real diagonal tensors only")
+        res = AbelianBackendData(d.dtype, self.device, self._new_buf(d.dtype, d.buf.numel()), d.block_inds, d.offsets,
+                                 d.shapes, sig=d._sig)
+        if d.num_blocks and not self.dry_run:
+            n = int(d.offsets[-1] + d.sizes[-1])
+            with self._ctx():
+                self._call("cyb_cutoff_inverse", ptr(d.buf), ptr(res.buf), n, float(cutoff), self._stream())
+        return res
 
     def scale_inplace(self, data: AbelianBackendData, factor: float):
         self._call("cyb_axpby", ptr(data.buf), ptr(data.buf), data.buf.numel(), data.cyb_dtype, float(factor), 0.0,

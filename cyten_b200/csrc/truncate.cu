@@ -189,6 +189,14 @@ __global__ void sumsq_kernel(const double* __restrict__ x, int64_t ndoubles, dou
     }
 }
 
+__global__ void cutoff_inverse_kernel(const double* __restrict__ x, double* __restrict__ y, int64_t n, double cutoff)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const double v = x[i];
+        y[i] = fabs(v) < cutoff ? 0.0 : 1.0 / v;
+    }
+}
+
 __global__ void axpby_kernel(const double* __restrict__ x, double* __restrict__ y, int64_t nd, double alpha, double beta)
 {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nd; i += (int64_t)gridDim.x * blockDim.x)
@@ -274,6 +282,17 @@ int cyb_sumsq(const void* x, int64_t n, int dtype, double* out, cyb_stream_t str
     const int64_t cap = (int64_t)sm_count() * 8;
     if (grid > cap) grid = cap;
     sumsq_kernel<false><<<(unsigned)grid, 256, 0, stream>>>(static_cast<const double*>(x), nd, out);
+    CYB_LAUNCH_CHECK();
+    return CYB_OK;
+}
+
+int cyb_cutoff_inverse(const double* x, double* y, int64_t n, double cutoff, cyb_stream_t stream_)
+{
+    if (n == 0) return CYB_OK;
+    int64_t grid = (n + 255) / 256;
+    const int64_t cap = (int64_t)sm_count() * 8;
+    if (grid > cap) grid = cap;
+    cutoff_inverse_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream_>>>(x, y, n, cutoff);
     CYB_LAUNCH_CHECK();
     return CYB_OK;
 }

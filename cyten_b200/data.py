@@ -85,8 +85,10 @@ class AbelianBackendData:
     @property
     def buf(self) -> torch.Tensor:
         if self._buf is None:
-            pending, self._pending = self._pending, None
-            self._buf = pending[0]()
+            buf = self._pending[0]()
+            if getattr(buf, "_cyb_dummy", False):
+                return buf             # plan-only (dry-run) pass: nothing was computed, the permutation stays pending
+            self._buf, self._pending = buf, None
         return self._buf
 
     @buf.setter

@@ -499,3 +499,61 @@ def truncated_svd_sharded(T: SymmetricTensor, pg: ProcessGroup, new_labels=("a",
     if cd:
         Vh = ct.split_legs(Vh, [1])
     return U, S, Vh, err, renormalize, owner
+
+
+# ---- BASELINE config 5 on N GPUs -------------------------------------------------------------------------------------
+def all_gather_diagonal(S: DiagonalTensor, pg: ProcessGroup) -> DiagonalTensor:
+    """Replicates a DiagonalTensor whose blocks are disjointly distributed over the ranks: every sector of the leg gets a
+    block (zeros where no rank holds one), the local blocks are written at their places, one all_reduce."""
+    be, leg = S.backend, S.leg
+    ns = leg.num_sectors
+    bi = np.stack([np.arange(ns), np.arange(ns)], axis=1).astype(np.int64)
+    data = AbelianBackendData.empty("float64", be.device, bi, np.asarray(leg.multiplicities, np.int64).reshape(-1, 1), zero=True)
+    for n, row in enumerate(S.data.block_inds):
+        data.block(int(row[0])).copy_(S.data.block(n))
+    pg.all_reduce(data.buf)
+    return DiagonalTensor(data, leg, be, S.labels)
+
+
+class ShardedSweepOps:
+    """``SweepStep`` operations on N ranks: the truncated SVD runs sector-sharded (global cut from the all-gathered
+    singular values), its factors are replicated afterwards; everything else runs replicated on every rank."""
+
+    def __init__(self, pg: ProcessGroup):
+        from .workloads import NativeOps
+        self.pg = pg
+        self._n = NativeOps()
+
+    def __getattr__(self, name):
+        return getattr(self._n, name)
+
+    def truncated_svd(self, theta, new_labels, chi_max, svd_min):
+        a, b = new_labels
+        U, S, Vh, err, _, _ = truncated_svd_sharded(theta, self.pg, new_labels=(a, a, b, b), chi_max=chi_max, svd_min=svd_min)
+        return all_gather_blocks(U, self.pg), all_gather_diagonal(S, self.pg), all_gather_blocks(Vh, self.pg), err
+
+
+def shard_sweep_step(step, pg: ProcessGroup, split_columns=True, column_heavy=0.35, column_align=16):
+    """Turns a ``cyten_b200.workloads.SweepStep`` into its N-rank version: H_eff matvec sharded along ``vR`` (replicated
+    in / out, one all_reduce), sharded truncated SVD, replicated environment updates."""
+    if pg.world == 1:
+        return step
+    from types import SimpleNamespace
+    step.ops = ShardedSweepOps(pg)
+    plain_heff = step.heff
+    cache = {}
+
+    def heff():
+        if "SH" not in cache:
+            cache["SH"] = ShardedHEffective(plain_heff(), pg, split_columns=split_columns, column_heavy=column_heavy,
+                                           column_align=column_align)
+
+        def matvec(theta):
+            SH = cache["SH"]
+            if "ready" not in cache:
+                SH.shard(theta)              # work partition for this theta structure (plan-only passes, once)
+                cache["ready"] = True
+            return SH.matvec_replicated(theta)
+        return SimpleNamespace(matvec=matvec)
+    step.heff = heff
+    return step

@@ -19,7 +19,7 @@ from .spaces import AbelianLegPipe, ElementarySpace, TensorProduct
 
 __all__ = ["SymmetricTensor", "DiagonalTensor", "permute_legs", "combine_legs", "split_legs",
            "compose", "tdot", "svd", "truncated_svd", "qr", "eigh", "norm", "inner", "linear_combination",
-           "scalar_multiply", "dagger", "scale_axis", "outer", "partial_compose", "lq"]
+           "scalar_multiply", "dagger", "scale_axis", "outer", "partial_compose", "lq", "pinv"]
 
 
 class SymmetricTensor:
@@ -491,6 +491,11 @@ def scale_axis(T: SymmetricTensor, D: DiagonalTensor, leg) -> SymmetricTensor:
     if not (tl == D.leg or tl == D.leg.dual):     # block indices count the defining sectors: same for a leg and its dual
         raise ValueError("scale_axis: incompatible legs")
     return SymmetricTensor(T.backend.scale_axis(T.data, D.data, i), T.codomain, T.domain, T.backend, T.labels)
+
+
+def pinv(D: DiagonalTensor, cutoff: float = 1e-15) -> DiagonalTensor:
+    """Pseudo-inverse of a diagonal tensor (``cyten.pinv``, src/tensors/ops_algebra.cpp:1505-1520)."""
+    return DiagonalTensor(D.backend.cutoff_inverse(D.data, cutoff), D.leg, D.backend, D.labels)
 
 
 def _install_operators():

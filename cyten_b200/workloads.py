@@ -147,3 +147,171 @@ def build_heff(chi: int, backend, dtype="float64", Q=None, sigma=None):
         host[name] = (bi, blocks)
         T[name] = SymmetricTensor.from_numpy_blocks(blocks, bi, cod, dom, backend, labels=HEFF_LABELS[name], dtype=dtype)
     return HEffective(T["LP"], T["RP"], T["W1"], T["W2"], ops), T["theta"], host, sp
+
+
+# ---- BASELINE config 5: one bond update of a two-site DMRG sweep ---------------------------------------------------------
+class NativeOps:
+    """The operations ``SweepStep`` needs, on cyten_b200 tensors (the same interface is implemented over the reference's
+    ``cyten`` module by ``bench.py`` / the tests, so that ONE call sequence runs on both)."""
+
+    def __init__(self):
+        from . import tensors as t
+        self.t = t
+
+    @staticmethod
+    def relabel(T, mapping):
+        labels = [mapping.get(l, l) for l in T.labels]
+        if hasattr(T, "codomain"):
+            return SymmetricTensor(T.data, T.codomain, T.domain, T.backend, labels)
+        from .tensors import DiagonalTensor
+        return DiagonalTensor(T.data, T.leg, T.backend, labels)
+
+    def permute_legs(self, T, codomain=None, domain=None):
+        return self.t.permute_legs(T, codomain, domain)
+
+    def compose(self, A, B, relabel1=None, relabel2=None):
+        if relabel1:
+            A = self.relabel(A, relabel1)
+        if relabel2:
+            B = self.relabel(B, relabel2)
+        return self.t.compose(A, B)
+
+    def truncated_svd(self, theta, new_labels, chi_max, svd_min):
+        U, S, Vh, err, _ = self.t.truncated_svd(theta, new_labels=(new_labels[0], new_labels[0], new_labels[1], new_labels[1]),
+                                                chi_max=chi_max, svd_min=svd_min)
+        return U, S, Vh, err
+
+    def scale_axis(self, T, D, leg):
+        return self.t.scale_axis(T, D, leg)
+
+    def pinv(self, D, cutoff):
+        return self.t.pinv(D, cutoff)
+
+    def hc(self, T):
+        return self.t.dagger(T)
+
+    def norm(self, T):
+        return float(self.t.norm(T))
+
+    def scale(self, T, a):
+        return self.t.scalar_multiply(a, T)
+
+
+class SweepStep:
+    """``DMRGEngine.update_bond`` of the reference's toy code (toycodes/tenpy_toycodes/d_dmrg.py:217-274, with
+    ``split_truncate_theta``, toycodes/tenpy_toycodes/a_mps.py:217-250), call for call, on synthetic tensors:
+
+    1. bend the environments / MPO tensors into the effective Hamiltonian (4 permute_legs),
+    2. ``nmv`` applications of H_eff to theta (the reference runs Lanczos here; a fixed number of matvecs + a
+       normalisation is the same kernel work without the data-dependent iteration count),
+    3. ``truncated_svd(theta, chi_max, svd_min=eps)`` + the permutation of ``B``,
+    4. ``scale_axis`` with ``pinv`` of the Schmidt values (the new B matrices),
+    5. ``update_LP`` (2 scale_axis, hc, 4 permute_legs, 3 compose) and ``update_RP`` (hc, 5 permute_legs, 3 compose).
+
+    ``ops``: :class:`NativeOps` or the same interface over the reference.  ``timings``: optional dict that receives the
+    seconds per part when ``sync`` (a callable that waits for the device) is given."""
+
+    def __init__(self, ops, LP, RP, W, S_left, chi_max, eps=1e-14, nmv=1, sync=None):
+        self.ops, self.LP, self.RP, self.W, self.S_left = ops, LP, RP, W, S_left
+        self.chi_max, self.eps, self.nmv, self.sync = chi_max, eps, nmv, sync
+        self.timings = {}
+
+    def _mark(self, name, t0):
+        import time
+        if self.sync is not None:
+            self.sync()
+            self.timings[name] = self.timings.get(name, 0.0) + time.perf_counter() - t0
+        return time.perf_counter()
+
+    def heff(self):
+        o = self.ops
+        LP = o.permute_legs(self.LP, ["vL", "wL*"], ["vL*"])
+        RP = o.permute_legs(self.RP, ["vR*", "wR*"], ["vR"])
+        W1 = o.relabel(o.permute_legs(self.W, ["p", "wR"], ["wL", "p*"]), {"p": "p0", "p*": "p0*", "wR": "wC"})
+        W2 = o.relabel(o.permute_legs(self.W, ["p", "wR"], ["wL", "p*"]), {"p": "p1", "p*": "p1*", "wL": "wC"})
+        return HEffective(LP, RP, W1, W2, o)
+
+    def update_bond(self, theta0):
+        import time
+        o = self.ops
+        t0 = time.perf_counter()
+        H = self.heff()
+        theta = theta0
+        for _ in range(self.nmv):
+            theta = H.matvec(theta)
+        theta = o.scale(theta, 1.0 / o.norm(theta))
+        t0 = self._mark("matvec", t0)
+        A, S, B, err = o.truncated_svd(theta, ["vR", "vL"], self.chi_max, self.eps)
+        B = o.permute_legs(B, codomain=["vL", "p1"])
+        A, B = o.relabel(A, {"p0": "p"}), o.relabel(B, {"p1": "p"})
+        t0 = self._mark("truncated_svd", t0)
+        G = o.scale_axis(A, o.pinv(self.S_left, self.eps), "vL")
+        Bi = o.scale_axis(G, S, "vR")
+        t0 = self._mark("scale_axis", t0)
+        LP_new = self.update_LP(Bi, S)
+        t0 = self._mark("update_LP", t0)
+        RP_new = self.update_RP(B)
+        self._mark("update_RP", t0)
+        return dict(Bi=Bi, Bj=B, S=S, err=err, LP=LP_new, RP=RP_new, theta=theta)
+
+    def update_LP(self, B, S_right):
+        o = self.ops
+        G = o.scale_axis(B, o.pinv(S_right, self.eps), "vR")
+        A = o.scale_axis(G, self.S_left, "vL")
+        Ac = o.permute_legs(o.hc(A), codomain=["vR*", "p*"])
+        LP = o.compose(Ac, self.LP)                                              # vR* p* wL* vL*
+        LP = o.permute_legs(LP, ["vL*", "vR*"], ["wL*", "p*"])
+        LP = o.compose(LP, self.W)                                               # vL* vR* wR p*
+        LP = o.permute_legs(LP, ["vR*", "wR"], ["vL*", "p*"])
+        LP = o.compose(LP, A, relabel1={"vR*": "vL", "wR": "wL*"}, relabel2={"vR": "vL*"})
+        return o.permute_legs(LP, domain=["vL*", "wL*"])
+
+    def update_RP(self, B):
+        o = self.ops
+        Bc = o.permute_legs(o.hc(B), ["p*", "vL*"], ["vR*"])
+        RP = o.compose(Bc, self.RP)                                              # p* vL* vR* wR*
+        RP = o.permute_legs(RP, ["vL*", "vR*"], ["p*", "wR*"])
+        W_ = o.permute_legs(self.W, ["p", "wR"], ["wL", "p*"])
+        RP = o.compose(RP, W_)                                                   # vL* vR* p* wL
+        RP = o.permute_legs(RP, ["wL", "vL*"], ["p*", "vR*"])
+        B_ = o.permute_legs(B, ["p", "vR"], ["vL"])
+        RP = o.compose(RP, B_, relabel1={"vL*": "vR", "wL": "wR*"}, relabel2={"vL": "vR*"})
+        return o.permute_legs(RP, ["vR"], ["wR*", "vR*"])
+
+
+def build_sweep_step(chi: int, backend, nmv=1, chi_max=None, eps=1e-14, Q=None, sigma=None, sync=None):
+    """(SweepStep, theta0) on ``backend``: the H_eff tensors of :func:`build_heff` un-bent into the toy code's storage
+    form (``LP[vL | vL*, wL*]``, ``RP[vR | wR*, vR*]``, ``W[wL, p | p*, wR]``), positive Schmidt values on the left bond."""
+    from . import tensors as ops
+    from .tensors import DiagonalTensor
+    H, theta, host, sp = build_heff(chi, backend, Q=Q, sigma=sigma)
+    o = NativeOps()
+    LP = ops.permute_legs(H.LP, ["vL"], ["vL*", "wL*"])
+    RP = ops.permute_legs(H.RP, ["vR"], ["wR*", "vR*"])
+    W = ops.permute_legs(o.relabel(H.W1, {"p0": "p", "p0*": "p*", "wC": "wR"}), ["wL", "p"], ["p*", "wR"])
+    v = sp["theta"][0][0]
+    S_left = diagonal_from_numpy(schmidt_values(v), v, backend, ["vL", "vR"])
+    return SweepStep(o, LP, RP, W, S_left, chi_max or chi, eps, nmv, sync), theta
+
+
+def schmidt_values(leg, seed=6) -> np.ndarray:
+    """Positive, normalised synthetic Schmidt values over the basis of ``leg`` (internal order)."""
+    rng = np.random.default_rng(seed)
+    s = np.abs(rng.standard_normal(int(leg.dim))) + 0.05
+    return s / np.linalg.norm(s)
+
+
+def diagonal_from_numpy(values: np.ndarray, leg, backend, labels=None):
+    """DiagonalTensor over ``leg`` from the dense diagonal (internal basis order), one block per sector."""
+    import torch
+    from .data import AbelianBackendData
+    from .tensors import DiagonalTensor
+    ns = leg.num_sectors
+    bi = np.stack([np.arange(ns), np.arange(ns)], axis=1).astype(np.int64)
+    data = AbelianBackendData.empty("float64", backend.device, bi, np.asarray(leg.multiplicities, np.int64).reshape(-1, 1))
+    host = np.zeros(data.buf.numel())
+    for i, off in enumerate(data.offsets):
+        b0, b1 = leg.slices[i]
+        host[off:off + (b1 - b0)] = values[b0:b1]
+    data.buf.copy_(torch.from_numpy(host))
+    return DiagonalTensor(data, leg, backend, labels or [None, None])

@@ -211,6 +211,10 @@ int cyb_sumsq(const void* x, int64_t n, int dtype, double* out, cyb_stream_t str
 /* y = alpha * x (+ beta * y) elementwise on arenas of n elements (real alpha/beta). */
 int cyb_axpby(const void* x, void* y, int64_t n, int dtype, double alpha, double beta,
               cyb_stream_t stream);
+/* y = 1 / x where |x| >= cutoff, else 0, on n real elements: the pseudo-inverse of the Schmidt values of a sweep
+ * (BlockBackend::cutoff_inverse, src/block_backend/numpy.cpp:645-656, behind cyten.pinv(DiagonalTensor),
+ * src/tensors/ops_algebra.cpp:1514-1515; toycodes/tenpy_toycodes/d_dmrg.py:228, 257). */
+int cyb_cutoff_inverse(const double* x, double* y, int64_t n, double cutoff, cyb_stream_t stream);
 /* scales row r of matrix i (m_i x n_i) by d[d_off[i] + r] (axis=0) or column (axis=1);
  * scale_axis / U*S products (abelian.cpp:3177-3232). `inv` != 0 divides. */
 int cyb_scale_rows_cols(void* x, const int64_t* dims, const int64_t* off, const double* d,

@@ -455,6 +455,15 @@ def cyb_axpby(x, y, n, dtype, alpha, beta, stream=None):
     return 0
 
 
+def cyb_cutoff_inverse(x, y, n, cutoff, stream=None):
+    """1 / np.where(np.abs(a) < cutoff, np.inf, a)  (NumpyBlockBackend::cutoff_inverse, numpy.cpp:645-656)."""
+    xv = _arr(x, n, np.float64).copy()
+    yv = _arr(y, n, np.float64)
+    with np.errstate(divide="ignore"):
+        yv[:] = 1.0 / np.where(np.abs(xv) < cutoff, np.inf, xv)
+    return 0
+
+
 def cyb_scale_rows_cols(x, dims, off, d, d_off, nmat, axis, dtype, stream=None):
     dt = _dt(dtype)
     isz = np.dtype(dt).itemsize

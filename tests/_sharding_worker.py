@@ -127,6 +127,20 @@ def worker(rank, world, port, out_dir, mode="gloo", chi=64):
             Ur, Vr = sh.all_gather_blocks(U, pg), sh.all_gather_blocks(Vh, pg)
             assert np.array_equal(_dense_of(Ur), _dense_of(sh.expand_to_full(U1)))
             assert np.array_equal(_dense_of(Vr), _dense_of(sh.expand_to_full(V1)))
+        # ---- BASELINE config 5: one bond update of a sweep on N ranks == single process ----
+        from cyten_b200.workloads import build_sweep_step
+        schi = 64 if chi <= 64 else chi
+        sQ, ssig = CONFIG_LEGS.get(schi, (3, 1.2))
+        st1, th_s = build_sweep_step(schi, be, chi_max=(3 * schi) // 4, Q=sQ, sigma=ssig)
+        r1 = st1.update_bond(th_s)
+        stN, _ = build_sweep_step(schi, be, chi_max=(3 * schi) // 4, Q=sQ, sigma=ssig)
+        stN = sh.shard_sweep_step(stN, pg, column_heavy=0.25, column_align=2 if chi <= 64 else 16)
+        rN = stN.update_bond(th_s)
+        assert abs(rN["err"] - r1["err"]) <= 1e-13
+        assert rN["S"].leg == r1["S"].leg
+        for name in ("LP", "RP", "Bi", "Bj"):
+            a, b = _dense_of(sh.expand_to_full(rN[name])), _dense_of(sh.expand_to_full(r1[name]))
+            assert np.allclose(a, b, rtol=0, atol=1e-9 * np.abs(b).max()), name
         res["ok"] = True
         np.save(os.path.join(out_dir, f"rank{rank}.npy"), np.asarray([1.0]))
     finally:

@@ -600,3 +600,16 @@ def test_scale_axis(lib, dtype, ddtype):
     for t, s in enumerate(shapes):
         ref = x[ox[t]:ox[t] + sizes[t]].reshape(s) * d[od[t]:od[t] + s[1]][None, :, None]
         assert np.allclose(got[oo[t]:oo[t] + sizes[t]].reshape(s), ref, rtol=0, atol=1e-15 * max(1.0, np.abs(ref).max()))
+
+
+def test_cutoff_inverse(lib):
+    """cyb_cutoff_inverse == 1 / np.where(|x| < cutoff, inf, x) (numpy.cpp:645-656), bit for bit."""
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal(1000)
+    x[::7] = 1e-16
+    x[3] = 0.0
+    y = lib.up(np.zeros_like(x))
+    lib.call("cyb_cutoff_inverse", lib.p(lib.up(x)), lib.p(y), len(x), 1e-12, lib.stream())
+    with np.errstate(divide="ignore"):
+        want = 1.0 / np.where(np.abs(x) < 1e-12, np.inf, x)
+    assert np.array_equal(y.cpu().numpy(), want)
