@@ -853,74 +853,145 @@ static int run_block_jacobi(const void* a, void* o0, double* s_out, void* o2, vo
     std::vector<int> rowbase((size_t)nbig + 1, 0);
     for (int q = 0; q < nbig; ++q) rowbase[(size_t)q + 1] = rowbase[(size_t)q] + (int)descs[(size_t)big[(size_t)q]].r;
     const size_t nrows = (size_t)rowbase[(size_t)nbig];
-    BjRounds R1, R2;
-    bj_build_rounds(R1, descs, big, rowbase, std::vector<int>((size_t)nbig, 0), CM);
-    // device scratch: items | Gram works | apply works (pass-2 lists are never longer than pass-1 ones) |
-    //                 active | flags | nnoise | rowbase | rowmap | norm2 | floor2 | skip | Gpart | Q
-    const size_t items_bytes = align_up(sizeof(BjItem) * std::max<size_t>(R1.flat.size(), 1), 256);
-    const size_t gw_bytes = align_up(sizeof(BjWork) * std::max<size_t>(R1.gworks.size(), 1), 256);
-    const size_t aw_bytes = align_up(sizeof(BjWork) * std::max<size_t>(R1.aworks.size(), 1), 256);
-    const size_t skip_bytes = align_up(sizeof(int) * std::max<size_t>(R1.max_items, 1), 256);
-    const size_t gpart_bytes = align_up(sizeof(double) * BJ_R * BJ_R * CM * std::max<size_t>(R1.max_gworks, 1), 256);
-    const size_t q_bytes = align_up(sizeof(double) * BJ_R * BJ_R * CM * std::max<size_t>(R1.max_items, 1), 256);
+    // Up to four groups of sectors (LPT on the sweep cost r^2 (2c + r)) run their rounds on separate streams: the rotation
+    // kernel of a round is latency-bound (one CTA per block pair, tensor pipe idle), so while one group rotates, the Gram /
+    // apply kernels of the others keep the tensor pipe busy.  Sectors are independent; only the rounds of ONE sector
+    // depend on each other.  chi = 4096 truncated SVD: 71.5 / 66.9 / 65.4 / 64.9 ms with 1 / 2 / 3 / 4 groups
+    // (profiles/r2); CYB_BJ_GROUPS overrides.
+    constexpr int MAXG = 4;
+    int NG = 4;
+    if (const char* e = getenv("CYB_BJ_GROUPS")) NG = atoi(e);
+    NG = std::max(1, std::min(std::min(NG, MAXG), nbig));
+    std::vector<int> group_of((size_t)nbig, 0);
+    if (NG >= 2) {
+        std::vector<int> idx((size_t)nbig);
+        for (int q = 0; q < nbig; ++q) idx[(size_t)q] = q;
+        auto cost = [&](int q) { const FzDesc& D = descs[(size_t)big[(size_t)q]]; return (double)D.r * (double)D.r * (2.0 * (double)D.c + (double)D.r); };
+        std::stable_sort(idx.begin(), idx.end(), [&](int x, int y) { return cost(x) > cost(y); });
+        double load[MAXG] = {0.0, 0.0, 0.0, 0.0};
+        for (int q : idx) {
+            int g = 0;
+            for (int h = 1; h < NG; ++h) if (load[h] < load[g]) g = h;
+            group_of[(size_t)q] = g; load[g] += cost(q);
+        }
+    }
+    std::vector<int64_t> gmats[MAXG];
+    std::vector<int> growbase[MAXG];
+    for (int q = 0; q < nbig; ++q) {
+        const int g = group_of[(size_t)q];
+        gmats[g].push_back(big[(size_t)q]);
+        growbase[g].push_back(rowbase[(size_t)q]);
+    }
+    BjRounds R1[MAXG], R2[MAXG];
+    size_t max_flat = 1, max_gw = 1, max_aw = 1, max_items = 1, max_gworks = 1;
+    for (int g = 0; g < NG; ++g) {
+        bj_build_rounds(R1[g], descs, gmats[g], growbase[g], std::vector<int>(gmats[g].size(), 0), CM);
+        max_flat = std::max(max_flat, R1[g].flat.size()); max_gw = std::max(max_gw, R1[g].gworks.size());
+        max_aw = std::max(max_aw, R1[g].aworks.size()); max_items = std::max(max_items, R1[g].max_items);
+        max_gworks = std::max(max_gworks, R1[g].max_gworks);
+    }
+    // device scratch, per group: items | Gram works | apply works (pass-2 lists are never longer than pass-1 ones) | skip |
+    //                 Gpart | Q;   shared: active | flags | nnoise | rowbase | rowmap | norm2 | floor2
+    const size_t items_bytes = align_up(sizeof(BjItem) * max_flat, 256);
+    const size_t gw_bytes = align_up(sizeof(BjWork) * max_gw, 256);
+    const size_t aw_bytes = align_up(sizeof(BjWork) * max_aw, 256);
+    const size_t skip_bytes = align_up(sizeof(int) * max_items, 256);
+    const size_t gpart_bytes = align_up(sizeof(double) * BJ_R * BJ_R * CM * max_gworks, 256);
+    const size_t q_bytes = align_up(sizeof(double) * BJ_R * BJ_R * CM * max_items, 256);
+    const size_t group_bytes = items_bytes + gw_bytes + aw_bytes + skip_bytes + gpart_bytes + q_bytes;
     const size_t ints_bytes = align_up(sizeof(int) * nmat, 256);
     const size_t rb_bytes = align_up(sizeof(int) * ((size_t)nbig + 1), 256);
     const size_t map_bytes = align_up(sizeof(int) * std::max<size_t>(nrows, 1), 256);
     const size_t nrm_bytes = align_up(sizeof(double) * std::max<size_t>(nrows, 1), 256);
     const size_t fl_bytes = align_up(sizeof(double) * nmat, 256);
-    Scratch scr(items_bytes + gw_bytes + aw_bytes + 3 * ints_bytes + rb_bytes + map_bytes + nrm_bytes + fl_bytes +
-                skip_bytes + gpart_bytes + q_bytes, stream);
+    Scratch scr(NG * group_bytes + 3 * ints_bytes + rb_bytes + map_bytes + nrm_bytes + fl_bytes, stream);
     if (!scr.ptr) return CYB_ERR_CUDA;
     size_t o = 0;
-    BjItem* d_items = scr.as<BjItem>(o); o += items_bytes;
-    BjWork* d_gworks = scr.as<BjWork>(o); o += gw_bytes;
-    BjWork* d_aworks = scr.as<BjWork>(o); o += aw_bytes;
+    BjItem* d_items[MAXG]; BjWork* d_gworks[MAXG]; BjWork* d_aworks[MAXG]; int* d_skip[MAXG]; double* d_gpart[MAXG]; double* d_qbuf[MAXG];
+    for (int g = 0; g < NG; ++g) {
+        d_items[g] = scr.as<BjItem>(o); o += items_bytes;
+        d_gworks[g] = scr.as<BjWork>(o); o += gw_bytes;
+        d_aworks[g] = scr.as<BjWork>(o); o += aw_bytes;
+        d_skip[g] = scr.as<int>(o); o += skip_bytes;
+        d_gpart[g] = scr.as<double>(o); o += gpart_bytes;
+        d_qbuf[g] = scr.as<double>(o); o += q_bytes;
+    }
     int* d_active = scr.as<int>(o); o += ints_bytes;
     int* d_flags = scr.as<int>(o); o += ints_bytes;
     int* d_nnoise = scr.as<int>(o); o += ints_bytes;
     int* d_rowbase = scr.as<int>(o); o += rb_bytes;
     int* d_rowmap = scr.as<int>(o); o += map_bytes;
     double* d_norm2 = scr.as<double>(o); o += nrm_bytes;
-    double* d_floor2 = scr.as<double>(o); o += fl_bytes;
-    int* d_skip = scr.as<int>(o); o += skip_bytes;
-    double* d_gpart = scr.as<double>(o); o += gpart_bytes;
-    double* d_qbuf = scr.as<double>(o);
+    double* d_floor2 = scr.as<double>(o);
     std::vector<int> active(nmat, 0), flags(nmat, 0), nnoise(nmat, 0);
     std::vector<int64_t> sweeps(nmat, 0);
     for (int64_t mat : big) active[(size_t)mat] = 1;
     CYB_CHECK_CUDA(cudaMemcpyAsync(d_rowbase, rowbase.data(), sizeof(int) * rowbase.size(), cudaMemcpyHostToDevice, stream));
     CYB_CHECK_CUDA(cudaMemsetAsync(d_floor2, 0, sizeof(double) * nmat, stream));
+    // the second stream and its fork / join events (per device, created once)
+    static cudaStream_t side_stream[64][MAXG] = {};
+    static cudaEvent_t ev_fork[64] = {}, ev_join[64][MAXG] = {};
+    int devid = 0;
+    CYB_CHECK_CUDA(cudaGetDevice(&devid));
+    devid &= 63;
+    if (NG >= 2 && !ev_fork[devid]) {
+        CYB_CHECK_CUDA(cudaEventCreateWithFlags(&ev_fork[devid], cudaEventDisableTiming));
+        for (int g = 1; g < MAXG; ++g) {
+            CYB_CHECK_CUDA(cudaStreamCreateWithFlags(&side_stream[devid][g], cudaStreamNonBlocking));
+            CYB_CHECK_CUDA(cudaEventCreateWithFlags(&ev_join[devid][g], cudaEventDisableTiming));
+        }
+    }
+    cudaStream_t gstream[MAXG] = {stream, stream, stream, stream};
+    for (int g = 1; g < NG; ++g) gstream[g] = side_stream[devid][g];
     const int norm_grid = sm_count() * 4;
     auto sort_rows = [&](int init) {
         bj_norms_kernel<<<norm_grid, 256, 0, stream>>>(static_cast<const double*>(d_ws), d_desc, sel_big, d_rowbase, nbig, d_norm2, CM);
         bj_sort_kernel<<<nbig, 1024, 0, stream>>>(d_desc, sel_big, d_rowbase, d_norm2, d_rowmap, d_floor2, d_nnoise, d_active, init);
     };
-    // runs sweeps over the item lists of R until no item rotates; returns false on a CUDA error
-    auto run_sweeps = [&](const BjRounds& R, bool phase1) -> int {
-        if (R.flat.empty()) return CYB_OK;
-        CYB_CHECK_CUDA(cudaMemcpyAsync(d_items, R.flat.data(), sizeof(BjItem) * R.flat.size(), cudaMemcpyHostToDevice, stream));
-        CYB_CHECK_CUDA(cudaMemcpyAsync(d_gworks, R.gworks.data(), sizeof(BjWork) * R.gworks.size(), cudaMemcpyHostToDevice, stream));
-        CYB_CHECK_CUDA(cudaMemcpyAsync(d_aworks, R.aworks.data(), sizeof(BjWork) * R.aworks.size(), cudaMemcpyHostToDevice, stream));
+    // runs sweeps over the item lists of R[0..NG) until no item rotates
+    auto run_sweeps = [&](const BjRounds* R, bool phase1) -> int {
+        bool have = false;
+        size_t nrounds = 0;
+        for (int g = 0; g < NG; ++g) {
+            if (R[g].flat.empty()) continue;
+            have = true;
+            nrounds = std::max(nrounds, R[g].rounds.size());
+            CYB_CHECK_CUDA(cudaMemcpyAsync(d_items[g], R[g].flat.data(), sizeof(BjItem) * R[g].flat.size(), cudaMemcpyHostToDevice, stream));
+            CYB_CHECK_CUDA(cudaMemcpyAsync(d_gworks[g], R[g].gworks.data(), sizeof(BjWork) * R[g].gworks.size(), cudaMemcpyHostToDevice, stream));
+            CYB_CHECK_CUDA(cudaMemcpyAsync(d_aworks[g], R[g].aworks.data(), sizeof(BjWork) * R[g].aworks.size(), cudaMemcpyHostToDevice, stream));
+        }
+        if (!have) return CYB_OK;
         bool any = false;
         for (size_t m = 0; m < nmat; ++m) any = any || active[m];
         for (int sweep = 0; sweep < FZ_MAX_SWEEPS && any; ++sweep) {
             CYB_CHECK_CUDA(cudaMemcpyAsync(d_active, active.data(), sizeof(int) * nmat, cudaMemcpyHostToDevice, stream));
             CYB_CHECK_CUDA(cudaMemsetAsync(d_flags, 0, sizeof(int) * nmat, stream));
             if (phase1) sort_rows(sweep == 0);
-            for (size_t rd = 0; rd < R.rounds.size(); ++rd) {
-                bool live = false;   // skip rounds whose items all belong to converged matrices
-                for (const BjItem& it : R.rounds[rd]) if (active[(size_t)it.mat]) { live = true; break; }
-                if (!live) continue;
-                const unsigned ni = (unsigned)R.rounds[rd].size();
-                const unsigned ng = (unsigned)(R.gstart[rd + 1] - R.gstart[rd]), na = (unsigned)(R.astart[rd + 1] - R.astart[rd]);
-                bj_gram_kernel<CX><<<ng, BJ_THREADS, BJ_SMEM_GRAM, stream>>>(
-                    static_cast<const double*>(d_ws), d_desc, d_items + R.start[rd], d_gworks + R.gstart[rd], d_active, d_rowmap, d_gpart);
-                bj_rotate_kernel<CX><<<ni, BJ_RT, SMEM_ROT, stream>>>(
-                    d_desc, d_items + R.start[rd], d_active, d_flags, d_floor2, phase1 ? 1 : 0, d_gpart, d_qbuf, d_skip);
-                bj_apply_kernel<CX><<<na, BJ_THREADS, SMEM_APPLY, stream>>>(
-                    static_cast<double*>(d_ws), d_desc, d_items + R.start[rd], d_aworks + R.astart[rd], d_rowmap, d_qbuf, d_skip);
+            if (NG >= 2) {
+                CYB_CHECK_CUDA(cudaEventRecord(ev_fork[devid], stream));
+                for (int g = 1; g < NG; ++g) CYB_CHECK_CUDA(cudaStreamWaitEvent(gstream[g], ev_fork[devid], 0));
+            }
+            for (size_t rd = 0; rd < nrounds; ++rd) {
+                for (int g = 0; g < NG; ++g) {
+                    if (rd >= R[g].rounds.size()) continue;
+                    bool live = false;   // skip rounds whose items all belong to converged matrices
+                    for (const BjItem& it : R[g].rounds[rd]) if (active[(size_t)it.mat]) { live = true; break; }
+                    if (!live) continue;
+                    const unsigned ni = (unsigned)R[g].rounds[rd].size();
+                    const unsigned ng = (unsigned)(R[g].gstart[rd + 1] - R[g].gstart[rd]), na = (unsigned)(R[g].astart[rd + 1] - R[g].astart[rd]);
+                    bj_gram_kernel<CX><<<ng, BJ_THREADS, BJ_SMEM_GRAM, gstream[g]>>>(
+                        static_cast<const double*>(d_ws), d_desc, d_items[g] + R[g].start[rd], d_gworks[g] + R[g].gstart[rd], d_active, d_rowmap, d_gpart[g]);
+                    bj_rotate_kernel<CX><<<ni, BJ_RT, SMEM_ROT, gstream[g]>>>(
+                        d_desc, d_items[g] + R[g].start[rd], d_active, d_flags, d_floor2, phase1 ? 1 : 0, d_gpart[g], d_qbuf[g], d_skip[g]);
+                    bj_apply_kernel<CX><<<na, BJ_THREADS, SMEM_APPLY, gstream[g]>>>(
+                        static_cast<double*>(d_ws), d_desc, d_items[g] + R[g].start[rd], d_aworks[g] + R[g].astart[rd], d_rowmap, d_qbuf[g], d_skip[g]);
+                }
             }
             CYB_LAUNCH_CHECK();
+            for (int g = 1; g < NG; ++g) {
+                CYB_CHECK_CUDA(cudaEventRecord(ev_join[devid][g], gstream[g]));
+                CYB_CHECK_CUDA(cudaStreamWaitEvent(stream, ev_join[devid][g], 0));
+            }
             CYB_CHECK_CUDA(cudaMemcpyAsync(flags.data(), d_flags, sizeof(int) * nmat, cudaMemcpyDeviceToHost, stream));
             CYB_CHECK_CUDA(cudaStreamSynchronize(stream));
             any = false;
@@ -946,15 +1017,17 @@ static int run_block_jacobi(const void* a, void* o0, double* s_out, void* o2, vo
         CYB_LAUNCH_CHECK();
         CYB_CHECK_CUDA(cudaMemcpyAsync(nnoise.data(), d_nnoise, sizeof(int) * nmat, cudaMemcpyDeviceToHost, stream));
         CYB_CHECK_CUDA(cudaStreamSynchronize(stream));
-        std::vector<int> first_block((size_t)nbig, 0);
-        for (int q = 0; q < nbig; ++q) {
-            const int64_t mat = big[(size_t)q];
-            const int64_t r = descs[(size_t)mat].r;
-            const int nn = nnoise[(size_t)mat];
-            active[(size_t)mat] = nn > 1;
-            first_block[(size_t)q] = nn > 1 ? (int)((r - nn) / BJ_B) : (int)((r + BJ_B - 1) / BJ_B);
+        for (int g = 0; g < NG; ++g) {
+            std::vector<int> first_block(gmats[g].size(), 0);
+            for (size_t q = 0; q < gmats[g].size(); ++q) {
+                const int64_t mat = gmats[g][q];
+                const int64_t r = descs[(size_t)mat].r;
+                const int nn = nnoise[(size_t)mat];
+                active[(size_t)mat] = nn > 1;
+                first_block[q] = nn > 1 ? (int)((r - nn) / BJ_B) : (int)((r + BJ_B - 1) / BJ_B);
+            }
+            bj_build_rounds(R2[g], descs, gmats[g], growbase[g], first_block, CM);
         }
-        bj_build_rounds(R2, descs, big, rowbase, first_block, CM);
         rc = run_sweeps(R2, false);
         if (rc != CYB_OK) return rc;
     }
