@@ -56,6 +56,9 @@ def parse():
     ap.add_argument("--svd-chi", type=int, default=None)
     ap.add_argument("--no-svd", action="store_true")
     ap.add_argument("--no-lanczos", action="store_true")
+    ap.add_argument("--unfused", action="store_true",
+                    help="time the call-for-call mirror of HEffective.matvec (5 permute_legs + 4 compose) instead of the fused "
+                         "GEMM / one streaming pass / GEMM operator")
     ap.add_argument("--no-sweep", action="store_true", help="skip the sweep-step leg (BASELINE config 5)")
     ap.add_argument("--no-plugin", action="store_true", help="skip the e2e_plugin leg (cyten API through the plugin)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -399,9 +402,18 @@ def run_b200(args):
     be = B200AbelianBackend(dev)
     pg = sh.attach_process_group(be, dist.group.WORLD if world > 1 else None)
     chi = args.chi
-    H, theta_full, host, sp = build_heff(chi, be)
-    SH = sh.ShardedHEffective(H, pg, split_columns=os.environ.get("CYB_SPLIT_COLUMNS", "1") == "1",
-                              column_heavy=float(os.environ.get("CYB_COL_HEAVY", "0.35")))
+    H_unfused, theta_full, host, sp = build_heff(chi, be)
+    # the product path: GEMM, one fused streaming pass for the two MPO applications, GEMM (cyten_b200/fused.py); --unfused
+    # times the call-for-call mirror of the reference's 5 permute_legs + 4 compose instead.  `flops` is always the
+    # algorithmic GEMM work of the reference's four composes (same number for both, and for the reference arm).
+    fused = not args.unfused
+    if fused:
+        from cyten_b200.fused import FusedHEffective
+        H = FusedHEffective(H_unfused)
+    else:
+        H = H_unfused
+    SH = sh.ShardedHEffective(H_unfused, pg, split_columns=os.environ.get("CYB_SPLIT_COLUMNS", "1") == "1",
+                              column_heavy=float(os.environ.get("CYB_COL_HEAVY", "0.35")), fused=fused)
     # multi-GPU: theta lives sharded along the sectors of vR (LPT by block volume); the matvec chain is
     # rank-local until vR is contracted, then one all_reduce of the (small) result arena
     theta = SH.shard(theta_full) if world > 1 else theta_full
@@ -437,11 +449,15 @@ def run_b200(args):
     # cold pass (plans are built on device here) -- timed separately, reported as ms_first_call
     barrier()
     t0 = time.perf_counter()
-    be.plan_mkn = []
     y = step()
     torch.cuda.synchronize()
     first_call_ms = (time.perf_counter() - t0) * 1e3
-    flops = total_over_ranks(2.0 * float(sum(be.plan_mkn)))     # algorithmic flops of the whole job
+    # algorithmic flops of the whole job = GEMM work of the reference's call sequence (4 composes) on this structure,
+    # counted by the planner during one unsharded, unfused matvec on this GPU
+    be.plan_mkn = []
+    H_unfused.matvec(theta_full).data.buf
+    flops = 2.0 * float(sum(be.plan_mkn))
+    be.plan_mkn = None
     for _ in range(max(args.warmup, 3)):
         y = step()
     be.plan_mkn = None
@@ -675,6 +691,8 @@ def run_b200(args):
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic",
                 "config": {"workload": f"U(1) DMRG two-site H_eff matvec (4 tdot + 5 permute_legs), chi={chi}, D=5, d=2, float64",
+                           "implementation": ("fused: GEMM, one cyb_middle_apply pass for both MPO applications, GEMM (cyten_b200/fused.py)"
+                                              if fused else "unfused: 5 permute_legs + 4 compose, call for call"),
                            "l2": "192 MiB buffer written between timed steps", "flops_per_step": flops,
                            "cuda_graph": {"enabled": use_graph, "ms_per_step_eager": eager_ms_per_step,
                                           "launches_per_replay": (captured[id(theta)].launches_per_replay if use_graph else None)},

@@ -49,6 +49,9 @@ SIGNATURES = {
     "cyb_sumsq": (_int, [_vp, _i64, _int, _vp, _vp]),
     "cyb_axpby": (_int, [_vp, _vp, _i64, _int, _dbl, _dbl, _vp]),
     "cyb_cutoff_inverse": (_int, [_vp, _vp, _i64, _dbl, _vp]),
+    "cyb_middle_apply_max_rows": (_i64, []),
+    "cyb_middle_apply_unit_cols": (_i64, []),
+    "cyb_middle_apply": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _int, _vp]),
     "cyb_scale_rows_cols": (_int, [_vp, _vp, _vp, _vp, _vp, _i64, _int, _int, _vp]),
     "cyb_gather_rows_cols": (_int, [_vp, _vp, _vp, _vp, _i64, _int, _int, _vp]),
     "cyb_blas1_workspace_bytes": (_i64, []),

@@ -178,7 +178,8 @@ class B200AbelianBackend(Blas1Mixin):
         return plan
 
     def _plan_put(self, key, plan):
-        if self.plan_cache:
+        # plan-only (dry-run) passes build tables without device schedules / workspaces: never cache those
+        if self.plan_cache and not self.dry_run:
             self._plans[key] = plan
         return plan
 

@@ -15,7 +15,7 @@ HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
 OBJ = CSRC / "_obj"
 LIB = HERE / "libcyten_b200.so"
-SOURCES = ["core", "bookkeeping", "copy_blocks", "grouped_gemm", "factorize", "truncate", "blas1"]
+SOURCES = ["core", "bookkeeping", "copy_blocks", "grouped_gemm", "factorize", "truncate", "blas1", "middle_apply"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default"]

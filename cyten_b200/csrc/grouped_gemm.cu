@@ -180,9 +180,12 @@ __global__ void __launch_bounds__(1024) gemm_schedule_kernel(const int64_t* __re
 // IL: a warp's 8x8 groups are interleaved over the tile (group = w + i * WARPS) instead of contiguous;
 // WMFAST: wm = warp % WARPS_M (else warp / WARPS_N);  SKIP: groups beyond the block edge issue no DMMA
 template <bool CPLX, int BM_, int BN_, int BK_, int WARPS_M_, int WARPS_N_, int STAGES_, bool IL_ = true,
-          bool WMFAST_ = true, bool SKIP_ = true, int MINB_ = 1>
+          bool WMFAST_ = true, bool SKIP_ = true, int MINB_ = 1, bool WSKIP_ = false>
 struct GemmCfg {
     static constexpr int MINB = MINB_;      // resident CTAs per SM (persistent grid = MINB x #SMs)
+    // WSKIP: a warp whose whole WM x WN sub-tile lies beyond the block edge issues no DMMA for that tile (one uniform
+    // branch per pipeline stage, no predicates inside the unrolled k-steps); needs contiguous warp tiles (IL = false)
+    static constexpr bool WSKIP = WSKIP_;
     static constexpr bool cplx = CPLX;
     static constexpr bool IL = IL_, WMFAST = WMFAST_, SKIP = SKIP_;
     static constexpr int BM = BM_, BN = BN_, BK = BK_, WARPS_M = WARPS_M_, WARPS_N = WARPS_N_, STAGES = STAGES_;
@@ -304,6 +307,8 @@ grouped_gemm_kernel(const double* __restrict__ A, const double* __restrict__ B, 
         const int nj_cnt = !Cfg::SKIP ? NI : Cfg::IL ? (int)max((int64_t)0, (ng - wn + Cfg::WARPS_N - 1) / Cfg::WARPS_N)
                                                      : (int)min((int64_t)NI, max((int64_t)0, ng - wn * NI));
         const bool full_tile = (mi_cnt == MI) && (nj_cnt == NI);
+        // WSKIP: rows [wm WM, +WM) x columns [wn WN, +WN) of the tile against the block edge
+        const bool warp_live = !Cfg::WSKIP || ((int64_t)wm * Cfg::WM < M - m0 && (int64_t)wn * Cfg::WN < N - n0);
         int64_t n_iters = 0;
         for (int64_t p = p_begin; p < p_end; ++p) n_iters += (T.pairs[3 * p + 2] + BK - 1) / BK;
 
@@ -390,7 +395,9 @@ grouped_gemm_kernel(const double* __restrict__ A, const double* __restrict__ B, 
             const double* tB = sB + (size_t)stage * Cfg::B_STAGE;
             // the full / ragged decision is hoisted out of the unrolled k-steps: one basic block per stage,
             // so the fragment loads of the next k-step are scheduled between the DMMAs of the current one
-            if (full_tile) compute_stage<Cfg, true>(tA, tB, acc, wm, wn, lr, lc, mi_cnt, nj_cnt);
+            if (Cfg::WSKIP) {
+                if (warp_live) compute_stage<Cfg, true>(tA, tB, acc, wm, wn, lr, lc, mi_cnt, nj_cnt);
+            } else if (full_tile) compute_stage<Cfg, true>(tA, tB, acc, wm, wn, lr, lc, mi_cnt, nj_cnt);
             else compute_stage<Cfg, false>(tA, tB, acc, wm, wn, lr, lc, mi_cnt, nj_cnt);
         }
         cp_async_wait<0>();
@@ -756,7 +763,8 @@ __global__ void __launch_bounds__(SK_THREADS, 3) skinny_gemm_kernel(const double
 // float64: 64 x 64 tiles, 4 warps, four CTAs per SM (22.8 TFLOP/s on the chi = 4096 H_eff GEMMs; the 128 x 128 /
 // one-CTA-per-SM layout of the first version reached 18.5, and 13 further tile / pipeline variants measured within
 // -2 ... -20 % of this one -- profiles/r1b, profiles/r1c)
-using CfgR = GemmCfg<false, 64, 64, 16, 2, 2, 3, false, false, false, 4>;
+using CfgR0 = GemmCfg<false, 64, 64, 16, 2, 2, 3, false, false, false, 4>;
+using CfgR = GemmCfg<false, 64, 64, 16, 2, 2, 3, false, false, false, 4, true>;     // + warp-tile edge skipping
 using CfgC = GemmCfg<true, 128, 64, 8, 4, 2, 4>;      // 8 warps, 4 x 4 interleaved groups per warp, complex
 
 template <class Cfg>
@@ -853,7 +861,8 @@ int cyb_grouped_gemm_run(const void* a, const void* b, void* c, int dtype, const
     if (dtype == CYB_F64) {
         skinny_gemm_kernel<false><<<sk_grid, SK_THREADS, SK_SMEM_RING, stream>>>(A, B, C, T[1]);
         CYB_LAUNCH_CHECK();
-        return launch_gemm<CfgR>(a, b, c, T[0], stream);
+        static const bool wskip = !(getenv("CYB_GEMM_WSKIP") && atoi(getenv("CYB_GEMM_WSKIP")) == 0);
+        return wskip ? launch_gemm<CfgR>(a, b, c, T[0], stream) : launch_gemm<CfgR0>(a, b, c, T[0], stream);
     }
     skinny_gemm_kernel<true><<<sk_grid, SK_THREADS, SK_SMEM_RING, stream>>>(A, B, C, T[1]);
     CYB_LAUNCH_CHECK();

@@ -1,0 +1,143 @@
+// (f3) One streaming pass for a small operator acting on the MIDDLE legs of a large tensor:
+//
+//     out[o][a][b] = sum_i C_g[o][i] * in[i][a][b]            for every group g, a < na_g, b < nb_g
+//
+// "in row" i of group g is the vector  in + in_off[i] + a * in_stride[i] + [0, nb)  (contiguous in b), likewise the
+// output rows.  This is the two MPO applications of the DMRG effective Hamiltonian (LP . theta -> W1 -> W2 -> . RP,
+// toycodes/tenpy_toycodes/d_dmrg.py:70-88; PlanarHEffective, :94-116) executed as ONE kernel between the two fat GEMMs:
+// the first GEMM leaves x[vL, (wL p0 p1), vR], the second wants x'[vL, (p0 p1 wR), vR]; for a fixed pair of (vL, vR)
+// sectors the blocks of x / x' are rows of a small dense operator (the contraction W1 . W2 over wC restricted to the
+// charges that conserve the total), the same for every (a, b).  The reference -- and the unfused path here -- does
+// compose + permute_legs twice, i.e. five read + write passes over the 5 x theta-sized intermediates; this kernel reads
+// them once and writes them once.  HBM-bound: algorithmic bytes = (nin + nout) * na * nb * sizeof(element) per group.
+#include "common.cuh"
+
+namespace cyb {
+
+constexpr int MID_THREADS = 128;
+constexpr int MID_COLS = 2 * MID_THREADS;      // columns per work unit (two per thread)
+constexpr int MID_MAX = 16;                    // rows per side of a group's operator
+
+struct MidGroup {
+    int64_t na, nb, nin, nout, desc0, coef0;
+};
+
+template <bool CPLX>
+__global__ void __launch_bounds__(MID_THREADS, 4)
+middle_apply_kernel(const double* __restrict__ in, double* __restrict__ out, const MidGroup* __restrict__ groups,
+                    const int64_t* __restrict__ desc, const double* __restrict__ coef, const int64_t* __restrict__ work0,
+                    int64_t ngroups, int64_t nwork)
+{
+    constexpr int ES = CPLX ? 2 : 1;
+    __shared__ double s_coef[MID_MAX * MID_MAX * ES];
+    __shared__ int64_t s_desc[2 * MID_MAX][2];
+    __shared__ MidGroup s_g;
+    const int tid = threadIdx.x;
+    int64_t cur = -1;
+    // contiguous ranges of units per CTA: consecutive units share their group, whose tables are staged once
+    const int64_t per = (nwork + gridDim.x - 1) / gridDim.x;
+    const int64_t u0 = (int64_t)blockIdx.x * per, u1 = u0 + per < nwork ? u0 + per : nwork;
+    for (int64_t u = u0; u < u1; ++u) {
+        int64_t lo = cur >= 0 ? cur : 0;
+        if (cur < 0 || u >= work0[cur + 1]) {
+            int64_t hi = ngroups;
+            lo = cur >= 0 ? cur : 0;
+            while (hi - lo > 1) {
+                const int64_t mid = (lo + hi) >> 1;
+                if (work0[mid] <= u) lo = mid; else hi = mid;
+            }
+            __syncthreads();                     // everybody is done with the previous group's tables
+            if (tid == 0) s_g = groups[lo];
+            __syncthreads();
+            const int nin = (int)s_g.nin, nout = (int)s_g.nout;
+            for (int e = tid; e < nin * nout * ES; e += MID_THREADS) s_coef[e] = coef[s_g.coef0 * ES + e];
+            for (int e = tid; e < 2 * (nin + nout); e += MID_THREADS) s_desc[e >> 1][e & 1] = desc[2 * s_g.desc0 + e];
+            __syncthreads();
+            cur = lo;
+        }
+        const int nin = (int)s_g.nin, nout = (int)s_g.nout;
+        const int64_t nb = s_g.nb;
+        const int64_t chunks = (nb + MID_COLS - 1) / MID_COLS;
+        const int64_t local = u - work0[cur];
+        const int64_t a = local / chunks, b0 = (local % chunks) * MID_COLS + tid, b1 = b0 + MID_THREADS;
+        const bool ok0 = b0 < nb, ok1 = b1 < nb;
+        if (!CPLX) {
+            double x0[MID_MAX], x1[MID_MAX];
+#pragma unroll
+            for (int i = 0; i < MID_MAX; ++i) {
+                x0[i] = x1[i] = 0.0;
+                if (i < nin) {
+                    const double* p = in + s_desc[i][0] + a * s_desc[i][1];
+                    if (ok0) x0[i] = __ldcs(p + b0);
+                    if (ok1) x1[i] = __ldcs(p + b1);
+                }
+            }
+            for (int o = 0; o < nout; ++o) {
+                double y0 = 0.0, y1 = 0.0;
+                const double* c = s_coef + o * nin;
+#pragma unroll
+                for (int i = 0; i < MID_MAX; ++i)
+                    if (i < nin) { y0 += c[i] * x0[i]; y1 += c[i] * x1[i]; }
+                double* q = out + s_desc[nin + o][0] + a * s_desc[nin + o][1];
+                if (ok0) __stcs(q + b0, y0);
+                if (ok1) __stcs(q + b1, y1);
+            }
+        } else {
+            double2 x0[MID_MAX], x1[MID_MAX];
+#pragma unroll
+            for (int i = 0; i < MID_MAX; ++i) {
+                x0[i] = x1[i] = make_double2(0.0, 0.0);
+                if (i < nin) {
+                    const double2* p = reinterpret_cast<const double2*>(in) + s_desc[i][0] + a * s_desc[i][1];
+                    if (ok0) x0[i] = __ldcs(p + b0);
+                    if (ok1) x1[i] = __ldcs(p + b1);
+                }
+            }
+            for (int o = 0; o < nout; ++o) {
+                double2 y0 = make_double2(0.0, 0.0), y1 = y0;
+                const double* c = s_coef + 2 * o * nin;
+#pragma unroll
+                for (int i = 0; i < MID_MAX; ++i)
+                    if (i < nin) {
+                        const double cr = c[2 * i], ci = c[2 * i + 1];
+                        y0.x += cr * x0[i].x - ci * x0[i].y; y0.y += cr * x0[i].y + ci * x0[i].x;
+                        y1.x += cr * x1[i].x - ci * x1[i].y; y1.y += cr * x1[i].y + ci * x1[i].x;
+                    }
+                double2* q = reinterpret_cast<double2*>(out) + s_desc[nin + o][0] + a * s_desc[nin + o][1];
+                if (ok0) __stcs(q + b0, y0);
+                if (ok1) __stcs(q + b1, y1);
+            }
+        }
+    }
+}
+
+}  // namespace cyb
+
+using namespace cyb;
+
+extern "C" {
+
+int64_t cyb_middle_apply_max_rows(void) { return MID_MAX; }
+int64_t cyb_middle_apply_unit_cols(void) { return MID_COLS; }
+
+int cyb_middle_apply(const void* in, void* out, const int64_t* groups, const int64_t* desc, const void* coef,
+                     const int64_t* work0, int64_t ngroups, int64_t nwork, int dtype, cyb_stream_t stream_)
+{
+    CYB_REQUIRE(dtype == CYB_F64 || dtype == CYB_C128, "middle_apply: bad dtype %d", dtype);
+    CYB_REQUIRE(ngroups >= 0 && nwork >= 0, "middle_apply: negative counts");
+    if (ngroups == 0 || nwork == 0) return CYB_OK;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    int64_t grid = (int64_t)sm_count() * 4;
+    if (grid > nwork) grid = nwork;
+    const MidGroup* g = reinterpret_cast<const MidGroup*>(groups);
+    if (dtype == CYB_F64)
+        middle_apply_kernel<false><<<(unsigned)grid, MID_THREADS, 0, stream>>>(static_cast<const double*>(in), static_cast<double*>(out), g, desc,
+                                                                         static_cast<const double*>(coef), work0, ngroups, nwork);
+    else
+        middle_apply_kernel<true><<<(unsigned)grid, MID_THREADS, 0, stream>>>(static_cast<const double*>(in), static_cast<double*>(out), g, desc,
+                                                                        static_cast<const double*>(coef), work0, ngroups, nwork);
+    CYB_LAUNCH_CHECK();
+    return CYB_OK;
+}
+
+}  // extern "C"

@@ -321,10 +321,18 @@ class ShardedHEffective:
     contractions leave ``vR`` open and are rank-local; the last one contracts ``vR`` with RP, so each
     rank holds a partial sum over its ``vR`` sectors and one all_reduce finishes the matvec."""
 
-    def __init__(self, H, pg: ProcessGroup, shard_leg="vR", split_columns=False, column_align=16, column_heavy=0.6):
+    def __init__(self, H, pg: ProcessGroup, shard_leg="vR", split_columns=False, column_align=16, column_heavy=0.6,
+                 fused=False):
         self.H, self.pg, self.shard_leg = H, pg, shard_leg
         self.split_columns, self.column_align, self.column_heavy = split_columns, column_align, column_heavy
-        self.chains = [(H, None)]
+        self.fused = fused                  # rank-local chains run as GEMM / fused middle pass / GEMM (cyten_b200/fused.py)
+        self.chains = [(self._op(H), None)]
+
+    def _op(self, H):
+        if not self.fused:
+            return H
+        from .fused import FusedHEffective
+        return FusedHEffective(H)
 
     def shard_columns(self, theta: SymmetricTensor) -> SymmetricTensor:
         """Split finer than sectors: a heavy ``vR`` sector is cut into INDEX RANGES (``slice_leg``).  theta restricted
@@ -348,14 +356,14 @@ class ShardedHEffective:
         theta_local = slice_leg(theta, self.shard_leg, mine)
         rp_ax = 0                          # RP[vR, wR | vR']: its first codomain leg is contracted with theta's vR
         RP_r = slice_leg(H.RP, rp_ax, mine)
-        self.chains = [(HEffective(H.LP, RP_r, H.W1, H.W2, H.ct), None)]
+        self.chains = [(self._op(HEffective(H.LP, RP_r, H.W1, H.W2, H.ct)), None)]
         return theta_local
 
     def shard(self, theta: SymmetricTensor) -> SymmetricTensor:
         """Rank-local part of theta.  Work items are the sectors of ``shard_leg`` weighted by the flops each causes
         in the matvec chain (plan-only passes); items go to ranks by LPT, identical on every rank (pure integer
         bookkeeping).  With ``split_columns`` the heavy sectors are cut into index ranges first (``shard_columns``)."""
-        self.chains = [(self.H, None)]
+        self.chains = [(self._op(self.H), None)]
         if self.pg.world == 1:
             return theta
         if self.split_columns:

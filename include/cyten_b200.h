@@ -249,6 +249,19 @@ int cyb_block_lincomb(const void* x, const void* y, const void* z, void* out, co
 int cyb_scale_axis(const void* in, void* out, const int64_t* desc, const int64_t* work0, int64_t nblk,
                    int64_t nwork, const void* diag, int dtype, int diag_dtype, cyb_stream_t stream);
 
+/* ---- (f3) fused application of a small operator to the middle legs of a large tensor ------------------------- *
+ * out[o][a][b] = sum_i C_g[o][i] * in[i][a][b] for every group g, a < na, b < nb: ONE streaming pass that replaces the
+ * compose + permute_legs pairs of the two MPO applications inside the DMRG effective Hamiltonian (HEffective.matvec,
+ * toycodes/tenpy_toycodes/d_dmrg.py:70-88; PlanarHEffective :94-116 -> src/tensors/planar.cpp).
+ * groups (device) int64[ngroups][6] = (na, nb, nin, nout, desc_begin, coef_begin); desc (device) int64[.][2] =
+ * (element offset, element stride per a) of the nin input rows, then of the nout output rows of each group;
+ * coef (device): C_g row-major [nout][nin] elements of `dtype` at coef_begin; work0 (device) int64[ngroups + 1]: running
+ * count of work units, na * ceil(nb / cyb_middle_apply_unit_cols()) per group; nin, nout <= cyb_middle_apply_max_rows(). */
+int64_t cyb_middle_apply_max_rows(void);
+int64_t cyb_middle_apply_unit_cols(void);
+int cyb_middle_apply(const void* in, void* out, const int64_t* groups, const int64_t* desc, const void* coef,
+                     const int64_t* work0, int64_t ngroups, int64_t nwork, int dtype, cyb_stream_t stream);
+
 /* Keep-mask compaction (apply_mask / _mask_contract, abelian.cpp:2483-2582, 645-673):
  * out_i = in_i[idx, :] (axis 0) or in_i[:, idx] (axis 1).  desc (device) int64[nmat][6] =
  * (m_in, n_in, src_off, dst_off, idx_begin, idx_count); idx (device) concatenated index lists. */

@@ -455,6 +455,41 @@ def cyb_axpby(x, y, n, dtype, alpha, beta, stream=None):
     return 0
 
 
+def cyb_middle_apply_max_rows():
+    return 16
+
+
+def cyb_middle_apply_unit_cols():
+    return 256
+
+
+def cyb_middle_apply(inp, out, groups, desc, coef, work0, ngroups, nwork, dtype, stream=None):
+    """out[o][a][b] = sum_i C[o][i] in[i][a][b] per group (see include/cyten_b200.h)."""
+    dt = _dt(dtype)
+    G = _i64(groups, 6 * ngroups).reshape(ngroups, 6)
+    if ngroups == 0:
+        return 0
+    ndesc = int(max(g[4] + g[2] + g[3] for g in G))
+    D = _i64(desc, 2 * ndesc).reshape(ndesc, 2)
+    ncoef = int(max(g[5] + g[2] * g[3] for g in G))
+    Cf = _arr(coef, ncoef, dt)
+    hi = 0
+    for na, nb, nin, nout, d0, c0 in G:
+        for off, st in D[d0:d0 + nin + nout]:
+            hi = max(hi, int(off + (na - 1) * st + nb))
+    X = _arr(inp, hi, dt)
+    Y = _arr(out, hi, dt)
+    for na, nb, nin, nout, d0, c0 in G:
+        C = Cf[c0:c0 + nin * nout].reshape(nout, nin)
+        rows = np.stack([np.stack([X[off + a * st: off + a * st + nb] for a in range(na)]) for off, st in D[d0:d0 + nin]]) \
+            if nin else np.zeros((0, na, nb), dt)
+        res = np.tensordot(C, rows, axes=(1, 0))
+        for o, (off, st) in enumerate(D[d0 + nin:d0 + nin + nout]):
+            for a in range(na):
+                Y[off + a * st: off + a * st + nb] = res[o, a]
+    return 0
+
+
 def cyb_cutoff_inverse(x, y, n, cutoff, stream=None):
     """1 / np.where(np.abs(a) < cutoff, np.inf, a)  (NumpyBlockBackend::cutoff_inverse, numpy.cpp:645-656)."""
     xv = _arr(x, n, np.float64).copy()

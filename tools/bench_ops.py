@@ -36,11 +36,17 @@ def parse():
                          "block pair, cuSOLVER per sector; src/block_backend/torch.cpp:1341-1394, 898-911) on the same inputs")
     ap.add_argument("--rows", default="permute,combine,split,tdot,svd,tsvd,qr,eigh,blas1")
     ap.add_argument("--out", default=None)
+    ap.add_argument("--hubbard", action="store_true",
+                    help="BASELINE config 4 legs: Fermi-Hubbard U(1) x U(1) (charge, 2Sz), d = 4, 2-D Gaussian multiplicities "
+                         "(cyten_b200.workloads.hubbard_bond_leg): many small irregular blocks")
     return ap.parse_args()
 
 
-def legs_for(chi):
+def legs_for(chi, hubbard=False):
     from cyten_b200.workloads import CONFIG_LEGS, u1_bond_leg, u1_phys_leg
+    if hubbard:
+        from cyten_b200.workloads import hubbard_bond_leg, hubbard_phys_leg
+        return hubbard_bond_leg(chi), hubbard_phys_leg()
     if chi in CONFIG_LEGS:
         Q, sigma = CONFIG_LEGS[chi]
     else:   # interpolate the Gaussian width with log2(chi) like the named configs
@@ -108,7 +114,7 @@ def main():
     chi, dt = args.chi, args.dtype
     cx = dt == "complex128"
     esz = 16 if cx else 8
-    v, p = legs_for(chi)
+    v, p = legs_for(chi, args.hubbard)
     rows = args.rows.split(",")
 
     hostA = random_blocks([v, p], [v], 7, dt)
@@ -260,7 +266,7 @@ def main():
         sys.path.insert(0, str(ROOT / "oracle" / "_ref"))
         import cyten as rc
         rbe = rc.get_backend("abelian", "numpy")
-        sym = rc.u1_symmetry
+        sym = rc.u1_symmetry * rc.u1_symmetry if args.hubbard else rc.u1_symmetry
         rdt = rc.Dtype.complex128 if cx else rc.Dtype.float64
 
         def conv(leg):
