@@ -199,6 +199,14 @@ class ReferenceOps:
     def scale(self, T, a):
         return a * T
 
+    @staticmethod
+    def shard(T, leg):
+        return T
+
+    @staticmethod
+    def gather(T):
+        return T
+
 
 def build_reference_sweep_step(chi, plugin=None, nmv=1, chi_max=None, eps=1e-14, sync=None):
     """``SweepStep`` (BASELINE config 5) on reference tensors -- numpy backend, or the plugin if given -- from the same
@@ -717,7 +725,7 @@ def sweep_bench(chi, be, reps=3):
     synchronisation after every part, second pass)."""
     import torch
     from cyten_b200.workloads import build_sweep_step
-    st, th = build_sweep_step(chi, be)
+    st, th = build_sweep_step(chi, be, fused=True)
     st.update_bond(th)                       # plans
     best = float("inf")
     for _ in range(reps):

@@ -32,6 +32,19 @@ class Blas1Mixin:
         return self._library if self._library is not None else _lib.load()
 
     def _b1_workspace(self) -> torch.Tensor:
+        """Reduction workspace (per-CTA partials + arrival counter, re-armed by the last CTA): ONE per (backend, stream).
+        Two dot / lincomb-with-norm launches on different streams would otherwise share counters and partials; the same
+        holds for a graph replay overlapping an eager call, so graphs are captured and replayed on the stream they run on."""
+        import torch as _t
+        key = _t.cuda.current_stream(self.device).cuda_stream if self.device.type == "cuda" else 0
+        pool = self.__dict__.setdefault("_b1_work_by_stream", {})
+        w = pool.get(key)
+        if w is None:
+            n = int(self._b1_lib().cyb_blas1_workspace_bytes())
+            w = pool[key] = torch.zeros(n, dtype=torch.uint8, device=self.device)   # zeroed once, kernels re-arm it
+        return w
+
+    def _b1_workspace_single(self) -> torch.Tensor:
         w = getattr(self, "_b1_work", None)
         if w is None:
             n = int(self._b1_lib().cyb_blas1_workspace_bytes())

@@ -215,7 +215,9 @@ class LanczosGroundState:
             w = self._same_structure(self._matvec(v), v)
             u = linear_combination(1.0, w, -self.h_krylov[k, k], v)
             if self.reortho:
-                for c in vs[-self.N_cache:]:
+                # the reference's rebuild pushes v_k to the cache first and loops over all but the last entry
+                # (krylov_based.cpp:902-910): N_cache - 1 vectors, the same set the build phase orthogonalised against
+                for c in (vs[-(self.N_cache - 1):] if self.N_cache > 1 else []):
                     u = linear_combination(1.0, u, -self.be.inner(c.data, u.data), c)
             elif k > 0:
                 u = linear_combination(1.0, u, -beta, v_prev)

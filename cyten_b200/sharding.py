@@ -525,7 +525,8 @@ def all_gather_diagonal(S: DiagonalTensor, pg: ProcessGroup) -> DiagonalTensor:
 
 class ShardedSweepOps:
     """``SweepStep`` operations on N ranks: the truncated SVD runs sector-sharded (global cut from the all-gathered
-    singular values), its factors are replicated afterwards; everything else runs replicated on every rank."""
+    singular values), its factors are replicated afterwards; the environment updates are sharded along the leg that stays
+    open through their three contractions (disjoint result blocks, one gather each); the scale_axis calls run replicated."""
 
     def __init__(self, pg: ProcessGroup):
         from .workloads import NativeOps
@@ -534,6 +535,14 @@ class ShardedSweepOps:
 
     def __getattr__(self, name):
         return getattr(self._n, name)
+
+    def shard(self, T, leg):
+        """Block subset of T owned by this rank along an OPEN leg (LPT by block volume): the environment-update chains
+        keep that leg open to the end, so the ranks produce disjoint blocks of the result."""
+        return shard_by_leg(T, leg, self.pg)[0]
+
+    def gather(self, T):
+        return all_gather_blocks(T, self.pg)
 
     def truncated_svd(self, theta, new_labels, chi_max, svd_min):
         a, b = new_labels
@@ -553,8 +562,13 @@ def shard_sweep_step(step, pg: ProcessGroup, split_columns=True, column_heavy=0.
 
     def heff():
         if "SH" not in cache:
-            cache["SH"] = ShardedHEffective(plain_heff(), pg, split_columns=split_columns, column_heavy=column_heavy,
-                                           column_align=column_align)
+            fused, step.fused = bool(getattr(step, "fused", False)), False       # the rank-local chains are fused instead
+            try:
+                H = plain_heff()
+            finally:
+                step.fused = fused
+            cache["SH"] = ShardedHEffective(H, pg, split_columns=split_columns, column_heavy=column_heavy,
+                                           column_align=column_align, fused=fused)
 
         def matvec(theta):
             SH = cache["SH"]

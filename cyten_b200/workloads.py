@@ -196,6 +196,15 @@ class NativeOps:
     def scale(self, T, a):
         return self.t.scalar_multiply(a, T)
 
+    # multi-GPU hooks (cyten_b200.sharding.ShardedSweepOps): identity on one GPU
+    @staticmethod
+    def shard(T, leg):
+        return T
+
+    @staticmethod
+    def gather(T):
+        return T
+
 
 class SweepStep:
     """``DMRGEngine.update_bond`` of the reference's toy code (toycodes/tenpy_toycodes/d_dmrg.py:217-274, with
@@ -211,9 +220,10 @@ class SweepStep:
     ``ops``: :class:`NativeOps` or the same interface over the reference.  ``timings``: optional dict that receives the
     seconds per part when ``sync`` (a callable that waits for the device) is given."""
 
-    def __init__(self, ops, LP, RP, W, S_left, chi_max, eps=1e-14, nmv=1, sync=None):
+    def __init__(self, ops, LP, RP, W, S_left, chi_max, eps=1e-14, nmv=1, sync=None, fused=False):
         self.ops, self.LP, self.RP, self.W, self.S_left = ops, LP, RP, W, S_left
         self.chi_max, self.eps, self.nmv, self.sync = chi_max, eps, nmv, sync
+        self.fused = fused          # native tensors only: H_eff as GEMM / one fused middle pass / GEMM (cyten_b200/fused.py)
         self.timings = {}
 
     def _mark(self, name, t0):
@@ -229,7 +239,11 @@ class SweepStep:
         RP = o.permute_legs(self.RP, ["vR*", "wR*"], ["vR"])
         W1 = o.relabel(o.permute_legs(self.W, ["p", "wR"], ["wL", "p*"]), {"p": "p0", "p*": "p0*", "wR": "wC"})
         W2 = o.relabel(o.permute_legs(self.W, ["p", "wR"], ["wL", "p*"]), {"p": "p1", "p*": "p1*", "wL": "wC"})
-        return HEffective(LP, RP, W1, W2, o)
+        H = HEffective(LP, RP, W1, W2, o)
+        if self.fused:
+            from .fused import FusedHEffective
+            return FusedHEffective(H)
+        return H
 
     def update_bond(self, theta0):
         import time
@@ -259,16 +273,18 @@ class SweepStep:
         G = o.scale_axis(B, o.pinv(S_right, self.eps), "vR")
         A = o.scale_axis(G, self.S_left, "vL")
         Ac = o.permute_legs(o.hc(A), codomain=["vR*", "p*"])
+        Ac = o.shard(Ac, "vR*")       # N ranks: vR* stays open to the end, so every rank builds disjoint blocks of the result
         LP = o.compose(Ac, self.LP)                                              # vR* p* wL* vL*
         LP = o.permute_legs(LP, ["vL*", "vR*"], ["wL*", "p*"])
         LP = o.compose(LP, self.W)                                               # vL* vR* wR p*
         LP = o.permute_legs(LP, ["vR*", "wR"], ["vL*", "p*"])
         LP = o.compose(LP, A, relabel1={"vR*": "vL", "wR": "wL*"}, relabel2={"vR": "vL*"})
-        return o.permute_legs(LP, domain=["vL*", "wL*"])
+        return o.gather(o.permute_legs(LP, domain=["vL*", "wL*"]))
 
     def update_RP(self, B):
         o = self.ops
         Bc = o.permute_legs(o.hc(B), ["p*", "vL*"], ["vR*"])
+        Bc = o.shard(Bc, "vL*")       # N ranks: vL* (the new vR) stays open to the end
         RP = o.compose(Bc, self.RP)                                              # p* vL* vR* wR*
         RP = o.permute_legs(RP, ["vL*", "vR*"], ["p*", "wR*"])
         W_ = o.permute_legs(self.W, ["p", "wR"], ["wL", "p*"])
@@ -276,10 +292,10 @@ class SweepStep:
         RP = o.permute_legs(RP, ["wL", "vL*"], ["p*", "vR*"])
         B_ = o.permute_legs(B, ["p", "vR"], ["vL"])
         RP = o.compose(RP, B_, relabel1={"vL*": "vR", "wL": "wR*"}, relabel2={"vL": "vR*"})
-        return o.permute_legs(RP, ["vR"], ["wR*", "vR*"])
+        return o.gather(o.permute_legs(RP, ["vR"], ["wR*", "vR*"]))
 
 
-def build_sweep_step(chi: int, backend, nmv=1, chi_max=None, eps=1e-14, Q=None, sigma=None, sync=None):
+def build_sweep_step(chi: int, backend, nmv=1, chi_max=None, eps=1e-14, Q=None, sigma=None, sync=None, fused=False):
     """(SweepStep, theta0) on ``backend``: the H_eff tensors of :func:`build_heff` un-bent into the toy code's storage
     form (``LP[vL | vL*, wL*]``, ``RP[vR | wR*, vR*]``, ``W[wL, p | p*, wR]``), positive Schmidt values on the left bond."""
     from . import tensors as ops
@@ -291,7 +307,7 @@ def build_sweep_step(chi: int, backend, nmv=1, chi_max=None, eps=1e-14, Q=None, 
     W = ops.permute_legs(o.relabel(H.W1, {"p0": "p", "p0*": "p*", "wC": "wR"}), ["wL", "p"], ["p*", "wR"])
     v = sp["theta"][0][0]
     S_left = diagonal_from_numpy(schmidt_values(v), v, backend, ["vL", "vR"])
-    return SweepStep(o, LP, RP, W, S_left, chi_max or chi, eps, nmv, sync), theta
+    return SweepStep(o, LP, RP, W, S_left, chi_max or chi, eps, nmv, sync, fused), theta
 
 
 def schmidt_values(leg, seed=6) -> np.ndarray:

@@ -133,7 +133,7 @@ def worker(rank, world, port, out_dir, mode="gloo", chi=64):
         sQ, ssig = CONFIG_LEGS.get(schi, (3, 1.2))
         st1, th_s = build_sweep_step(schi, be, chi_max=(3 * schi) // 4, Q=sQ, sigma=ssig)
         r1 = st1.update_bond(th_s)
-        stN, _ = build_sweep_step(schi, be, chi_max=(3 * schi) // 4, Q=sQ, sigma=ssig)
+        stN, _ = build_sweep_step(schi, be, chi_max=(3 * schi) // 4, Q=sQ, sigma=ssig, fused=True)
         stN = sh.shard_sweep_step(stN, pg, column_heavy=0.25, column_align=2 if chi <= 64 else 16)
         rN = stN.update_bond(th_s)
         assert abs(rN["err"] - r1["err"]) <= 1e-13

@@ -28,8 +28,8 @@ def _ref_blocks(T):
     return bi, [np.asarray(b.to_numpy()) for b in T.data.blocks]
 
 
-def _check(chi, chi_max, backend):
-    st, th = build_sweep_step(chi, backend, chi_max=chi_max)
+def _check(chi, chi_max, backend, fused=False):
+    st, th = build_sweep_step(chi, backend, chi_max=chi_max, fused=fused)
     r = st.update_bond(th)
     st0, th0, ct = bench.build_reference_sweep_step(chi, chi_max=chi_max)
     r0 = st0.update_bond(th0)
@@ -53,11 +53,12 @@ def _check(chi, chi_max, backend):
     return st
 
 
-def test_sweep_step_matches_reference_oracle(oracle_backend):
-    _check(128, 100, oracle_backend)
+@pytest.mark.parametrize("fused", [False, True])
+def test_sweep_step_matches_reference_oracle(oracle_backend, fused):
+    _check(128, 100, oracle_backend, fused)
 
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("chi,chi_max", [(128, 100), (1024, 800)])
 def test_sweep_step_matches_reference_cuda(cuda_backend, chi, chi_max):
-    _check(chi, chi_max, cuda_backend)
+    _check(chi, chi_max, cuda_backend, fused=(chi > 128))

@@ -38,7 +38,7 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     be = B200AbelianBackend(dev)
     pg = sh.attach_process_group(be, dist.group.WORLD if world > 1 else None)
-    st, th = build_sweep_step(args.chi, be, chi_max=args.chi_max)
+    st, th = build_sweep_step(args.chi, be, chi_max=args.chi_max, fused=True)
     st = sh.shard_sweep_step(st, pg)
 
     def barrier():
