@@ -34,7 +34,8 @@ SIGNATURES = {
     "cyb_copy_blocks_run": (_int, [_vp, _vp, _vp, _i64, _int, _int, _vp]),
     "cyb_grouped_gemm_workspace": (_i64, [_i64]),
     "cyb_grouped_gemm_prepare": (_int, [_int, _vp, _vp, _vp, _vp, _i64, _vp, _i64, _vp]),
-    "cyb_grouped_gemm_run": (_int, [_vp, _vp, _vp, _int, _vp, _vp, _vp, _vp, _i64, _vp, _vp]),
+    "cyb_grouped_gemm_run": (_int, [_vp, _vp, _vp, _int, _vp, _vp, _vp, _vp, _i64, _vp, _int, _vp]),
+    "cyb_grouped_gemm_skinny_rows": (_i64, []),
     "cyb_compose_plan_workspace": (_i64, [_i64, _i64]),
     "cyb_compose_plan": (_int, [_vp, _i64, _i64, _i64, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _i64,
                                 _vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp,
@@ -51,7 +52,7 @@ SIGNATURES = {
     "cyb_cutoff_inverse": (_int, [_vp, _vp, _i64, _dbl, _vp]),
     "cyb_middle_apply_max_rows": (_i64, []),
     "cyb_middle_apply_unit_cols": (_i64, []),
-    "cyb_middle_apply": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _int, _vp]),
+    "cyb_middle_apply": (_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _int, _vp]),
     "cyb_scale_rows_cols": (_int, [_vp, _vp, _vp, _vp, _vp, _i64, _int, _int, _vp]),
     "cyb_gather_rows_cols": (_int, [_vp, _vp, _vp, _vp, _i64, _int, _int, _vp]),
     "cyb_blas1_workspace_bytes": (_i64, []),

@@ -64,11 +64,13 @@ class B200AbelianBackend(Blas1Mixin):
             self._plan_ws = lambda na, nb: _lib.load().cyb_compose_plan_workspace(na, nb)
             self._copy_ws = lambda jobs, n: _lib.load().cyb_copy_blocks_workspace(jobs.ctypes.data_as(C.c_void_p), n)
             self._gemm_ws = lambda n: _lib.load().cyb_grouped_gemm_workspace(n)
+            self._gemm_skinny_rows = int(_lib.load().cyb_grouped_gemm_skinny_rows())
         else:
             self._lib_call = _library.call
             self._plan_ws = _library.cyb_compose_plan_workspace
             self._copy_ws = lambda jobs, n: _library.cyb_copy_blocks_workspace(jobs.ctypes.data_as(C.c_void_p), n)
             self._gemm_ws = _library.cyb_grouped_gemm_workspace
+            self._gemm_skinny_rows = int(_library.cyb_grouped_gemm_skinny_rows())
         # Plans: the integer bookkeeping of an operation (sorted block_inds, copy job lists, GEMM work
         # lists and tile schedules) depends only on the structure of its operands (block_inds + legs),
         # not on the block contents.  It is computed ON DEVICE on the first call and replayed for every
@@ -563,6 +565,12 @@ class B200AbelianBackend(Blas1Mixin):
             plan["sig"] = None
             plan["nrun"] = n_out if subset is None else len(subset)
             plan["gemm_ws"] = None
+            # which of the two kernels have work (a launch without work costs ~13 us): streaming kernel for blocks of
+            # at most SK rows, DMMA kernel for the others
+            mn = plan["out_mn"] if subset is None else plan["out_mn"][np.asarray(subset, dtype=np.int64)]
+            live = (mn[:, 0] > 0) & (mn[:, 1] > 0)
+            plan["gemm_kernels"] = (1 if np.any(live & (mn[:, 0] <= self._gemm_skinny_rows)) else 0) | \
+                                   (2 if np.any(live & (mn[:, 0] > self._gemm_skinny_rows)) else 0)
             if plan["nrun"] and not self.dry_run:
                 with self._ctx():
                     d_sub = None if subset is None else to_device_i64(np.asarray(subset), self.device)
@@ -651,7 +659,7 @@ class B200AbelianBackend(Blas1Mixin):
         with self._ctx():
             self._call("cyb_grouped_gemm_run", ptr(a_buf), ptr(b_buf), ptr(res.buf), res.cyb_dtype,
                        ptr(plan["d_mn"]), ptr(plan["d_off"]), ptr(plan["d_pp"]), ptr(plan["d_pairs"]),
-                       plan["nrun"], ptr(plan["gemm_ws"]), self._stream())
+                       plan["nrun"], ptr(plan["gemm_ws"]), plan["gemm_kernels"], self._stream())
         if timed:
             e1.record()
             self.gemm_events.append((e0, e1))

@@ -620,32 +620,60 @@ householder_qr_kernel(const void* __restrict__ a_, void* __restrict__ q_, void* 
     }
     if constexpr (BLK) {
         double* qb_smem = reinterpret_cast<double*>(qr_smem);
+        // factorisation of the outer panel [J0, J0 + nbo) by the calling CTA
+        auto factor_outer = [&](int64_t J0, int nbo) {
+            const int64_t Jend = J0 + nbo;
+            if (panel_in_smem) {
+                qr_factor_outer_panel(reinterpret_cast<double*>(Wt), reinterpret_cast<double*>(uhead), tau, J0, nbo, nbo_max, m, qb_smem, prof ? pt : nullptr);
+                tick(1);
+                return;
+            }
+            for (int64_t j0 = J0; j0 < Jend; j0 += QR_NB) {
+                const int nb = (int)((Jend - j0) < QR_NB ? (Jend - j0) : QR_NB);
+                factor_panel(j0, nb);
+                __syncthreads();
+                tick(1);
+                if (j0 + nb < Jend) {           // the rest of the OUTER panel only
+                    load_panel(j0, nb);
+                    build_T(j0, nb);
+                    for (int64_t i = j0 + nb + warp; i < Jend; i += NW) apply_panel(Wt + i * m, j0, nb, true);
+                    __threadfence();
+                    __syncthreads();
+                }
+                tick(2);
+            }
+        };
+        // Look-ahead: while CTAs 1..G-1 apply panel p to the rows behind the NEXT panel, CTA 0 applies it to the next
+        // panel's rows only and factors that panel -- the panel factorisation (one CTA, shared-memory latency) leaves the
+        // critical path as long as it is not longer than the others' share of the trailing update.
+        if (trank == 0) factor_outer(0, (int)(k < nbo_max ? k : nbo_max));
+        Team<G>::sync();
+        tick(2);
         for (int64_t J0 = 0; J0 < k; J0 += nbo_max) {
             const int nbo = (int)((k - J0) < nbo_max ? (k - J0) : nbo_max);
             const int64_t Jend = J0 + nbo;
-            if (trank == 0 && panel_in_smem) {
-                qr_factor_outer_panel(reinterpret_cast<double*>(Wt), reinterpret_cast<double*>(uhead), tau, J0, nbo, nbo_max, m, qb_smem, prof ? pt : nullptr);
-                tick(1);
-            } else if (trank == 0) {
-                for (int64_t j0 = J0; j0 < Jend; j0 += QR_NB) {
-                    const int nb = (int)((Jend - j0) < QR_NB ? (Jend - j0) : QR_NB);
-                    factor_panel(j0, nb);
-                    __syncthreads();
-                    tick(1);
-                    if (j0 + nb < Jend) {           // the rest of the OUTER panel only
-                        load_panel(j0, nb);
-                        build_T(j0, nb);
-                        for (int64_t i = j0 + nb + warp; i < Jend; i += NW) apply_panel(Wt + i * m, j0, nb, true);
-                        __threadfence();
-                        __syncthreads();
-                    }
-                    tick(2);
+            const int nbo_next = (int)((k - Jend) < nbo_max ? (k - Jend) : nbo_max);     // 0 after the last panel
+            const int64_t Jnext_end = Jend + nbo_next;
+            const double* Wc = reinterpret_cast<const double*>(Wt);
+            const double* uh = reinterpret_cast<const double*>(uhead);
+            // look-ahead pays when the others' share of the trailing update (>= two 64-row blocks each) outlasts CTA 0's
+            // fixed cost of one small block apply + one panel factorisation (974 x 520: it does not; 3500 x 1800: 115 -> 95 ms)
+            const bool ahead = G > 1 && nbo_next > 0 && (n - Jnext_end) >= (int64_t)2 * QB_RB * (G - 1);
+            if (!ahead) {
+                if (Jend < n) qr_block_apply(reinterpret_cast<double*>(Wt), Jend, n, Wc, uh, tau, J0, nbo, m, true, qb_smem, trank, G, prof ? pt : nullptr);
+                if (nbo_next > 0) {
+                    Team<G>::sync();
+                    tick(3);
+                    if (trank == 0) factor_outer(Jend, nbo_next);
                 }
+            } else if (trank == 0) {
+                qr_block_apply(reinterpret_cast<double*>(Wt), Jend, Jnext_end, Wc, uh, tau, J0, nbo, m, true, qb_smem, 0, 1, prof ? pt : nullptr);
+                __threadfence();
+                __syncthreads();
+                factor_outer(Jend, nbo_next);
+            } else if (Jnext_end < n) {
+                qr_block_apply(reinterpret_cast<double*>(Wt), Jnext_end, n, Wc, uh, tau, J0, nbo, m, true, qb_smem, trank - 1, G - 1, nullptr);
             }
-            Team<G>::sync();
-            tick(2);
-            if (Jend < n) qr_block_apply(reinterpret_cast<double*>(Wt), Jend, n, reinterpret_cast<const double*>(Wt),
-                                         reinterpret_cast<const double*>(uhead), tau, J0, nbo, m, true, qb_smem, trank, G, prof ? pt : nullptr);
             Team<G>::sync();
             tick(3);
         }

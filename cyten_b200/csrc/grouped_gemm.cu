@@ -834,9 +834,11 @@ int cyb_grouped_gemm_prepare(int dtype, const int64_t* out_mn, const int64_t* ou
     return CYB_OK;
 }
 
+int64_t cyb_grouped_gemm_skinny_rows(void) { return SK_MAXM; }
+
 int cyb_grouped_gemm_run(const void* a, const void* b, void* c, int dtype, const int64_t* out_mn,
                          const int64_t* out_off, const int64_t* out_pair_ptr, const int64_t* pairs,
-                         int64_t nblocks, void* workspace, cyb_stream_t stream_)
+                         int64_t nblocks, void* workspace, int kernels, cyb_stream_t stream_)
 {
     CYB_REQUIRE(dtype == CYB_F64 || dtype == CYB_C128, "grouped_gemm_run: bad dtype %d", dtype);
     CYB_REQUIRE(nblocks >= 0, "grouped_gemm_run: nblocks < 0");
@@ -858,14 +860,23 @@ int cyb_grouped_gemm_run(const void* a, const void* b, void* c, int dtype, const
         CYB_CHECK_CUDA(cudaFuncSetAttribute(skinny_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SK_SMEM_RING));
     }
     const int sk_grid = sm_count() * 3;   // resident CTAs; units are drawn from an atomic ticket
+    // `kernels`: bit 0 = some block has 1 <= M <= SK_MAXM rows (streaming kernel), bit 1 = some block has more (DMMA kernel);
+    // the caller knows from out_mn, and a kernel without work is not launched (13 us each under ncu)
+    const bool run_sk = (kernels & 1) != 0, run_mma = (kernels & 2) != 0;
     if (dtype == CYB_F64) {
-        skinny_gemm_kernel<false><<<sk_grid, SK_THREADS, SK_SMEM_RING, stream>>>(A, B, C, T[1]);
-        CYB_LAUNCH_CHECK();
+        if (run_sk) {
+            skinny_gemm_kernel<false><<<sk_grid, SK_THREADS, SK_SMEM_RING, stream>>>(A, B, C, T[1]);
+            CYB_LAUNCH_CHECK();
+        }
+        if (!run_mma) return CYB_OK;
         static const bool wskip = !(getenv("CYB_GEMM_WSKIP") && atoi(getenv("CYB_GEMM_WSKIP")) == 0);
         return wskip ? launch_gemm<CfgR>(a, b, c, T[0], stream) : launch_gemm<CfgR0>(a, b, c, T[0], stream);
     }
-    skinny_gemm_kernel<true><<<sk_grid, SK_THREADS, SK_SMEM_RING, stream>>>(A, B, C, T[1]);
-    CYB_LAUNCH_CHECK();
+    if (run_sk) {
+        skinny_gemm_kernel<true><<<sk_grid, SK_THREADS, SK_SMEM_RING, stream>>>(A, B, C, T[1]);
+        CYB_LAUNCH_CHECK();
+    }
+    if (!run_mma) return CYB_OK;
     return launch_gemm<CfgC>(a, b, c, T[0], stream);
 }
 
@@ -881,7 +892,7 @@ int cyb_grouped_gemm(const void* a, const void* b, void* c, int dtype, const int
     if (!ws.ptr) return CYB_ERR_CUDA;
     int rc = cyb_grouped_gemm_prepare(dtype, out_mn, out_pair_ptr, pairs, block_subset, nblocks, ws.ptr, bytes, stream_);
     if (rc != CYB_OK) return rc;
-    return cyb_grouped_gemm_run(a, b, c, dtype, out_mn, out_off, out_pair_ptr, pairs, nblocks, ws.ptr, stream_);
+    return cyb_grouped_gemm_run(a, b, c, dtype, out_mn, out_off, out_pair_ptr, pairs, nblocks, ws.ptr, 3, stream_);
 }
 
 }  // extern "C"

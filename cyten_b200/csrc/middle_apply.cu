@@ -22,15 +22,17 @@ struct MidGroup {
     int64_t na, nb, nin, nout, desc0, coef0;
 };
 
-template <bool CPLX>
-__global__ void __launch_bounds__(MID_THREADS, 4)
+// MAXR: compile-time bound on the rows per side of every group's operator (8 for the D = 5, d = 2 effective Hamiltonian:
+// half the registers of the general 16-row version, twice the resident CTAs and bytes in flight)
+template <bool CPLX, int MAXR>
+__global__ void __launch_bounds__(MID_THREADS, MAXR <= 8 ? 8 : 4)
 middle_apply_kernel(const double* __restrict__ in, double* __restrict__ out, const MidGroup* __restrict__ groups,
                     const int64_t* __restrict__ desc, const double* __restrict__ coef, const int64_t* __restrict__ work0,
                     int64_t ngroups, int64_t nwork)
 {
     constexpr int ES = CPLX ? 2 : 1;
-    __shared__ double s_coef[MID_MAX * MID_MAX * ES];
-    __shared__ int64_t s_desc[2 * MID_MAX][2];
+    __shared__ double s_coef[MAXR * MAXR * ES];
+    __shared__ int64_t s_desc[2 * MAXR][2];
     __shared__ MidGroup s_g;
     const int tid = threadIdx.x;
     int64_t cur = -1;
@@ -62,9 +64,9 @@ middle_apply_kernel(const double* __restrict__ in, double* __restrict__ out, con
         const int64_t a = local / chunks, b0 = (local % chunks) * MID_COLS + tid, b1 = b0 + MID_THREADS;
         const bool ok0 = b0 < nb, ok1 = b1 < nb;
         if (!CPLX) {
-            double x0[MID_MAX], x1[MID_MAX];
+            double x0[MAXR], x1[MAXR];
 #pragma unroll
-            for (int i = 0; i < MID_MAX; ++i) {
+            for (int i = 0; i < MAXR; ++i) {
                 x0[i] = x1[i] = 0.0;
                 if (i < nin) {
                     const double* p = in + s_desc[i][0] + a * s_desc[i][1];
@@ -76,16 +78,16 @@ middle_apply_kernel(const double* __restrict__ in, double* __restrict__ out, con
                 double y0 = 0.0, y1 = 0.0;
                 const double* c = s_coef + o * nin;
 #pragma unroll
-                for (int i = 0; i < MID_MAX; ++i)
+                for (int i = 0; i < MAXR; ++i)
                     if (i < nin) { y0 += c[i] * x0[i]; y1 += c[i] * x1[i]; }
                 double* q = out + s_desc[nin + o][0] + a * s_desc[nin + o][1];
                 if (ok0) __stcs(q + b0, y0);
                 if (ok1) __stcs(q + b1, y1);
             }
         } else {
-            double2 x0[MID_MAX], x1[MID_MAX];
+            double2 x0[MAXR], x1[MAXR];
 #pragma unroll
-            for (int i = 0; i < MID_MAX; ++i) {
+            for (int i = 0; i < MAXR; ++i) {
                 x0[i] = x1[i] = make_double2(0.0, 0.0);
                 if (i < nin) {
                     const double2* p = reinterpret_cast<const double2*>(in) + s_desc[i][0] + a * s_desc[i][1];
@@ -97,7 +99,7 @@ middle_apply_kernel(const double* __restrict__ in, double* __restrict__ out, con
                 double2 y0 = make_double2(0.0, 0.0), y1 = y0;
                 const double* c = s_coef + 2 * o * nin;
 #pragma unroll
-                for (int i = 0; i < MID_MAX; ++i)
+                for (int i = 0; i < MAXR; ++i)
                     if (i < nin) {
                         const double cr = c[2 * i], ci = c[2 * i + 1];
                         y0.x += cr * x0[i].x - ci * x0[i].y; y0.y += cr * x0[i].y + ci * x0[i].x;
@@ -121,21 +123,23 @@ int64_t cyb_middle_apply_max_rows(void) { return MID_MAX; }
 int64_t cyb_middle_apply_unit_cols(void) { return MID_COLS; }
 
 int cyb_middle_apply(const void* in, void* out, const int64_t* groups, const int64_t* desc, const void* coef,
-                     const int64_t* work0, int64_t ngroups, int64_t nwork, int dtype, cyb_stream_t stream_)
+                     const int64_t* work0, int64_t ngroups, int64_t nwork, int64_t max_rows, int dtype, cyb_stream_t stream_)
 {
+    CYB_REQUIRE(max_rows >= 0 && max_rows <= MID_MAX, "middle_apply: max_rows %lld outside [0, %d]", (long long)max_rows, MID_MAX);
     CYB_REQUIRE(dtype == CYB_F64 || dtype == CYB_C128, "middle_apply: bad dtype %d", dtype);
     CYB_REQUIRE(ngroups >= 0 && nwork >= 0, "middle_apply: negative counts");
     if (ngroups == 0 || nwork == 0) return CYB_OK;
     cudaStream_t stream = (cudaStream_t)stream_;
-    int64_t grid = (int64_t)sm_count() * 4;
+    const bool small = max_rows <= 8;
+    int64_t grid = (int64_t)sm_count() * (small ? 8 : 4);
     if (grid > nwork) grid = nwork;
     const MidGroup* g = reinterpret_cast<const MidGroup*>(groups);
-    if (dtype == CYB_F64)
-        middle_apply_kernel<false><<<(unsigned)grid, MID_THREADS, 0, stream>>>(static_cast<const double*>(in), static_cast<double*>(out), g, desc,
-                                                                         static_cast<const double*>(coef), work0, ngroups, nwork);
-    else
-        middle_apply_kernel<true><<<(unsigned)grid, MID_THREADS, 0, stream>>>(static_cast<const double*>(in), static_cast<double*>(out), g, desc,
-                                                                        static_cast<const double*>(coef), work0, ngroups, nwork);
+    const double *pi = static_cast<const double*>(in), *pc = static_cast<const double*>(coef);
+    double* po = static_cast<double*>(out);
+#define CYB_MID_LAUNCH(CP, MR) middle_apply_kernel<CP, MR><<<(unsigned)grid, MID_THREADS, 0, stream>>>(pi, po, g, desc, pc, work0, ngroups, nwork)
+    if (dtype == CYB_F64) { if (small) CYB_MID_LAUNCH(false, 8); else CYB_MID_LAUNCH(false, MID_MAX); }
+    else { if (small) CYB_MID_LAUNCH(true, 8); else CYB_MID_LAUNCH(true, MID_MAX); }
+#undef CYB_MID_LAUNCH
     CYB_LAUNCH_CHECK();
     return CYB_OK;
 }

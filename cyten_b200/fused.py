@@ -123,6 +123,7 @@ class FusedHEffective:
             Cf.append(coef.reshape(-1))
             W0.append(W0[-1] + na * ((nb + ucols - 1) // ucols))
         plan = dict(y_bi=y_bi, y_shapes=y_shapes, y_cod=y_cod, y_dom=y_dom, y_labels=y_labels, ngroups=len(G), nwork=W0[-1],
+                    max_rows=max([max(g[2], g[3]) for g in G], default=0),
                     bytes=sum((g[2] + g[3]) * g[0] * g[1] for g in G) * (16 if cx else 8), sig=None)
         if G and not be.dry_run:
             with be._ctx():
@@ -146,7 +147,7 @@ class FusedHEffective:
         if plan["ngroups"] and not be.dry_run:
             with be._ctx():
                 be._call("cyb_middle_apply", ptr(x.data.buf), ptr(Y.buf), ptr(plan["groups"]), ptr(plan["desc"]), ptr(plan["coef"]),
-                         ptr(plan["work0"]), plan["ngroups"], plan["nwork"], Y.cyb_dtype, be._stream())
+                         ptr(plan["work0"]), plan["ngroups"], plan["nwork"], plan["max_rows"], Y.cyb_dtype, be._stream())
         return SymmetricTensor(Y, plan["y_cod"], plan["y_dom"], be, plan["y_labels"])
 
     def matvec(self, theta: SymmetricTensor) -> SymmetricTensor:

@@ -161,9 +161,12 @@ int64_t cyb_grouped_gemm_workspace(int64_t nblocks);
 int cyb_grouped_gemm_prepare(int dtype, const int64_t* out_mn, const int64_t* out_pair_ptr,
                              const int64_t* pairs, const int64_t* block_subset, int64_t nblocks,
                              void* workspace, int64_t workspace_bytes, cyb_stream_t stream);
+/* `kernels`: bit 0 = launch the streaming kernel (some block has 1 <= M <= cyb_grouped_gemm_skinny_rows() rows), bit 1 =
+ * launch the DMMA kernel (some block has more); 3 launches both. */
+int64_t cyb_grouped_gemm_skinny_rows(void);
 int cyb_grouped_gemm_run(const void* a, const void* b, void* c, int dtype, const int64_t* out_mn,
                          const int64_t* out_off, const int64_t* out_pair_ptr, const int64_t* pairs,
-                         int64_t nblocks, void* workspace, cyb_stream_t stream);
+                         int64_t nblocks, void* workspace, int kernels, cyb_stream_t stream);
 
 /* ---- (a7,a9,a10) per-sector factorisations ----------------------------------------------- *
  * Batched over `nmat` independent row-major matrices inside arenas (device pointers a,u,s,...).
@@ -256,11 +259,12 @@ int cyb_scale_axis(const void* in, void* out, const int64_t* desc, const int64_t
  * groups (device) int64[ngroups][6] = (na, nb, nin, nout, desc_begin, coef_begin); desc (device) int64[.][2] =
  * (element offset, element stride per a) of the nin input rows, then of the nout output rows of each group;
  * coef (device): C_g row-major [nout][nin] elements of `dtype` at coef_begin; work0 (device) int64[ngroups + 1]: running
- * count of work units, na * ceil(nb / cyb_middle_apply_unit_cols()) per group; nin, nout <= cyb_middle_apply_max_rows(). */
+ * count of work units, na * ceil(nb / cyb_middle_apply_unit_cols()) per group; max_rows = max over groups of nin, nout
+ * (<= cyb_middle_apply_max_rows(); <= 8 selects the kernel with half the registers). */
 int64_t cyb_middle_apply_max_rows(void);
 int64_t cyb_middle_apply_unit_cols(void);
 int cyb_middle_apply(const void* in, void* out, const int64_t* groups, const int64_t* desc, const void* coef,
-                     const int64_t* work0, int64_t ngroups, int64_t nwork, int dtype, cyb_stream_t stream);
+                     const int64_t* work0, int64_t ngroups, int64_t nwork, int64_t max_rows, int dtype, cyb_stream_t stream);
 
 /* Keep-mask compaction (apply_mask / _mask_contract, abelian.cpp:2483-2582, 645-673):
  * out_i = in_i[idx, :] (axis 0) or in_i[:, idx] (axis 1).  desc (device) int64[nmat][6] =

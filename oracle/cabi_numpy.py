@@ -309,7 +309,11 @@ def cyb_grouped_gemm_prepare(dtype, out_mn, out_pair_ptr, pairs, block_subset, n
     return 0
 
 
-def cyb_grouped_gemm_run(a, b, c, dtype, out_mn, out_off, out_pair_ptr, pairs, nblocks, workspace,
+def cyb_grouped_gemm_skinny_rows():
+    return 8
+
+
+def cyb_grouped_gemm_run(a, b, c, dtype, out_mn, out_off, out_pair_ptr, pairs, nblocks, workspace, kernels=3,
                          stream=None):
     return cyb_grouped_gemm(a, b, c, dtype, out_mn, out_off, out_pair_ptr, pairs, workspace, nblocks)
 
@@ -463,7 +467,7 @@ def cyb_middle_apply_unit_cols():
     return 256
 
 
-def cyb_middle_apply(inp, out, groups, desc, coef, work0, ngroups, nwork, dtype, stream=None):
+def cyb_middle_apply(inp, out, groups, desc, coef, work0, ngroups, nwork, max_rows, dtype, stream=None):
     """out[o][a][b] = sum_i C[o][i] in[i][a][b] per group (see include/cyten_b200.h)."""
     dt = _dt(dtype)
     G = _i64(groups, 6 * ngroups).reshape(ngroups, 6)

@@ -87,7 +87,7 @@ def test_middle_apply_kernel(kind, dtype):
     d_c = t(np.concatenate(coefs))
     p = lambda z: C.c_void_p(z.data_ptr())
     stream = C.c_void_p(torch.cuda.current_stream().cuda_stream if kind == "cuda" else 0)
-    call("cyb_middle_apply", p(d_x), p(d_y), p(d_g), p(d_d), p(d_c), p(d_w), len(groups), work0[-1], 1 if cx else 0, stream)
+    call("cyb_middle_apply", p(d_x), p(d_y), p(d_g), p(d_d), p(d_c), p(d_w), len(groups), work0[-1], 16, 1 if cx else 0, stream)
     got = d_y.cpu().numpy()
     for (na, nb, nin, nout), (ins, outs, c) in zip(spec, layout):
         X = np.stack([x[off:off + na * nb].reshape(na, nb) for off, _ in ins]) if nin else np.zeros((0, na, nb), npdt)
