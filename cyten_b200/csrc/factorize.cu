@@ -643,39 +643,39 @@ householder_qr_kernel(const void* __restrict__ a_, void* __restrict__ q_, void* 
                 tick(2);
             }
         };
-        // Look-ahead: while CTAs 1..G-1 apply panel p to the rows behind the NEXT panel, CTA 0 applies it to the next
-        // panel's rows only and factors that panel -- the panel factorisation (one CTA, shared-memory latency) leaves the
-        // critical path as long as it is not longer than the others' share of the trailing update.
-        if (trank == 0) factor_outer(0, (int)(k < nbo_max ? k : nbo_max));
-        Team<G>::sync();
-        tick(2);
-        for (int64_t J0 = 0; J0 < k; J0 += nbo_max) {
-            const int nbo = (int)((k - J0) < nbo_max ? (k - J0) : nbo_max);
-            const int64_t Jend = J0 + nbo;
-            const int nbo_next = (int)((k - Jend) < nbo_max ? (k - Jend) : nbo_max);     // 0 after the last panel
+        // Iteration `it` applies outer panel it-1 to the trailing rows and factors outer panel `it` (one call site each, so
+        // that the two big device functions are inlined once and keep their shared-memory address space).
+        // Look-ahead: while CTAs 1..G-1 apply panel it-1 to the rows behind panel `it`, CTA 0 applies it to the rows of
+        // panel `it` only and factors that panel.  It pays when the others' share of the trailing update (>= two 64-row
+        // blocks each) outlasts CTA 0's fixed cost of one small block apply + one panel factorisation (974 x 520: it does
+        // not; 3500 x 1800: 115 -> 95 ms).
+        const int64_t npanels = (k + nbo_max - 1) / nbo_max;
+        const double* Wc = reinterpret_cast<const double*>(Wt);
+        const double* uh = reinterpret_cast<const double*>(uhead);
+        for (int64_t it = 0; it <= npanels; ++it) {
+            const int64_t Jend = it * nbo_max < k ? it * nbo_max : k;                    // first row behind panel it-1
+            const int nbo_next = it < npanels ? (int)((k - Jend) < nbo_max ? (k - Jend) : nbo_max) : 0;
             const int64_t Jnext_end = Jend + nbo_next;
-            const double* Wc = reinterpret_cast<const double*>(Wt);
-            const double* uh = reinterpret_cast<const double*>(uhead);
-            // look-ahead pays when the others' share of the trailing update (>= two 64-row blocks each) outlasts CTA 0's
-            // fixed cost of one small block apply + one panel factorisation (974 x 520: it does not; 3500 x 1800: 115 -> 95 ms)
-            const bool ahead = G > 1 && nbo_next > 0 && (n - Jnext_end) >= (int64_t)2 * QB_RB * (G - 1);
-            if (!ahead) {
-                if (Jend < n) qr_block_apply(reinterpret_cast<double*>(Wt), Jend, n, Wc, uh, tau, J0, nbo, m, true, qb_smem, trank, G, prof ? pt : nullptr);
-                if (nbo_next > 0) {
-                    Team<G>::sync();
-                    tick(3);
-                    if (trank == 0) factor_outer(Jend, nbo_next);
+            const bool ahead = G > 1 && it >= 1 && nbo_next > 0 && (n - Jnext_end) >= (int64_t)2 * QB_RB * (G - 1);
+            if (it >= 1) {
+                const int64_t J0 = (it - 1) * nbo_max;
+                const int nbo = (int)(Jend - J0);
+                int64_t rb = Jend, re = n;
+                unsigned c = trank, nc = G;
+                if (ahead) {
+                    if (trank == 0) { re = Jnext_end; c = 0; nc = 1; }
+                    else { rb = Jnext_end; c = trank - 1; nc = G - 1; }
                 }
-            } else if (trank == 0) {
-                qr_block_apply(reinterpret_cast<double*>(Wt), Jend, Jnext_end, Wc, uh, tau, J0, nbo, m, true, qb_smem, 0, 1, prof ? pt : nullptr);
-                __threadfence();
-                __syncthreads();
-                factor_outer(Jend, nbo_next);
-            } else if (Jnext_end < n) {
-                qr_block_apply(reinterpret_cast<double*>(Wt), Jnext_end, n, Wc, uh, tau, J0, nbo, m, true, qb_smem, trank - 1, G - 1, nullptr);
+                if (rb < re) qr_block_apply(reinterpret_cast<double*>(Wt), rb, re, Wc, uh, tau, J0, nbo, m, true, qb_smem, c, nc, prof ? pt : nullptr);
+                if (nbo_next > 0) {
+                    if (ahead) { __threadfence(); __syncthreads(); }
+                    else Team<G>::sync();
+                }
+                tick(3);
             }
-            Team<G>::sync();
-            tick(3);
+            if (nbo_next > 0 && trank == 0) factor_outer(Jend, nbo_next);
+            if (nbo_next > 0 || it >= 1) Team<G>::sync();
+            tick(2);
         }
     } else {
     for (int64_t j0 = 0; j0 < k; j0 += QR_NB) {

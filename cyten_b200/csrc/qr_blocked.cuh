@@ -62,7 +62,7 @@ struct QbProf {
 // ---- the outer panel, factored in shared memory by the calling CTA (all 1024 threads) -------------------------------
 // Ps: (nbo_cap + QB_NBI) x m doubles of shared memory (nbo <= nbo_cap).  On return rows [J0, J0 + nbo) of Wt hold R (columns <= row) and the reflector
 // tails, uhead / tau the heads and scalars (global memory, fenced).
-__device__ __noinline__ void qr_factor_outer_panel(double* __restrict__ Wt, double* __restrict__ uhead, double* __restrict__ tau,
+__device__ __forceinline__ void qr_factor_outer_panel(double* __restrict__ Wt, double* __restrict__ uhead, double* __restrict__ tau,
                                       int64_t J0, int nbo, int nbo_cap, int64_t m, double* Ps, unsigned long long* pt = nullptr)
 {
     QbProf P{pt, 0};
@@ -223,7 +223,7 @@ __device__ __noinline__ void qr_factor_outer_panel(double* __restrict__ Wt, doub
 // one A fragment feeds the four reflector tiles in pass 1, W fragments held in registers feed the eight column tiles in
 // pass 2 -- fewer shared-memory reads per DMMA than one 8 x 8 tile per warp), warps 8..11 accumulate Z = U U^T on the
 // CTA's first pass, warps 12..15 only issue the cp.async of the 3-stage operand pipeline.
-__device__ __noinline__ void qr_block_apply(double* __restrict__ Y, int64_t row_begin, int64_t row_end, const double* __restrict__ Wt,
+__device__ __forceinline__ void qr_block_apply(double* __restrict__ Y, int64_t row_begin, int64_t row_end, const double* __restrict__ Wt,
                                const double* __restrict__ uhead, const double* __restrict__ tau, int64_t J0, int nbo,
                                int64_t m, bool adj, double* smem, unsigned cta, unsigned ncta,
                                unsigned long long* pt = nullptr)
