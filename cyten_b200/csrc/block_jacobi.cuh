@@ -327,7 +327,21 @@ bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ it
     // G = sum of the partials, in slice order
     for (int e = tid; e < BJ_R * BJ_R; e += BJ_RT) {
         double g = 0.0, gi = 0.0;
-        for (int w = 0; w < it.nw; ++w) {
+        // fixed summation order; four partials are in flight at a time (one L2 round trip instead of four)
+        int w = 0;
+        for (; w + 3 < it.nw; w += 4) {
+            const double* part = gpart + (size_t)(it.w0 + w) * (BJ_R * BJ_R * CM);
+            const double a0 = __ldcg(part + e), a1 = __ldcg(part + (size_t)(BJ_R * BJ_R * CM) + e);
+            const double a2 = __ldcg(part + (size_t)2 * (BJ_R * BJ_R * CM) + e), a3 = __ldcg(part + (size_t)3 * (BJ_R * BJ_R * CM) + e);
+            g += a0; g += a1; g += a2; g += a3;
+            if (CX) {
+                const double b0 = __ldcg(part + BJ_R * BJ_R + e), b1 = __ldcg(part + (size_t)(BJ_R * BJ_R * CM) + BJ_R * BJ_R + e);
+                const double b2 = __ldcg(part + (size_t)2 * (BJ_R * BJ_R * CM) + BJ_R * BJ_R + e);
+                const double b3 = __ldcg(part + (size_t)3 * (BJ_R * BJ_R * CM) + BJ_R * BJ_R + e);
+                gi += b0; gi += b1; gi += b2; gi += b3;
+            }
+        }
+        for (; w < it.nw; ++w) {
             const double* part = gpart + (size_t)(it.w0 + w) * (BJ_R * BJ_R * CM);
             g += __ldcg(part + e);
             if (CX) gi += __ldcg(part + BJ_R * BJ_R + e);
@@ -362,6 +376,114 @@ bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ it
     const int nsteps = cross ? BJ_B : BJ_B - 1;
     const int nrot = cross ? BJ_B : BJ_B / 2;
     __syncthreads();
+    if (cross) {
+        // Block pairs (every round but the first of a sweep): ONE barrier per step, rotations computed once.
+        // Rotation b of step s pairs row p_b = b with row q_b = 32 + (b + s) % 32.  Thread (warp a, lane b) owns the
+        // 2 x 2 block G[{p_a, q_a}][{p_b, q_b}] and columns a, a + 32 of the two rows of Q that rotation b mixes.  The
+        // rotations of step s + 1 need the new diagonal and the new pivots G[p_b][q_{b+1}]: exactly the blocks (b, b) and
+        // (b, b + 1).  Warp 0 updates those 64 blocks FIRST (two per lane), derives the next rotations from its own
+        // registers (+ one shuffle) and publishes them in the other half of a double-buffered table while the other
+        // warps are still updating their blocks -- so the serial sqrt / divide / rsqrt chain of a step hides behind the
+        // block updates instead of sitting between two barriers.
+        __shared__ double s_cs[2][BJ_B], s_sn[2][BJ_B], s_si[2][BJ_B];
+        const int wa = tid >> 5, lb = tid & 31;
+        auto rotation = [&](int pb, int qb, double al, double be, double gr, double gi, double& cs, double& sn, double& si) {
+            cs = 1.0; sn = 0.0; si = 0.0;
+            if (pb < it.ni && qb - BJ_B < it.nj) {
+                const double g2 = gr * gr + gi * gi;
+                if (al >= FZ_TINY && be >= FZ_TINY && !(al <= fl && be <= fl) && g2 > tol2 * al * be) {
+                    const double rg = CX ? rsqrt(g2) : 0.0;
+                    const double gabs = CX ? g2 * rg : fabs(gr);
+                    const double d = be - al, g2x = 2.0 * gabs;
+                    const double t = (d >= 0.0 ? g2x : -g2x) / (fabs(d) + sqrt(d * d + g2x * g2x));
+                    cs = rsqrt(1.0 + t * t);
+                    const double s0 = cs * t;
+                    if (CX) { sn = s0 * gr * rg; si = s0 * gi * rg; }
+                    else sn = gr >= 0.0 ? s0 : -s0;
+                }
+            }
+        };
+        // one 2 x 2 block: rows rotated by (csa, sna, sia), columns by (csb, snb, sib); returns the new (0,0), (0,1), (1,1)
+        auto block = [&](int pa, int qa, int pb, int qb, double csa, double sna, double sia, double csb, double snb, double sib,
+                         double& n00, double& n01, double& n01i, double& n11) {
+            const int i00 = pa * BJ_LDG + pb, i01 = pa * BJ_LDG + qb, i10 = qa * BJ_LDG + pb, i11 = qa * BJ_LDG + qb;
+            if (!CX) {
+                const double g00 = sG[i00], g01 = sG[i01], g10 = sG[i10], g11 = sG[i11];
+                const double h00 = csa * g00 - sna * g10, h01 = csa * g01 - sna * g11;
+                const double h10 = sna * g00 + csa * g10, h11 = sna * g01 + csa * g11;
+                n00 = csb * h00 - snb * h01;
+                n01 = snb * h00 + csb * h01;
+                const double n10 = csb * h10 - snb * h11;
+                n11 = snb * h10 + csb * h11;
+                n01i = 0.0;
+                sG[i00] = n00; sG[i01] = n01; sG[i10] = n10; sG[i11] = n11;
+            } else {
+                const double g00r = sG[i00], g01r = sG[i01], g10r = sG[i10], g11r = sG[i11];
+                const double g00i = sGi[i00], g01i = sGi[i01], g10i = sGi[i10], g11i = sGi[i11];
+                const double h00r = csa * g00r - (sna * g10r - sia * g10i), h00i = csa * g00i - (sna * g10i + sia * g10r);
+                const double h01r = csa * g01r - (sna * g11r - sia * g11i), h01i = csa * g01i - (sna * g11i + sia * g11r);
+                const double h10r = (sna * g00r + sia * g00i) + csa * g10r, h10i = (sna * g00i - sia * g00r) + csa * g10i;
+                const double h11r = (sna * g01r + sia * g01i) + csa * g11r, h11i = (sna * g01i - sia * g01r) + csa * g11i;
+                n00 = csb * h00r - (snb * h01r + sib * h01i);
+                const double n00i = csb * h00i - (snb * h01i - sib * h01r);
+                n01 = (snb * h00r - sib * h00i) + csb * h01r;
+                n01i = (snb * h00i + sib * h00r) + csb * h01i;
+                const double n10 = csb * h10r - (snb * h11r + sib * h11i), n10i = csb * h10i - (snb * h11i - sib * h11r);
+                n11 = (snb * h10r - sib * h10i) + csb * h11r;
+                const double n11i = (snb * h10i + sib * h10r) + csb * h11i;
+                sG[i00] = n00; sGi[i00] = n00i; sG[i01] = n01; sGi[i01] = n01i;
+                sG[i10] = n10; sGi[i10] = n10i; sG[i11] = n11; sGi[i11] = n11i;
+            }
+        };
+        if (wa == 0) {                      // rotations of step 0 straight from G
+            double cs, sn, si;
+            const int q0 = BJ_B + lb;
+            rotation(lb, q0, sG[lb * BJ_LDG + lb], sG[q0 * BJ_LDG + q0], sG[lb * BJ_LDG + q0], CX ? sGi[lb * BJ_LDG + q0] : 0.0, cs, sn, si);
+            s_cs[0][lb] = cs; s_sn[0][lb] = sn; s_si[0][lb] = si;
+        }
+        __syncthreads();
+        for (int step = 0; step < BJ_B; ++step) {
+            const int par = step & 1, np = par ^ 1;
+            const int pb = lb, qb = BJ_B + ((lb + step) & (BJ_B - 1));
+            const int pa = wa, qa = BJ_B + ((wa + step) & (BJ_B - 1));
+            const double cs = s_cs[par][lb], sn = s_sn[par][lb], si = CX ? s_si[par][lb] : 0.0;
+            double n00, n01, n01i, n11;
+            if (wa == 0) {
+                // the blocks (b, b) and (b, b + 1) first, then the rotations of the next step
+                const int l1 = (lb + 1) & (BJ_B - 1);
+                const int p1 = l1, q1 = BJ_B + ((l1 + step) & (BJ_B - 1));
+                const double cs1 = s_cs[par][l1], sn1 = s_sn[par][l1], si1 = CX ? s_si[par][l1] : 0.0;
+                double d00, dxx, dxi, d11;
+                block(pb, qb, pb, qb, cs, sn, si, cs, sn, si, d00, dxx, dxi, d11);          // (b, b): new diagonal of p_b, q_b
+                block(pb, qb, p1, q1, cs, sn, si, cs1, sn1, si1, n00, n01, n01i, n11);      // (b, b+1): n01 = new G[p_b][q_{b+1}]
+                const double be = __shfl_sync(0xffffffffu, d11, l1);                        // new G[q_{b+1}][q_{b+1}]
+                double c2, s2, i2;
+                rotation(pb, q1, d00, be, n01, n01i, c2, s2, i2);
+                s_cs[np][lb] = c2; s_sn[np][lb] = s2; s_si[np][lb] = i2;
+            }
+            const bool special = lb == wa || lb == ((wa + 1) & (BJ_B - 1));
+            if (!special) {
+                const double csa = s_cs[par][wa], sna = s_sn[par][wa], sia = CX ? s_si[par][wa] : 0.0;
+                block(pa, qa, pb, qb, csa, sna, sia, cs, sn, si, n00, n01, n01i, n11);
+            }
+            if (sn != 0.0 || si != 0.0) {
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int ip = pb * BJ_LDG + wa + h * BJ_B, iq = qb * BJ_LDG + wa + h * BJ_B;
+                    if (!CX) {
+                        const double x = sQ[ip], y = sQ[iq];
+                        sQ[ip] = cs * x - sn * y;
+                        sQ[iq] = sn * x + cs * y;
+                    } else {
+                        const double xr = sQ[ip], xi = sQi[ip], yr = sQ[iq], yi = sQi[iq];
+                        sQ[ip] = cs * xr - (sn * yr - si * yi);   sQi[ip] = cs * xi - (sn * yi + si * yr);
+                        sQ[iq] = (sn * xr + si * xi) + cs * yr;   sQi[iq] = (sn * xi - si * xr) + cs * yi;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+    } else
     for (int step = 0; step < nsteps; ++step) {
         if (tid < nrot) {
             int p, q;
