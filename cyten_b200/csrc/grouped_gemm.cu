@@ -46,6 +46,31 @@ __device__ __forceinline__ double neg_bits(double x)
     return __longlong_as_double(__double_as_longlong(x) ^ (long long)0x8000000000000000ull);
 }
 
+// One operand tile global -> shared.  Thread t copies chunk column cc = t % CC (a chunk = CD doubles: 16 or 8 bytes) of the
+// rows r_i = t / CC + i * (THREADS / CC): the same assignment as "chunk c = t + i * THREADS" when CC divides THREADS, but
+// cc, the first row and the validity of the column are computed once, and the source pointer advances by a constant.
+// `src` is the tile origin in global memory (row stride ld doubles), rows_valid / cols_valid (doubles) bound the block;
+// chunks outside are zero-filled (cp.async src-size 0 from a valid dummy address).
+template <int ROWS, int CC, int CD, int LDS, int THREADS>
+__device__ __forceinline__ void load_tile(double* __restrict__ dst, const double* __restrict__ src, int64_t ld,
+                                          int rows_valid, int cols_valid, const double* __restrict__ dummy, int tid)
+{
+    static_assert(THREADS % CC == 0 && ROWS % (THREADS / CC) == 0, "load_tile: chunk columns must divide the CTA");
+    constexpr int RS = THREADS / CC, IT = ROWS / RS;
+    const int cc = tid % CC, r0 = tid / CC;
+    const bool colok = cc * CD < cols_valid;
+    const double* p = src + (int64_t)r0 * ld + cc * CD;
+    double* d = dst + r0 * LDS + cc * CD;
+    const int64_t step = (int64_t)RS * ld;
+#pragma unroll
+    for (int i = 0; i < IT; ++i) {
+        const bool ok = colok && (r0 + i * RS < rows_valid);
+        if (CD == 2) cp_async_16(d + i * RS * LDS, ok ? p : dummy, ok);
+        else cp_async_8(d + i * RS * LDS, ok ? p : dummy, ok);
+        p += step;
+    }
+}
+
 struct GemmTables {
     const int64_t* out_mn;        // [nblocks][2]
     const int64_t* out_off;       // [nblocks]
@@ -257,6 +282,44 @@ __device__ __forceinline__ void compute_stage(const double* __restrict__ tA, con
     }
 }
 
+// Real sectors, contiguous warp tiles: all k-steps of one stage for a warp of which only the first MIE x NJE 8 x 8 groups lie
+// inside the block.  The counts are template arguments, so the ragged variants are as free of predicates as the full one
+// (the uniform `if (i >= mi_cnt) continue` of compute_stage<.., false> cost more than the DMMAs it saved); the warp picks
+// its variant with one uniform switch per pipeline stage.  At chi = 4096 this takes the executed / algorithmic DMMA ratio
+// of the 64 x 64 tiling from 1.11 to the 8-row granularity of the instruction.
+template <class Cfg, int MIE, int NJE>
+__device__ __forceinline__ void compute_stage_edge(const double* __restrict__ tA, const double* __restrict__ tB,
+                                                   double (&acc)[1][Cfg::MI][Cfg::NI][2], int wm, int wn, int lr, int lc)
+{
+    constexpr int BK = Cfg::BK, LDA = Cfg::LDA, LDB = Cfg::LDB, MI = Cfg::MI, NI = Cfg::NI;
+    static_assert(!Cfg::cplx && !Cfg::IL, "compute_stage_edge: real sectors, contiguous warp tiles");
+#pragma unroll
+    for (int kk = 0; kk < BK; kk += 4) {
+        double a[MIE], b[NJE];
+#pragma unroll
+        for (int i = 0; i < MIE; ++i) a[i] = tA[(size_t)((wm * MI + i) * 8 + lr) * LDA + kk + lc];
+#pragma unroll
+        for (int j = 0; j < NJE; ++j) b[j] = tB[(size_t)(kk + lc) * LDB + (wn * NI + j) * 8 + lr];
+#pragma unroll
+        for (int i = 0; i < MIE; ++i)
+#pragma unroll
+            for (int j = 0; j < NJE; ++j) dmma884(acc[0][i][j][0], acc[0][i][j][1], a[i], b[j]);
+    }
+}
+
+template <class Cfg, int MIE>
+__device__ __forceinline__ void compute_stage_edge_n(const double* __restrict__ tA, const double* __restrict__ tB,
+                                                     double (&acc)[1][Cfg::MI][Cfg::NI][2], int wm, int wn, int lr, int lc, int nj)
+{
+    static_assert(Cfg::NI == 4, "compute_stage_edge_n: four column groups per warp");
+    switch (nj) {
+    case 1: compute_stage_edge<Cfg, MIE, 1>(tA, tB, acc, wm, wn, lr, lc); break;
+    case 2: compute_stage_edge<Cfg, MIE, 2>(tA, tB, acc, wm, wn, lr, lc); break;
+    case 3: compute_stage_edge<Cfg, MIE, 3>(tA, tB, acc, wm, wn, lr, lc); break;
+    default: compute_stage_edge<Cfg, MIE, 4>(tA, tB, acc, wm, wn, lr, lc); break;
+    }
+}
+
 template <class Cfg>
 __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MINB)
 grouped_gemm_kernel(const double* __restrict__ A, const double* __restrict__ B, double* __restrict__ C,
@@ -309,6 +372,9 @@ grouped_gemm_kernel(const double* __restrict__ A, const double* __restrict__ B, 
         const bool full_tile = (mi_cnt == MI) && (nj_cnt == NI);
         // WSKIP: rows [wm WM, +WM) x columns [wn WN, +WN) of the tile against the block edge
         const bool warp_live = !Cfg::WSKIP || ((int64_t)wm * Cfg::WM < M - m0 && (int64_t)wn * Cfg::WN < N - n0);
+        // WSKIP: 8 x 8 groups of this warp inside the block (contiguous warp tiles)
+        const int rem_m = (int)min((int64_t)BM, M - m0) - wm * Cfg::WM, rem_n = (int)min((int64_t)BN, N - n0) - wn * Cfg::WN;
+        const int mi_eff = rem_m <= 0 ? 0 : min(MI, (rem_m + 7) >> 3), nj_eff = rem_n <= 0 ? 0 : min(NI, (rem_n + 7) >> 3);
         int64_t n_iters = 0;
         for (int64_t p = p_begin; p < p_end; ++p) n_iters += (T.pairs[3 * p + 2] + BK - 1) / BK;
 
@@ -325,46 +391,23 @@ grouped_gemm_kernel(const double* __restrict__ A, const double* __restrict__ B, 
                 const int64_t K = ld_K, k0 = ld_k;
                 const double* gA = A + (ld_aoff + m0 * K + k0) * ES;   // element (m0, k0)
                 const double* gB = B + (ld_boff + k0 * N + n0) * ES;   // element (k0, n0)
+                // per-thread invariants (chunk column, first row) are hoisted by load_tile: ~7 instructions per copy
+                // instead of a divide / modulo / 64-bit multiply per chunk (the loader used to be 80 % of the
+                // instructions of a pipeline stage and kept the DMMA pipe at 73 %)
+                const int rows_a = (int)min((int64_t)BM, M - m0), rows_b = (int)min((int64_t)BK, K - k0);
+                const int cols_a = (int)min((int64_t)BK, K - k0) * ES, cols_b = (int)min((int64_t)BN, N - n0) * ES;
+#ifndef CYB_GEMM_NOLOAD   /* experiment: ceiling of the consumer side (results are garbage) */
                 if (CPLX) {
                     // one complex element = 16 bytes, always aligned
-                    for (int c = tid; c < BM * BK; c += THREADS) {
-                        const int r = c / BK, k = c % BK;
-                        const bool ok = (m0 + r < M) && (k0 + k < K);
-                        cp_async_16(dA + ((size_t)r * LDA + k) * 2, ok ? gA + ((int64_t)r * K + k) * 2 : A, ok);
-                    }
-                    for (int c = tid; c < BK * BN; c += THREADS) {
-                        const int k = c / BN, n = c % BN;
-                        const bool ok = (k0 + k < K) && (n0 + n < N);
-                        cp_async_16(dB + ((size_t)k * LDB + n) * 2, ok ? gB + ((int64_t)k * N + n) * 2 : B, ok);
-                    }
+                    load_tile<BM, BK, 2, LDA * 2, THREADS>(dA, gA, K * 2, rows_a, cols_a, A, tid);
+                    load_tile<BK, BN, 2, LDB * 2, THREADS>(dB, gB, N * 2, rows_b, cols_b, B, tid);
                 } else {
-                    if ((K & 1) == 0) {
-                        for (int c = tid; c < BM * (BK / 2); c += THREADS) {
-                            const int r = c / (BK / 2), k = (c % (BK / 2)) * 2;
-                            const bool ok = (m0 + r < M) && (k0 + k < K);
-                            cp_async_16(dA + (size_t)r * LDA + k, ok ? gA + (int64_t)r * K + k : A, ok);
-                        }
-                    } else {
-                        for (int c = tid; c < BM * BK; c += THREADS) {
-                            const int r = c / BK, k = c % BK;
-                            const bool ok = (m0 + r < M) && (k0 + k < K);
-                            cp_async_8(dA + (size_t)r * LDA + k, ok ? gA + (int64_t)r * K + k : A, ok);
-                        }
-                    }
-                    if (vecB) {
-                        for (int c = tid; c < BK * (BN / 2); c += THREADS) {
-                            const int k = c / (BN / 2), n = (c % (BN / 2)) * 2;
-                            const bool ok = (k0 + k < K) && (n0 + n < N);
-                            cp_async_16(dB + (size_t)k * LDB + n, ok ? gB + (int64_t)k * N + n : B, ok);
-                        }
-                    } else {
-                        for (int c = tid; c < BK * BN; c += THREADS) {
-                            const int k = c / BN, n = c % BN;
-                            const bool ok = (k0 + k < K) && (n0 + n < N);
-                            cp_async_8(dB + (size_t)k * LDB + n, ok ? gB + (int64_t)k * N + n : B, ok);
-                        }
-                    }
+                    if ((K & 1) == 0) load_tile<BM, BK / 2, 2, LDA, THREADS>(dA, gA, K, rows_a, cols_a, A, tid);
+                    else load_tile<BM, BK, 1, LDA, THREADS>(dA, gA, K, rows_a, cols_a, A, tid);
+                    if (vecB) load_tile<BK, BN / 2, 2, LDB, THREADS>(dB, gB, N, rows_b, cols_b, B, tid);
+                    else load_tile<BK, BN, 1, LDB, THREADS>(dB, gB, N, rows_b, cols_b, B, tid);
                 }
+#endif
                 ld_k += BK;
                 if (ld_k >= K) {
                     ++ld_p; ld_k = 0;
@@ -386,17 +429,26 @@ grouped_gemm_kernel(const double* __restrict__ A, const double* __restrict__ B, 
 #pragma unroll
         for (int s = 0; s < STAGES - 1; ++s) issue_load(s);
 
-        for (int64_t it = 0; it < n_iters; ++it) {
+        int stage = 0, stage_ld = STAGES - 1;     // rolling stage indices (no 64-bit modulo in the loop)
+        for (int64_t it = 0; it < n_iters; ++it, stage = stage + 1 == STAGES ? 0 : stage + 1) {
             cp_async_wait<STAGES - 2>();
             __syncthreads();
-            issue_load((int)((it + STAGES - 1) % STAGES));
-            const int stage = (int)(it % STAGES);
+            issue_load(stage_ld);
+            stage_ld = stage_ld + 1 == STAGES ? 0 : stage_ld + 1;
             const double* tA = sA + (size_t)stage * Cfg::A_STAGE;
             const double* tB = sB + (size_t)stage * Cfg::B_STAGE;
             // the full / ragged decision is hoisted out of the unrolled k-steps: one basic block per stage,
             // so the fragment loads of the next k-step are scheduled between the DMMAs of the current one
-            if (Cfg::WSKIP) {
-                if (warp_live) compute_stage<Cfg, true>(tA, tB, acc, wm, wn, lr, lc, mi_cnt, nj_cnt);
+            if constexpr (Cfg::WSKIP) {
+                if (mi_eff == MI && nj_eff == NI) compute_stage<Cfg, true>(tA, tB, acc, wm, wn, lr, lc, mi_cnt, nj_cnt);
+                else if (warp_live) {
+                    switch (mi_eff) {
+                    case 1: compute_stage_edge_n<Cfg, 1>(tA, tB, acc, wm, wn, lr, lc, nj_eff); break;
+                    case 2: compute_stage_edge_n<Cfg, 2>(tA, tB, acc, wm, wn, lr, lc, nj_eff); break;
+                    case 3: compute_stage_edge_n<Cfg, 3>(tA, tB, acc, wm, wn, lr, lc, nj_eff); break;
+                    default: compute_stage_edge_n<Cfg, 4>(tA, tB, acc, wm, wn, lr, lc, nj_eff); break;
+                    }
+                }
             } else if (full_tile) compute_stage<Cfg, true>(tA, tB, acc, wm, wn, lr, lc, mi_cnt, nj_cnt);
             else compute_stage<Cfg, false>(tA, tB, acc, wm, wn, lr, lc, mi_cnt, nj_cnt);
         }
