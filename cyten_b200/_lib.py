@@ -47,6 +47,7 @@ SIGNATURES = {
     "cyb_batched_eigh": (_int, [_vp, _vp, _vp, _vp, _i64, _int, _vp, _vp]),
     "cyb_fill_eye": (_int, [_vp, _vp, _vp, _i64, _int, _vp]),
     "cyb_truncate_select": (_int, [_vp, _i64, _i64, _i64, _dbl, _dbl, _dbl, _int, _vp, _vp, _vp]),
+    "cyb_truncate_select_static": (_int, [_vp, _i64, _i64, _i64, _dbl, _dbl, _dbl, _int, _vp, _vp, _vp]),
     "cyb_sumsq": (_int, [_vp, _i64, _int, _vp, _vp]),
     "cyb_axpby": (_int, [_vp, _vp, _i64, _int, _dbl, _dbl, _vp]),
     "cyb_cutoff_inverse": (_int, [_vp, _vp, _i64, _dbl, _vp]),

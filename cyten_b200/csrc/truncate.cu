@@ -9,6 +9,7 @@
 // admissible cut is ignored, like combine_constraints in the reference.
 #include "common.cuh"
 #include <math_constants.h>
+#include <mutex>
 
 namespace cyb {
 
@@ -238,6 +239,34 @@ __global__ void gather_rows_cols_kernel(const double* __restrict__ src, double* 
     }
 }
 
+// ---- scratch of cyb_truncate_select_static: no allocation at call time -------------------------------------------
+// Same layout as the cudaMallocAsync scratch of cyb_truncate_select, sized for TR_STATIC_MAX_N values; every GPU that
+// loads the library holds these TR_STATIC_BYTES (2.1 MiB) until the process exits.
+constexpr int64_t TR_STATIC_MAX_N = 65536;          // == CYB_TRUNCATE_STATIC_MAX_N in include/cyten_b200.h
+constexpr size_t tr_align256(size_t x) { return (x + 255) / 256 * 256; }
+constexpr size_t TR_STATIC_BYTES = tr_align256(8 * (size_t)TR_STATIC_MAX_N) * 4 + tr_align256((size_t)TR_STATIC_MAX_N) * 2 + 256;
+static __device__ __align__(256) unsigned char tr_static_scratch[TR_STATIC_BYTES];
+
+// In host code `tr_static_scratch` is only a stand-in for the symbol, not a device address: the address a kernel may use
+// comes from cudaGetSymbolAddress, asked once per device with that device current.
+static int tr_static_address(unsigned char** out)
+{
+    static std::mutex mu;
+    static unsigned char* addr[64] = {};
+    int dev = 0;
+    CYB_CHECK_CUDA(cudaGetDevice(&dev));
+    CYB_REQUIRE(dev >= 0 && dev < 64, "truncate_select_static: device index %d outside [0, 64)", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        unsigned char* p = nullptr;
+        CYB_CHECK_CUDA(cudaGetSymbolAddress((void**)&p, tr_static_scratch));
+        CYB_REQUIRE(p != nullptr, "truncate_select_static: cudaGetSymbolAddress returned a null address");
+        addr[dev] = p;
+    }
+    *out = addr[dev];
+    return CYB_OK;
+}
+
 }  // namespace cyb
 
 using namespace cyb;
@@ -266,6 +295,42 @@ int cyb_truncate_select(const double* s, int64_t n, int64_t chi_max, int64_t chi
     P.good = ws.as<uint8_t>(o); o += align_up(N, 256);
     P.good2 = ws.as<uint8_t>(o); o += align_up(N, 256);
     P.flag = ws.as<int64_t>(o);
+    truncate_rank_kernel<<<(unsigned)((n + TR_RANK_THREADS - 1) / TR_RANK_THREADS), TR_RANK_THREADS, 0, stream>>>(P);
+    truncate_select_kernel<<<1, TR_THREADS, 0, stream>>>(P);
+    CYB_LAUNCH_CHECK();
+    return CYB_OK;
+}
+
+int cyb_truncate_select_static(const double* s, int64_t n, int64_t chi_max, int64_t chi_min,
+                               double degeneracy_tol, double trunc_cut, double svd_min,
+                               int minimize_error, uint8_t* keep, double* result, cyb_stream_t stream_)
+{
+    CYB_REQUIRE(n >= 1, "truncate_select_static: need at least one singular value");
+    if (n > TR_STATIC_MAX_N) {
+        set_error("truncate_select_static: n = %lld exceeds the static scratch (CYB_TRUNCATE_STATIC_MAX_N = %lld values); "
+                  "use cyb_truncate_select", (long long)n, (long long)TR_STATIC_MAX_N);
+        return CYB_ERR_LIMIT;
+    }
+    CYB_REQUIRE(s != nullptr && keep != nullptr && result != nullptr, "truncate_select_static: s / keep / result must not be null");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    unsigned char* base = nullptr;
+    const int rc = tr_static_address(&base);
+    if (rc != CYB_OK) return rc;
+    const size_t N = (size_t)n;
+    TruncArgs P;
+    P.s = s; P.n = n; P.chi_max = chi_max; P.chi_min = chi_min; P.degeneracy_tol = degeneracy_tol;
+    P.trunc_cut = trunc_cut; P.svd_min = svd_min; P.minimize_error = minimize_error;
+    P.keep = keep; P.result = result;
+    // The kernels write every scratch slot they later read (ranks are a permutation of 0 .. n-1), so nothing has to start
+    // at zero and the previous call's contents are harmless.  Two calls that overlap on the GPU (different streams) race.
+    size_t o = 0;
+    P.piv = reinterpret_cast<int64_t*>(base + o); o += tr_align256(8 * N);
+    P.merr = reinterpret_cast<double*>(base + o); o += tr_align256(8 * N);
+    P.ssort = reinterpret_cast<double*>(base + o); o += tr_align256(8 * N);
+    P.csum = reinterpret_cast<double*>(base + o); o += tr_align256(8 * N);
+    P.good = reinterpret_cast<uint8_t*>(base + o); o += tr_align256(N);
+    P.good2 = reinterpret_cast<uint8_t*>(base + o); o += tr_align256(N);
+    P.flag = reinterpret_cast<int64_t*>(base + o);
     truncate_rank_kernel<<<(unsigned)((n + TR_RANK_THREADS - 1) / TR_RANK_THREADS), TR_RANK_THREADS, 0, stream>>>(P);
     truncate_select_kernel<<<1, TR_THREADS, 0, stream>>>(P);
     CYB_LAUNCH_CHECK();

@@ -208,6 +208,19 @@ int cyb_truncate_select(const double* s, int64_t n, int64_t chi_max, int64_t chi
                         double degeneracy_tol, double trunc_cut, double svd_min,
                         int minimize_error, uint8_t* keep, double* result, cyb_stream_t stream);
 
+/* cyb_truncate_select without any allocation at call time (no cudaMalloc / cudaMallocAsync / cudaFree): the scratch is a
+ * file-scope static __device__ array of the library, sized for CYB_TRUNCATE_STATIC_MAX_N values (2.1 MiB, held by every GPU
+ * that loads the library until the process exits).  For callers that cannot allocate: code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc.  Same arguments and results as cyb_truncate_select;
+ * n > CYB_TRUNCATE_STATIC_MAX_N is rejected with CYB_ERR_LIMIT.  All calls share the one array (it keeps the last call's
+ * contents, none of which is read before it is rewritten): calls that overlap on the GPU -- different streams, or
+ * different host threads without ordering -- race and must be serialised by the caller.
+ * This entry point has no counterpart in the reference. */
+#define CYB_TRUNCATE_STATIC_MAX_N 65536
+int cyb_truncate_select_static(const double* s, int64_t n, int64_t chi_max, int64_t chi_min,
+                               double degeneracy_tol, double trunc_cut, double svd_min,
+                               int minimize_error, uint8_t* keep, double* result, cyb_stream_t stream);
+
 /* ---- (f1) block-batched BLAS-1 used between the hot ops ---------------------------------- */
 /* out[0] = sum |x|^2 over `n` elements (norm squared; abelian.cpp:2780-2791). */
 int cyb_sumsq(const void* x, int64_t n, int dtype, double* out, cyb_stream_t stream);

@@ -445,6 +445,14 @@ def cyb_truncate_select(s, n, chi_max, chi_min, degeneracy_tol, trunc_cut, svd_m
     return 0
 
 
+def cyb_truncate_select_static(s, n, chi_max, chi_min, degeneracy_tol, trunc_cut, svd_min, minimize_error,
+                               keep, result, stream=None):
+    """The no-allocation variant has the same results; its size limit is CYB_TRUNCATE_STATIC_MAX_N of include/cyten_b200.h."""
+    if n > 65536:
+        return 3          # CYB_ERR_LIMIT
+    return cyb_truncate_select(s, n, chi_max, chi_min, degeneracy_tol, trunc_cut, svd_min, minimize_error, keep, result, stream)
+
+
 # ---- BLAS-1 helpers ---------------------------------------------------------------------------------------------
 def cyb_sumsq(x, n, dtype, out, stream=None):
     v = _arr(x, n, _dt(dtype))
