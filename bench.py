@@ -426,18 +426,44 @@ def run_b200(args):
     # rank-local until vR is contracted, then one all_reduce of the (small) result arena
     theta = SH.shard(theta_full) if world > 1 else theta_full
 
+    # N > 1, fused operator, CYB_OVERLAP=1: the last GEMM runs in column groups of the result and each group's all_reduce is
+    # issued as soon as the group is queued (cyten_b200.sharding.OverlappedMatvec).  Measured SLOWER on 2 B200 (1.24 vs
+    # 1.11 ms, profiles/r2/scale/r2t_*): the persistent GEMM CTAs fill every SM (4 x 56 KB of shared memory), so NCCL's
+    # CTAs only become resident when the GEMM drains and the second launch costs more than the collective it was to hide.
+    # Default: whole chain, then one all_reduce.
+    overlap = world > 1 and fused and os.environ.get("CYB_OVERLAP", "0") == "1"
+    overlap_fractions = tuple(float(x) for x in os.environ.get("CYB_OVERLAP_FRACTIONS", "0.6,0.4").split(","))
+    overlapped = {}
+
+    def ov_of(t):
+        if id(t) not in overlapped:
+            overlapped[id(t)] = sh.OverlappedMatvec(SH, t, fractions=overlap_fractions)
+        return overlapped[id(t)]
+
     def eager(t):
+        if overlap:
+            return ov_of(t)(t)
         return SH.matvec(t) if world > 1 else H.matvec(t)
 
     def local_chain(t):      # the part of a step without a collective: what a CUDA graph captures
         return SH.matvec_local(t) if world > 1 else H.matvec(t)
     captured = {}
 
+    def capture(t):
+        if overlap:
+            from cyten_b200.graphs import CapturedPipeline
+            ov = ov_of(t)
+            return CapturedPipeline([lambda x, g=g: ov.part(g, x) for g in range(ov.num_parts)], t, warmup=2)
+        from cyten_b200.graphs import CapturedStep
+        return CapturedStep(local_chain, t, warmup=2)
+
     def step(t=None):
         t = theta if t is None else t
         cap = captured.get(id(t))
         if cap is None:
             return eager(t)
+        if overlap:
+            return ov_of(t)(t, run_part=cap.replay)
         y = cap()
         if world > 1:
             pg.all_reduce(y.data.buf)
@@ -473,8 +499,7 @@ def run_b200(args):
     # the plan-cached chain is pure kernel launches: capture it once into a CUDA graph and replay it
     use_graph = not args.no_graph
     if use_graph:
-        from cyten_b200.graphs import CapturedStep
-        captured[id(theta)] = CapturedStep(local_chain, theta, warmup=2)
+        captured[id(theta)] = capture(theta)
         for _ in range(2):
             y = step()
 
@@ -510,6 +535,18 @@ def run_b200(args):
     ms_per_step = total_ms / args.steps
     value = flops / (ms_per_step * 1e-3) / 1e9
 
+    # ---- N > 1: the WHOLE reduced result against the unsharded operator on this GPU (outside every timed region) ----
+    sharded_check = None
+    if world > 1:
+        y_sh = step()
+        y_un = sh.expand_to_full(H.matvec(theta_full))
+        same_blocks = bool(np.array_equal(y_sh.data.block_inds, y_un.data.block_inds))
+        scale = float(y_un.data.buf.abs().max())
+        diff = float((y_sh.data.buf - y_un.data.buf).abs().max()) if same_blocks else float("inf")
+        worst = total_over_ranks(diff / scale if scale > 0 else diff, dist.ReduceOp.MAX)
+        sharded_check = {"max_abs_diff_over_max_abs": worst, "tolerance": 1e-12, "ok": bool(same_blocks and worst <= 1e-12),
+                         "what": "graph-replayed sharded step (all ranks reduced) vs the unsharded fused operator, every element"}
+
     # ---- the same step with the plan cache disabled (bookkeeping recomputed on device every call) ----
     be.plan_cache = False
     eager(theta)
@@ -533,7 +570,7 @@ def run_b200(args):
     thetas = [theta, SymmetricTensor(d2, theta.codomain, theta.domain, be, theta.labels)]
 
     if use_graph:
-        captured[id(thetas[1])] = CapturedStep(local_chain, thetas[1], warmup=2)   # one graph per theta arena
+        captured[id(thetas[1])] = capture(thetas[1])   # one graph (or pipeline of graphs) per theta arena
     stepk = step
     y = stepk(thetas[1])
     nres = y.data.buf.numel()
@@ -706,14 +743,18 @@ def run_b200(args):
                                           "launches_per_replay": (captured[id(theta)].launches_per_replay if use_graph else None)},
                            "plan_cache": {"enabled": True, "hits": be.plan_hits, "misses": be.plan_misses,
                                           "ms_per_step_without": noplan_ms, "ms_first_call": first_call_ms},
-                           "sharding": ("theta sharded along vR sectors (LPT), rank-local chain, one all_reduce per matvec"
+                           "sharding": (("theta sharded along vR (sectors and index ranges, LPT by flops), rank-local chain; last GEMM in "
+                                         f"{len(overlap_fractions)} column groups {overlap_fractions}, each group's all_reduce behind the next group's GEMM")
+                                        if overlap else
+                                        "theta sharded along vR sectors (LPT), rank-local chain, one all_reduce per matvec"
                                         if world > 1 else "single GPU")},
                 "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "ms_per_step": e2e_s * 1e3, "ms_per_step_serial": e2e_serial_s * 1e3, "steps": pipe_steps,
                         "mode": "3-stream pipeline (upload | matvec | download), two theta arenas; bytes are per rank",
                         "host_checksum": e2e_check},
                 "gpu_launches": launches, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu,
-                "e2e_plugin": plugin_info, "sweep": sweep_info, "svd_ms": svd_ms, "svd": svd_info, "lanczos": lanczos_info}
+                "e2e_plugin": plugin_info, "sweep": sweep_info, "svd_ms": svd_ms, "svd": svd_info, "lanczos": lanczos_info,
+                "sharded_check": sharded_check}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

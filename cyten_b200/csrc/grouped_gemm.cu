@@ -815,8 +815,18 @@ __global__ void __launch_bounds__(SK_THREADS, 3) skinny_gemm_kernel(const double
 // float64: 64 x 64 tiles, 4 warps, four CTAs per SM (22.8 TFLOP/s on the chi = 4096 H_eff GEMMs; the 128 x 128 /
 // one-CTA-per-SM layout of the first version reached 18.5, and 13 further tile / pipeline variants measured within
 // -2 ... -20 % of this one -- profiles/r1b, profiles/r1c)
-using CfgR0 = GemmCfg<false, 64, 64, 16, 2, 2, 3, false, false, false, 4>;
-using CfgR = GemmCfg<false, 64, 64, 16, 2, 2, 3, false, false, false, 4, true>;     // + warp-tile edge skipping
+// (tuning aid: -DCYB_GEMM_BM= ... builds another real tiling -- 4 x 4 groups per warp: BM = 32 WARPS_M, BN = 32 WARPS_N)
+#ifndef CYB_GEMM_BM
+#define CYB_GEMM_BM 64
+#define CYB_GEMM_BN 64
+#define CYB_GEMM_BK 16
+#define CYB_GEMM_STAGES 3
+#define CYB_GEMM_MINB 4
+#endif
+#define CYB_GEMM_R CYB_GEMM_BM, CYB_GEMM_BN, CYB_GEMM_BK, CYB_GEMM_BM / 32, CYB_GEMM_BN / 32, CYB_GEMM_STAGES
+#define CYB_GEMM_R_MINB CYB_GEMM_MINB
+using CfgR0 = GemmCfg<false, CYB_GEMM_R, false, false, false, CYB_GEMM_R_MINB>;
+using CfgR = GemmCfg<false, CYB_GEMM_R, false, false, false, CYB_GEMM_R_MINB, true>;     // + warp-tile edge skipping
 using CfgC = GemmCfg<true, 128, 64, 8, 4, 2, 4>;      // 8 warps, 4 x 4 interleaved groups per warp, complex
 
 template <class Cfg>

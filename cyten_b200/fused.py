@@ -150,10 +150,17 @@ class FusedHEffective:
                          ptr(plan["work0"]), plan["ngroups"], plan["nwork"], plan["max_rows"], Y.cyb_dtype, be._stream())
         return SymmetricTensor(Y, plan["y_cod"], plan["y_dom"], be, plan["y_labels"])
 
-    def matvec(self, theta: SymmetricTensor) -> SymmetricTensor:
-        H = self.H
+    def prefix(self, theta: SymmetricTensor) -> SymmetricTensor:
+        """Everything before ``vR`` is contracted: ``LP . theta`` and the fused middle pass -> x'[vL, p0, p1 | vR, wR]."""
         x = ct.permute_legs(theta, ["vL"], ["vR", "p1", "p0"])
-        x = ct.compose(H.LP, x)                                     # vL wL* p0 p1 vR
-        x = self.middle(x)                                          # vL p0 p1 wR vR
-        x = ct.compose(x, H.RP)                                     # vL p0 p1 vR
+        x = ct.compose(self.H.LP, x)                                # vL wL* p0 p1 vR
+        return self.middle(x)                                       # vL p0 p1 wR vR
+
+    def suffix(self, x: SymmetricTensor, RP=None) -> SymmetricTensor:
+        """``x' . RP`` (``RP``: the right environment or a subset of its blocks -- the multi-GPU path runs this GEMM in
+        groups of output sectors so that each group's all_reduce hides behind the next group's GEMM)."""
+        x = ct.compose(x, self.H.RP if RP is None else RP)          # vL p0 p1 vR
         return ct.permute_legs(x, domain=["vR", "p1"])
+
+    def matvec(self, theta: SymmetricTensor) -> SymmetricTensor:
+        return self.suffix(self.prefix(theta))

@@ -54,3 +54,47 @@ class CapturedStep:
         self.graph.replay()
         self.backend.launches += self.launches_per_replay
         return self.output
+
+
+class CapturedPipeline:
+    """``parts[g](input)`` (side effects into static arenas, e.g. ``OverlappedMatvec.part``) captured as ONE GRAPH PER PART
+    in a shared memory pool, so the caller can issue work that cannot live in the graphs -- the NCCL all_reduce of part
+    g's range -- between the replays.  Later parts may read tensors an earlier part produced (same pool, kept alive by
+    the producer's references; the replays run in order on one stream)."""
+
+    def __init__(self, parts, input_tensor, warmup: int = 2):
+        be = input_tensor.backend
+        if be.device.type != "cuda":
+            raise RuntimeError("CapturedPipeline needs a CUDA backend")
+        self.input, self.backend = input_tensor, be
+        input_tensor.data.buf
+        for _ in range(max(1, warmup)):
+            for fn in parts:
+                fn(input_tensor)
+        torch.cuda.synchronize(be.device)
+        input_tensor.data._relayout = None          # see CapturedStep: the static input's re-layout is a graph node
+        misses = be.plan_misses
+        saved = (be.gemm_events, be.plan_mkn)
+        be.gemm_events, be.plan_mkn = None, None
+        self.graphs, self.launches = [], []
+        pool = None
+        try:
+            with torch.cuda.device(be.device):
+                for fn in parts:
+                    g = torch.cuda.CUDAGraph()
+                    n0 = be.launches
+                    with torch.cuda.graph(g, pool=pool):
+                        fn(input_tensor)
+                    pool = g.pool() if pool is None else pool
+                    self.graphs.append(g)
+                    self.launches.append(be.launches - n0)
+        finally:
+            be.gemm_events, be.plan_mkn = saved
+        if be.plan_misses != misses:
+            raise RuntimeError("a plan was built during graph capture: run more warm-up calls first")
+        self.launches_per_replay = sum(self.launches)
+        input_tensor.data._relayout = None
+
+    def replay(self, g: int):
+        self.graphs[g].replay()
+        self.backend.launches += self.launches[g]

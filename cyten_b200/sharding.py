@@ -69,6 +69,13 @@ class ProcessGroup:
             dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
         return t
 
+    def all_reduce_async(self, t: torch.Tensor):
+        """Starts the all_reduce behind the work already queued on the current stream and returns a handle whose
+        ``wait()`` orders the current stream after it; kernels launched in between run beside the collective."""
+        if self.world > 1:
+            return dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        return None
+
     def all_gather_into(self, out: torch.Tensor, t: torch.Tensor):
         if self.world > 1:
             dist.all_gather_into_tensor(out, t, group=self.group)
@@ -422,6 +429,140 @@ class ShardedHEffective:
         if not full.backend.dry_run:
             self.pg.all_reduce(full.data.buf)
         return full
+
+
+class OverlappedMatvec:
+    """``ShardedHEffective.matvec`` with the all_reduce hidden behind the last GEMM.
+
+    The result's ``vR`` leg comes from the open leg of RP.  Its sectors are cut into K contiguous groups; RP restricted
+    to a group gives exactly the result blocks of that group, and because ``vR`` is the primary key of the block order
+    those blocks are ONE contiguous range of the shared all-blocks arena.  A step is
+
+        part 0:   x' = prefix(theta_r)   (LP . theta, fused middle pass -- once)      y_0 = x' . RP_0 -> range 0 of Y
+        part g:                                                                         y_g = x' . RP_g -> range g of Y
+
+    with ``all_reduce(Y[range g])`` started as soon as part g is queued: the collective of group g runs beside the GEMM
+    of group g + 1 (NCCL's own stream), only the last group's all_reduce is exposed -- so the groups get decreasing
+    shares of the arena (``fractions``).  No flop is duplicated (the groups partition the output blocks of the last
+    GEMM) and the result equals ``ShardedHEffective.matvec`` up to the summation order of the all_reduce.
+    ``Y`` is static (one per OverlappedMatvec): the parts are captured as one CUDA graph each (cyten_b200.graphs.
+    CapturedPipeline) and the collectives are issued between the replays."""
+
+    def __init__(self, SH: "ShardedHEffective", theta_local: SymmetricTensor, fractions=(0.6, 0.4)):
+        if not SH.fused:
+            raise ValueError("OverlappedMatvec needs the fused rank-local chain (ShardedHEffective(fused=True))")
+        self.SH, self.pg = SH, SH.pg
+        be = self.be = theta_local.backend
+        self.chain = SH.chains[0][0] if SH.chains else None            # FusedHEffective over (LP, RP_r, W1, W2)
+        # ---- the shared layout of the result: structure only (plan-only pass), identical on every rank ----
+        was = be.dry_run
+        be.dry_run = True
+        try:
+            if self.chain is not None:
+                like = self.chain.matvec(theta_local)
+            else:
+                like = SH.H.matvec(take_blocks(getattr(SH, "_empty_like", theta_local), np.zeros(0, np.int64)))
+        finally:
+            be.dry_run = was
+        self.codomain, self.domain, self.labels = like.codomain, like.domain, list(like.labels)
+        legs = conventional_leg_order(like.codomain, like.domain)
+        ax = like.get_leg_idcs(["vR"])[0]
+        if ax != len(legs) - 1:
+            raise ValueError("OverlappedMatvec: vR must be the last leg (the primary key of the block order)")
+        full_bi = valid_block_inds(like.codomain, like.domain)
+        shapes = np.stack([np.asarray(l.multiplicities)[full_bi[:, a]] for a, l in enumerate(legs)], axis=1)
+        self.Y = be._empty(like.data.dtype, be.device, full_bi, shapes, zero=True)
+        nsec = np.asarray([l.num_sectors for l in legs], dtype=np.int64)
+        self._strides = np.concatenate([[1], np.cumprod(nsec[:-1])]).astype(np.int64)      # last column primary
+        self._key_full = full_bi @ self._strides
+        # ---- K contiguous groups of vR sectors holding about `fractions` of the arena ----
+        sizes = np.prod(shapes, axis=1).astype(np.float64)
+        per_sec = np.bincount(full_bi[:, ax], weights=sizes, minlength=int(nsec[ax]))
+        cum = np.cumsum(per_sec) / max(per_sec.sum(), 1.0)
+        cuts, acc = [0], 0.0
+        for f in fractions[:-1]:
+            acc += f
+            c = int(np.searchsorted(cum, acc - 1e-12)) + 1
+            cuts.append(min(max(c, cuts[-1] + 1), int(nsec[ax])))
+        cuts.append(int(nsec[ax]))
+        cuts = sorted(set(cuts))
+        self.sector_groups = [(cuts[i], cuts[i + 1]) for i in range(len(cuts) - 1)]
+        total = self.Y.buf.numel() if not be.dry_run else int(self.Y.offsets[-1] + sizes[-1]) if len(sizes) else 0
+        self.block_ranges, self.ranges = [], []
+        for s0, s1 in self.sector_groups:
+            b0, b1 = int(np.searchsorted(full_bi[:, ax], s0)), int(np.searchsorted(full_bi[:, ax], s1))
+            self.block_ranges.append((b0, b1))
+            self.ranges.append((int(self.Y.offsets[b0]) if b0 < len(full_bi) else total,
+                                int(self.Y.offsets[b1]) if b1 < len(full_bi) else total))
+        # ---- RP restricted to each group (its open leg is its last leg) ----
+        self.RP = []
+        if self.chain is not None:
+            RP = self.chain.H.RP
+            col = RP.data.block_inds[:, RP.num_legs - 1]
+            for s0, s1 in self.sector_groups:
+                self.RP.append(take_blocks(RP, np.nonzero((col >= s0) & (col < s1))[0]))
+        self._xp = None
+        self.result = SymmetricTensor(self.Y, self.codomain, self.domain, be, self.labels)
+
+    @property
+    def num_parts(self):
+        return len(self.sector_groups)
+
+    def _expand_into(self, y: SymmetricTensor, g: int):
+        be, Y, d = self.be, self.Y, y.data
+        a, b = self.ranges[g]
+        key = ("expand_into", d.sig, Y.sig, g, a, b)
+        plan = be._plan_get(key)
+        if plan is None:
+            prepared = (0, None)
+            if d.num_blocks:
+                keys = d.block_inds @ self._strides
+                pos = np.searchsorted(self._key_full, keys)
+                if not np.array_equal(self._key_full[pos], keys):
+                    raise ValueError("OverlappedMatvec: a part has blocks that violate the charge rule")
+                b0, b1 = self.block_ranges[g]
+                if pos.min() < b0 or pos.max() >= b1:
+                    raise ValueError("OverlappedMatvec: a part wrote outside its range of the arena")
+                sizes = d.sizes.reshape(-1, 1)
+                ones = np.ones_like(sizes)
+                prepared = be._prepare_copy(be._make_jobs(d.offsets, Y.offsets[pos], sizes, ones, ones))
+            plan = dict(copy=prepared, complete=d.num_blocks == self.block_ranges[g][1] - self.block_ranges[g][0])
+            if not be.dry_run:
+                be._plan_put(key, plan)
+        if be.dry_run:
+            return
+        if not plan["complete"] and b > a:          # the previous step's all_reduce left sums in the absent blocks
+            Y.buf[a:b].zero_()
+        be._run_copy(d.buf, Y.buf, plan["copy"], d.cyb_dtype)
+
+    def part(self, g: int, theta_local: SymmetricTensor):
+        """Queues part g of a step (kernel launches only once the plans are cached: capturable)."""
+        a, b = self.ranges[g]
+        if self.chain is None:                      # a rank without work contributes zeros
+            if not self.be.dry_run and b > a:
+                self.Y.buf[a:b].zero_()
+            return
+        if g == 0:
+            self._xp = self.chain.prefix(theta_local)
+        self._expand_into(self.chain.suffix(self._xp, self.RP[g]), g)
+
+    def reduce_async(self, g: int):
+        a, b = self.ranges[g]
+        return self.pg.all_reduce_async(self.Y.buf[a:b]) if b > a and not self.be.dry_run else None
+
+    def __call__(self, theta_local: SymmetricTensor, run_part=None) -> SymmetricTensor:
+        """One step; ``run_part(g)`` replaces the eager part g (a graph replay)."""
+        works = []
+        for g in range(self.num_parts):
+            if run_part is None:
+                self.part(g, theta_local)
+            else:
+                run_part(g)
+            works.append(self.reduce_async(g))
+        for w in works:
+            if w is not None:
+                w.wait()
+        return self.result
 
 
 def svd_costs(tens: SymmetricTensor) -> np.ndarray:

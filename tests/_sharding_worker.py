@@ -89,6 +89,41 @@ def worker(rank, world, port, out_dir, mode="gloo", chi=64):
         nsplit = sum(1 for r in SC.ranges for s, (a, b) in r.items() if (a, b) != (0, int(theta.domain.factors[0].multiplicities[s])))
         assert nsplit >= 2, "the test must exercise a sector that is cut into ranges"
 
+        # ---- all_reduce hidden behind the last GEMM: column groups of the result, one collective per group ----
+        SO = sh.ShardedHEffective(H, pg, split_columns=True, column_align=2 if chi <= 64 else 16, column_heavy=0.25, fused=True)
+        th_o = SO.shard(theta)
+        from cyten_b200.fused import FusedHEffective
+        HF = FusedHEffective(H)
+        HF.matvec(theta)                                   # (the first call also plans the unfused middle: not counted)
+        be.plan_mkn = []
+        HF.matvec(theta)
+        fl_fused = float(sum(be.plan_mkn))                 # the two fat GEMMs of the fused operator, unsharded
+        be.plan_mkn = None
+        for fractions in ((0.6, 0.4), (0.5, 0.3, 0.2)):
+            OV = sh.OverlappedMatvec(SO, th_o, fractions=fractions)
+            assert OV.num_parts == len(fractions) and OV.ranges[0][0] == 0
+            assert all(OV.ranges[g][1] == OV.ranges[g + 1][0] for g in range(OV.num_parts - 1))      # a partition of the arena
+            OV(th_o)
+            be.plan_mkn = []
+            got_o = OV(th_o)
+            fl = tt([float(sum(be.plan_mkn))], dtype=torch.float64)
+            be.plan_mkn = None
+            dist.all_reduce(fl)
+            assert float(fl.item()) == fl_fused, ("the grouped last GEMM must not duplicate flops", float(fl.item()), fl_fused, fl_full, fractions)
+            for rep in range(2):                  # the static arena is reused: a second step must not see the first one's sums
+                if rep:
+                    got_o = OV(th_o)
+                assert np.array_equal(got_o.data.block_inds, full_want.data.block_inds)
+                d_o = _dense_of(got_o)
+                assert np.allclose(d_o, d_want, rtol=0, atol=1e-12 * np.abs(d_want).max()), (fractions, rep)
+        if mode == "nccl":                        # the same step as one CUDA graph per part, collectives between the replays
+            from cyten_b200.graphs import CapturedPipeline
+            cap = CapturedPipeline([lambda t, g=g: OV.part(g, t) for g in range(OV.num_parts)], th_o)
+            for rep in range(2):
+                d_g = _dense_of(OV(th_o, run_part=cap.replay))
+                assert np.allclose(d_g, d_want, rtol=0, atol=1e-12 * np.abs(d_want).max()), ("graphs", rep)
+            res["overlap_graph_launches"] = cap.launches
+
         # ---- the Krylov loop on top of the sharded matvec: same iterations, same Ritz value as single process ----
         from types import SimpleNamespace
         from cyten_b200.krylov import lanczos
