@@ -92,6 +92,17 @@ __device__ __forceinline__ void bj_cp16(void* smem, const void* g, bool pred)
 __device__ __forceinline__ void bj_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
 template <int N> __device__ __forceinline__ void bj_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
 
+// Programmatic dependent launch (CYB_BJ_PDL=1; off by default, see factorize.cu): the three kernels of a round are then
+// launched with cudaLaunchAttributeProgrammaticStreamSerialization, so the CTAs of kernel N + 1 are scheduled (parameters
+// fetched, prologue run) while kernel N still works; this wait returns once kernel N has completed and its writes are
+// visible.  The trigger comes AFTER the wait: at most two kernels of a stream are in flight, and completion stays
+// transitive (N + 1 cannot complete before N has).  Without the launch attribute both instructions are no-ops.
+__device__ __forceinline__ void bj_pdl_enter()
+{
+    asm volatile("griddepcontrol.wait;\n" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
+}
+
 __device__ __forceinline__ void bj_dmma(double& c0, double& c1, double a, double b)
 {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
@@ -224,6 +235,7 @@ bj_gram_kernel(const double* __restrict__ ws, const FzDesc* __restrict__ descs, 
                double* __restrict__ gpart)
 {
     extern __shared__ __align__(16) double bj_smem[];
+    bj_pdl_enter();
     double* sT = bj_smem;                    // two tiles [64][36]
     __shared__ int s_rows[BJ_R];
     const BjWork wk = works[blockIdx.x];
@@ -309,6 +321,7 @@ bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ it
                  const double* __restrict__ gpart, double* __restrict__ qbuf, int* __restrict__ skip)
 {
     extern __shared__ __align__(16) double bj_smem[];
+    bj_pdl_enter();
     constexpr int CM = CX ? 2 : 1;
     constexpr int PL = BJ_R * BJ_LDG;        // one [64][65] plane
     double* sG = bj_smem;                    // Re G
@@ -377,6 +390,9 @@ bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ it
     const int nrot = cross ? BJ_B : BJ_B / 2;
     __syncthreads();
     if (cross) {
+        // (What bounds a step, profiles/r2/svd_groups_r2f.txt: not the FP64 pipe -- tools/dfma_probe.cu measures 61 lane-FMA /
+        //  clk / SM, and computing only the upper triangle of G changed nothing -- but the shared-memory pipe, which serves
+        //  the ~1000 warp-wide 8-byte requests of a step in order, with warp 0's dependent loads queued among them.)
         // Block pairs (every round but the first of a sweep): ONE barrier per step, rotations computed once.
         // Rotation b of step s pairs row p_b = b with row q_b = 32 + (b + s) % 32.  Thread (warp a, lane b) owns the
         // 2 x 2 block G[{p_a, q_a}][{p_b, q_b}] and columns a, a + 32 of the two rows of Q that rotation b mixes.  The
@@ -394,10 +410,16 @@ bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ it
                 if (al >= FZ_TINY && be >= FZ_TINY && !(al <= fl && be <= fl) && g2 > tol2 * al * be) {
                     const double rg = CX ? rsqrt(g2) : 0.0;
                     const double gabs = CX ? g2 * rg : fabs(gr);
+                    // with h = sqrt(d^2 + g^2), g = 2 |gamma|:  cos^2 = (h + |d|) / (2 h),  sin = sign(d) g / (2 h cos) -- the
+                    // same rotation as t = sign(d) g / (|d| + h), cos = 1 / sqrt(1 + t^2), with two rsqrt in series
+                    // (75 cycles each) instead of sqrt + divide + rsqrt (100 + 80 + 75) on the chain of a step
                     const double d = be - al, g2x = 2.0 * gabs;
-                    const double t = (d >= 0.0 ? g2x : -g2x) / (fabs(d) + sqrt(d * d + g2x * g2x));
-                    cs = rsqrt(1.0 + t * t);
-                    const double s0 = cs * t;
+                    const double rh = rsqrt(d * d + g2x * g2x);
+                    const double c2 = 0.5 + 0.5 * (fabs(d) * rh);
+                    const double rc = rsqrt(c2);
+                    cs = c2 * rc;
+                    double s0 = (0.5 * g2x) * rh * rc;
+                    if (d < 0.0) s0 = -s0;
                     if (CX) { sn = s0 * gr * rg; si = s0 * gi * rg; }
                     else sn = gr >= 0.0 ? s0 : -s0;
                 }
@@ -435,6 +457,17 @@ bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ it
                 sG[i10] = n10; sGi[i10] = n10i; sG[i11] = n11; sGi[i11] = n11i;
             }
         };
+        // Real sectors: Q lives in registers during the pass (shared-memory bandwidth bounds a step: 128 B / clk / SM against
+        // 64 KB of G and, before, 64 KB of Q read and written per step; chi = 4096: 46.3 -> 42.2 us per launch).  Complex
+        // sectors keep Q in shared memory: with 1024 threads the kernel has 64 registers per thread and the four extra
+        // doubles spill.
+        constexpr bool REGQ = !CX;
+        double qp_r[2], qq_r[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            qp_r[h] = (wa + h * BJ_B == lb) ? 1.0 : 0.0;
+            qq_r[h] = (wa + h * BJ_B == BJ_B + lb) ? 1.0 : 0.0;
+        }
         if (wa == 0) {                      // rotations of step 0 straight from G
             double cs, sn, si;
             const int q0 = BJ_B + lb;
@@ -466,20 +499,31 @@ bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ it
                 const double csa = s_cs[par][wa], sna = s_sn[par][wa], sia = CX ? s_si[par][wa] : 0.0;
                 block(pa, qa, pb, qb, csa, sna, sia, cs, sn, si, n00, n01, n01i, n11);
             }
-            if (sn != 0.0 || si != 0.0) {
+            if (REGQ) {
+                // Q <- J Q in registers: rows p_b and q_b, columns wa and wa + 32; the p row stays with the lane, the q row
+                // of the next step (q_b(s + 1) = q_{b+1}(s)) comes from lane b + 1
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const double x = qp_r[h], y = qq_r[h];
+                    qp_r[h] = cs * x - sn * y;
+                    qq_r[h] = __shfl_sync(0xffffffffu, sn * x + cs * y, (lb + 1) & (BJ_B - 1));
+                }
+            } else if (sn != 0.0 || si != 0.0) {
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                     const int ip = pb * BJ_LDG + wa + h * BJ_B, iq = qb * BJ_LDG + wa + h * BJ_B;
-                    if (!CX) {
-                        const double x = sQ[ip], y = sQ[iq];
-                        sQ[ip] = cs * x - sn * y;
-                        sQ[iq] = sn * x + cs * y;
-                    } else {
-                        const double xr = sQ[ip], xi = sQi[ip], yr = sQ[iq], yi = sQi[iq];
-                        sQ[ip] = cs * xr - (sn * yr - si * yi);   sQi[ip] = cs * xi - (sn * yi + si * yr);
-                        sQ[iq] = (sn * xr + si * xi) + cs * yr;   sQi[iq] = (sn * xi - si * xr) + cs * yi;
-                    }
+                    const double xr = sQ[ip], xi = sQi[ip], yr = sQ[iq], yi = sQi[iq];
+                    sQ[ip] = cs * xr - (sn * yr - si * yi);   sQi[ip] = cs * xi - (sn * yi + si * yr);
+                    sQ[iq] = (sn * xr + si * xi) + cs * yr;   sQi[iq] = (sn * xi - si * xr) + cs * yi;
                 }
+            }
+            __syncthreads();
+        }
+        if (REGQ) {                         // after 32 shifts the q row of lane b is row 32 + b again
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                sQ[lb * BJ_LDG + wa + h * BJ_B] = qp_r[h];
+                sQ[(BJ_B + lb) * BJ_LDG + wa + h * BJ_B] = qq_r[h];
             }
             __syncthreads();
         }
@@ -584,6 +628,7 @@ bj_apply_kernel(double* __restrict__ ws, const FzDesc* __restrict__ descs, const
                 const int* __restrict__ skip)
 {
     extern __shared__ __align__(16) double bj_smem[];
+    bj_pdl_enter();
     constexpr int CM = CX ? 2 : 1;
     double* sQ = bj_smem;                              // Re Q [64][68]
     double* sQi = bj_smem + BJ_SQ;                     // Im Q (complex sectors only)

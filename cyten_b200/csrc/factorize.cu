@@ -392,6 +392,26 @@ jacobi_svd_kernel(const void* __restrict__ a_, void* __restrict__ o0_, double* _
 
 }  // namespace cyb
 #include "block_jacobi.cuh"
+
+namespace cyb {
+// launch with (or without) programmatic stream serialization; the kernels call bj_pdl_enter() first thing either way
+template <class... KArgs, class... Args>
+static cudaError_t bj_launch(bool pdl, void (*kernel)(KArgs...), unsigned grid, unsigned block, size_t smem, cudaStream_t stream, Args... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid, 1, 1);
+    cfg.blockDim = dim3(block, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+}  // namespace cyb
+
 #include "qr_blocked.cuh"
 namespace cyb {
 
@@ -889,6 +909,11 @@ static int run_block_jacobi(const void* a, void* o0, double* s_out, void* o2, vo
     constexpr int MAXG = 4;
     int NG = 4;
     if (const char* e = getenv("CYB_BJ_GROUPS")) NG = atoi(e);
+    // programmatic dependent launch of the round kernels (bj_pdl_enter), CYB_BJ_PDL=1.  Measured (profiles/r2/svd_groups_r2f.txt):
+    // chi = 4096 SVD 58.8 -> 62.1 ms (the early-resident CTAs of the next kernel take shared memory from the other groups'
+    // kernels), eigh 22.75 -> 22.19 ms, complex chi = 1024 25.8 -> 25.2 / 13.7 -> 13.1 ms: off by default.
+    bool pdl = false;
+    if (const char* e = getenv("CYB_BJ_PDL")) pdl = atoi(e) != 0;
     NG = std::max(1, std::min(std::min(NG, MAXG), nbig));
     std::vector<int> group_of((size_t)nbig, 0);
     if (NG >= 2) {
@@ -1007,12 +1032,18 @@ static int run_block_jacobi(const void* a, void* o0, double* s_out, void* o2, vo
                     if (!live) continue;
                     const unsigned ni = (unsigned)R[g].rounds[rd].size();
                     const unsigned ng = (unsigned)(R[g].gstart[rd + 1] - R[g].gstart[rd]), na = (unsigned)(R[g].astart[rd + 1] - R[g].astart[rd]);
-                    bj_gram_kernel<CX><<<ng, BJ_THREADS, BJ_SMEM_GRAM, gstream[g]>>>(
-                        static_cast<const double*>(d_ws), d_desc, d_items[g] + R[g].start[rd], d_gworks[g] + R[g].gstart[rd], d_active, d_rowmap, d_gpart[g]);
-                    bj_rotate_kernel<CX><<<ni, BJ_RT, SMEM_ROT, gstream[g]>>>(
-                        d_desc, d_items[g] + R[g].start[rd], d_active, d_flags, d_floor2, phase1 ? 1 : 0, d_gpart[g], d_qbuf[g], d_skip[g]);
-                    bj_apply_kernel<CX><<<na, BJ_THREADS, SMEM_APPLY, gstream[g]>>>(
-                        static_cast<double*>(d_ws), d_desc, d_items[g] + R[g].start[rd], d_aworks[g] + R[g].astart[rd], d_rowmap, d_qbuf[g], d_skip[g]);
+                    cudaError_t le = bj_launch(pdl, bj_gram_kernel<CX>, ng, BJ_THREADS, BJ_SMEM_GRAM, gstream[g],
+                        static_cast<const double*>(d_ws), (const FzDesc*)d_desc, (const BjItem*)(d_items[g] + R[g].start[rd]),
+                        (const BjWork*)(d_gworks[g] + R[g].gstart[rd]), (const int*)d_active, (const int*)d_rowmap, d_gpart[g]);
+                    if (le == cudaSuccess)
+                        le = bj_launch(pdl, bj_rotate_kernel<CX>, ni, BJ_RT, SMEM_ROT, gstream[g],
+                            (const FzDesc*)d_desc, (const BjItem*)(d_items[g] + R[g].start[rd]), (const int*)d_active, d_flags,
+                            (const double*)d_floor2, phase1 ? 1 : 0, (const double*)d_gpart[g], d_qbuf[g], d_skip[g]);
+                    if (le == cudaSuccess)
+                        le = bj_launch(pdl, bj_apply_kernel<CX>, na, BJ_THREADS, SMEM_APPLY, gstream[g],
+                            static_cast<double*>(d_ws), (const FzDesc*)d_desc, (const BjItem*)(d_items[g] + R[g].start[rd]),
+                            (const BjWork*)(d_aworks[g] + R[g].astart[rd]), (const int*)d_rowmap, (const double*)d_qbuf[g], (const int*)d_skip[g]);
+                    if (le != cudaSuccess) { set_error("block jacobi: round launch failed: %s", cudaGetErrorString(le)); return CYB_ERR_CUDA; }
                 }
             }
             CYB_LAUNCH_CHECK();
