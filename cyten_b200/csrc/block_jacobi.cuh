@@ -47,7 +47,8 @@ constexpr size_t BJ_SMEM = sizeof(double) * (size_t)(BJ_SQ + BJ_SBUF);
 #endif
 constexpr int BJ_KS = CYB_BJ_KS;         // columns per partial Gram matrix
 constexpr int BJ_AC = CYB_BJ_AC;         // columns per apply work unit
-constexpr size_t BJ_SMEM_GRAM = sizeof(double) * (size_t)(2 * BJ_R * BJ_LDT);
+constexpr int BJ_GST = BJ_KS / BJ_BK;        // k-chunks of a Gram slice: all of them are in flight at once
+constexpr size_t BJ_SMEM_GRAM = sizeof(double) * (size_t)(BJ_GST * BJ_R * BJ_LDT);
 constexpr size_t BJ_SMEM_ROT = sizeof(double) * (size_t)(2 * BJ_R * BJ_LDG);
 constexpr size_t BJ_SMEM_APPLY = sizeof(double) * (size_t)(BJ_SQ + BJ_SBUF_B);
 constexpr size_t BJ_SMEM_ROT_CX = 2 * BJ_SMEM_ROT;                                            // + Im G, Im Q
@@ -91,6 +92,17 @@ __device__ __forceinline__ void bj_cp16(void* smem, const void* g, bool pred)
 }
 __device__ __forceinline__ void bj_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
 template <int N> __device__ __forceinline__ void bj_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+// at most n (0 .. 3) of the most recently committed groups still pending; n folds to a constant in unrolled loops
+__device__ __forceinline__ void bj_wait_pending(int n)
+{
+    switch (n) {
+    case 3: bj_wait<3>(); break;
+    case 2: bj_wait<2>(); break;
+    case 1: bj_wait<1>(); break;
+    default: bj_wait<0>(); break;
+    }
+}
+static_assert(CYB_BJ_KS / 32 >= 1 && CYB_BJ_KS / 32 <= 4, "bj_gram_kernel keeps every 32-column chunk of a slice in flight (at most 4)");
 
 // Programmatic dependent launch (CYB_BJ_PDL=1; off by default, see factorize.cu): the three kernels of a round are then
 // launched with cudaLaunchAttributeProgrammaticStreamSerialization, so the CTAs of kernel N + 1 are scheduled (parameters
@@ -147,7 +159,7 @@ __device__ __forceinline__ void bj_load_tile(double* tile, const double* __restr
 // per step, in place
 template <bool CX>
 __device__ __forceinline__ void bj_apply(const double* sQ, const double* sQi, double* sBuf, double* __restrict__ base, int64_t ld,
-                                         int64_t ncols, const int* s_rows, int64_t cbeg, int64_t cend)
+                                         int64_t ncols, const int* s_rows, int64_t cbeg, int64_t cend, bool preloaded = false)
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int lr = lane >> 2, lc = lane & 3;
@@ -155,8 +167,10 @@ __device__ __forceinline__ void bj_apply(const double* sQ, const double* sQi, do
     const bool vec = (ld & 1) == 0 && (ncols & 1) == 0;
     if (cend > ncols) cend = ncols;
     const int64_t nchunks = (cend - cbeg + BJ_BN - 1) / BJ_BN;
-    bj_load_tile<BJ_BN, BJ_LDB>(sBuf, base, ld, cend, cbeg, s_rows, vec);
-    bj_commit();
+    if (!preloaded) {                        // (the caller may have requested the first tile already: bj_apply_kernel)
+        bj_load_tile<BJ_BN, BJ_LDB>(sBuf, base, ld, cend, cbeg, s_rows, vec);
+        bj_commit();
+    }
     for (int64_t ch = 0; ch < nchunks; ++ch) {
         double* cur = sBuf + (ch & 1) * (BJ_R * BJ_LDB);
         if (ch + 1 < nchunks) bj_load_tile<BJ_BN, BJ_LDB>(sBuf + ((ch + 1) & 1) * (BJ_R * BJ_LDB), base, ld, cend, cbeg + (ch + 1) * BJ_BN, s_rows, vec);
@@ -236,7 +250,7 @@ bj_gram_kernel(const double* __restrict__ ws, const FzDesc* __restrict__ descs, 
 {
     extern __shared__ __align__(16) double bj_smem[];
     bj_pdl_enter();
-    double* sT = bj_smem;                    // two tiles [64][36]
+    double* sT = bj_smem;                    // BJ_GST tiles [64][36]
     __shared__ int s_rows[BJ_R];
     const BjWork wk = works[blockIdx.x];
     const BjItem it = items[wk.item];
@@ -264,13 +278,17 @@ bj_gram_kernel(const double* __restrict__ ws, const FzDesc* __restrict__ descs, 
 #pragma unroll
         for (int j = 0; j < 2; ++j) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
     const int64_t nk = (k_end - k_beg + BJ_BK - 1) / BJ_BK;
-    bj_load_tile<BJ_BK, BJ_LDT>(sT, W, c, k_end, k_beg, s_rows, vec);
-    bj_commit();
-    for (int64_t kc = 0; kc < nk; ++kc) {
-        const double* cur = sT + (kc & 1) * (BJ_R * BJ_LDT);
-        if (kc + 1 < nk) bj_load_tile<BJ_BK, BJ_LDT>(sT + ((kc + 1) & 1) * (BJ_R * BJ_LDT), W, c, k_end, k_beg + (kc + 1) * BJ_BK, s_rows, vec);
+    // the whole slice (<= BJ_GST chunks of 32 columns) is requested up front: one L2 round trip instead of one per chunk
+#pragma unroll
+    for (int kc = 0; kc < BJ_GST; ++kc) {
+        if (kc < nk) bj_load_tile<BJ_BK, BJ_LDT>(sT + kc * (BJ_R * BJ_LDT), W, c, k_end, k_beg + kc * BJ_BK, s_rows, vec);
         bj_commit();
-        bj_wait<1>();
+    }
+#pragma unroll
+    for (int kc = 0; kc < BJ_GST; ++kc) {
+        if (kc >= nk) break;
+        const double* cur = sT + kc * (BJ_R * BJ_LDT);
+        bj_wait_pending(BJ_GST - 1 - kc);    // chunks 0 .. kc have landed (the groups complete in order)
         __syncthreads();
 #pragma unroll
         for (int kk = 0; kk < BJ_BK; kk += 4) {
@@ -297,7 +315,6 @@ bj_gram_kernel(const double* __restrict__ ws, const FzDesc* __restrict__ descs, 
                     for (int j = 0; j < 2; ++j) bj_dmma(acci[CX ? i : 0][j][0], acci[CX ? i : 0][j][1], a[i], bs[j]);
             }
         }
-        __syncthreads();
     }
     bj_wait<0>();
     double* out = gpart + (size_t)blockIdx.x * (BJ_R * BJ_R * CM);
@@ -340,8 +357,19 @@ bj_rotate_kernel(const FzDesc* __restrict__ descs, const BjItem* __restrict__ it
     // G = sum of the partials, in slice order
     for (int e = tid; e < BJ_R * BJ_R; e += BJ_RT) {
         double g = 0.0, gi = 0.0;
-        // fixed summation order; four partials are in flight at a time (one L2 round trip instead of four)
+        // fixed summation order; eight (then four) partials are in flight at a time (one L2 round trip instead of one each)
         int w = 0;
+        for (; w + 7 < it.nw; w += 8) {      // real sectors of the chi = 4096 configuration: nw = 8 (974 columns / 128)
+            const double* part = gpart + (size_t)(it.w0 + w) * (BJ_R * BJ_R * CM);
+            double a[8], b[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                a[k] = __ldcg(part + (size_t)k * (BJ_R * BJ_R * CM) + e);
+                if (CX) b[k] = __ldcg(part + (size_t)k * (BJ_R * BJ_R * CM) + BJ_R * BJ_R + e);
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { g += a[k]; if (CX) gi += b[k]; }
+        }
         for (; w + 3 < it.nw; w += 4) {
             const double* part = gpart + (size_t)(it.w0 + w) * (BJ_R * BJ_R * CM);
             const double a0 = __ldcg(part + e), a1 = __ldcg(part + (size_t)(BJ_R * BJ_R * CM) + e);
@@ -638,24 +666,40 @@ bj_apply_kernel(double* __restrict__ ws, const FzDesc* __restrict__ descs, const
     if (skip[wk.item]) return;
     const BjItem it = items[wk.item];
     bj_fill_rows(s_rows, it, rowmap);
+    // Q (32 KB, L2) and the first tile of the rows are requested together: Q into registers, then -- as soon as the row
+    // table is visible -- the tile with cp.async, and only then Q goes to shared memory (two round trips used to be serial)
     const double* q = qbuf + (size_t)wk.item * (BJ_R * BJ_R * CM);
-    for (int e = threadIdx.x; e < BJ_R * BJ_R / 2; e += BJ_THREADS) {
-        const int row = (2 * e) / BJ_R, col = (2 * e) % BJ_R;
-        const double2 v = __ldcg(reinterpret_cast<const double2*>(q) + e);
-        sQ[row * BJ_LDQ + col] = v.x;
-        sQ[row * BJ_LDQ + col + 1] = v.y;
-        if (CX) {
-            const double2 vi = __ldcg(reinterpret_cast<const double2*>(q + BJ_R * BJ_R) + e);
-            sQi[row * BJ_LDQ + col] = vi.x;
-            sQi[row * BJ_LDQ + col + 1] = vi.y;
-        }
+    constexpr int QV = BJ_R * BJ_R / 2 / BJ_THREADS;       // double2 per thread
+    double2 qv[QV], qvi[CX ? QV : 1];
+#pragma unroll
+    for (int k = 0; k < QV; ++k) {
+        qv[k] = __ldcg(reinterpret_cast<const double2*>(q) + threadIdx.x + k * BJ_THREADS);
+        if (CX) qvi[k] = __ldcg(reinterpret_cast<const double2*>(q + BJ_R * BJ_R) + threadIdx.x + k * BJ_THREADS);
     }
-    __syncthreads();
     const FzDesc D = descs[it.mat];
     const int which = wk.arg >> 24;
     const int64_t cbeg = (int64_t)(wk.arg & 0xffffff) * BJ_AC;
-    if (which == 0) bj_apply<CX>(sQ, sQi, sBuf, ws + D.w_off * CM, D.c * CM, D.c * CM, s_rows, cbeg, cbeg + BJ_AC);
-    else bj_apply<CX>(sQ, sQi, sBuf, ws + D.z_off * CM, D.r * CM, D.r * CM, s_rows, cbeg, cbeg + BJ_AC);
+    double* base = ws + (which == 0 ? D.w_off : D.z_off) * CM;
+    const int64_t ld = (which == 0 ? D.c : D.r) * CM;
+    __syncthreads();                                       // s_rows
+    {
+        const int64_t cend = cbeg + BJ_AC < ld ? cbeg + BJ_AC : ld;
+        bj_load_tile<BJ_BN, BJ_LDB>(sBuf, base, ld, cend, cbeg, s_rows, (ld & 1) == 0);
+        bj_commit();
+    }
+#pragma unroll
+    for (int k = 0; k < QV; ++k) {
+        const int e = threadIdx.x + k * BJ_THREADS;
+        const int row = (2 * e) / BJ_R, col = (2 * e) % BJ_R;
+        sQ[row * BJ_LDQ + col] = qv[k].x;
+        sQ[row * BJ_LDQ + col + 1] = qv[k].y;
+        if (CX) {
+            sQi[row * BJ_LDQ + col] = qvi[k].x;
+            sQi[row * BJ_LDQ + col + 1] = qvi[k].y;
+        }
+    }
+    __syncthreads();
+    bj_apply<CX>(sQ, sQi, sBuf, base, ld, ld, s_rows, cbeg, cbeg + BJ_AC, true);
 }
 
 // squared row norms of the working copies: one warp per row, grid-stride over (matrix, row)
