@@ -305,22 +305,21 @@ static int b1_grid(K kernel, size_t smem, int64_t nchunk)
     return (int)std::max<int64_t>(1, std::min<int64_t>(want, cap));
 }
 
-// dynamic shared memory above 48 KB is opt-in per kernel; done once per process
+// dynamic shared memory above 48 KB is opt-in per kernel and per DEVICE
 static cudaError_t b1_attr()
 {
-    static cudaError_t done = [] {
-        cudaError_t e = cudaSuccess;
-        auto set = [&](const void* f) {
-            if (e == cudaSuccess) e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)B1_SMEM_MAX);
-        };
-        set((const void*)block_dot_kernel<true>); set((const void*)block_dot_kernel<false>);
-        set((const void*)block_lincomb_kernel<true, true>); set((const void*)block_lincomb_kernel<true, false>);
-        set((const void*)block_lincomb_kernel<false, true>); set((const void*)block_lincomb_kernel<false, false>);
-        set((const void*)scale_axis_kernel<true, true>); set((const void*)scale_axis_kernel<true, false>);
-        set((const void*)scale_axis_kernel<false, false>);
-        return e;
-    }();
-    return done;
+    static PerDeviceOnce configured;
+    if (!configured.first()) return cudaSuccess;
+    cudaError_t e = cudaSuccess;
+    auto set = [&](const void* f) {
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)B1_SMEM_MAX);
+    };
+    set((const void*)block_dot_kernel<true>); set((const void*)block_dot_kernel<false>);
+    set((const void*)block_lincomb_kernel<true, true>); set((const void*)block_lincomb_kernel<true, false>);
+    set((const void*)block_lincomb_kernel<false, true>); set((const void*)block_lincomb_kernel<false, false>);
+    set((const void*)scale_axis_kernel<true, true>); set((const void*)scale_axis_kernel<true, false>);
+    set((const void*)scale_axis_kernel<false, false>);
+    return e;
 }
 
 }  // namespace cyb
