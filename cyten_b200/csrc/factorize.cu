@@ -20,6 +20,7 @@
 //  Gauge: singular/eigen vectors are defined up to phases (and rotations in degenerate spaces), R's
 //  diagonal up to phases; parity with the reference is on S / W values, reconstruction and isometry.
 #include "common.cuh"
+#include <cstdio>
 #include <vector>
 #include <cmath>
 #include <algorithm>
@@ -1068,6 +1069,11 @@ static int run_block_jacobi(const void* a, void* o0, double* s_out, void* o2, vo
     if (rc != CYB_OK) return rc;
     bool failed = false;
     for (size_t m = 0; m < nmat; ++m) failed = failed || active[m];
+    const bool debug = getenv("CYB_BJ_DEBUG") != nullptr;          // sweeps per sector after each pass, on stderr
+    if (debug)
+        for (int64_t mat : big)
+            fprintf(stderr, "block jacobi: sector %lld (%lld x %lld) pass 1: %lld sweeps\n", (long long)mat,
+                    (long long)descs[(size_t)mat].r, (long long)descs[(size_t)mat].c, (long long)sweeps[(size_t)mat]);
     // ---- pass 2: orthogonalise the noise rows among themselves (trailing blocks of the sorted order) ----
     if (!failed) {
         for (int64_t mat : big) active[(size_t)mat] = 1;
@@ -1089,6 +1095,10 @@ static int run_block_jacobi(const void* a, void* o0, double* s_out, void* o2, vo
         }
         rc = run_sweeps(R2, false);
         if (rc != CYB_OK) return rc;
+        if (debug)
+            for (int64_t mat : big)
+                fprintf(stderr, "block jacobi: sector %lld pass 1 + 2: %lld sweeps, %d rows at the noise floor\n", (long long)mat,
+                        (long long)sweeps[(size_t)mat], nnoise[(size_t)mat]);
     }
     err = launch_team(jacobi_svd_kernel<CX, FZ_BIG_G, EIGH, PH_FINISH>, FZ_BIG_G, nbig, stream,
                       a, o0, s_out, o2, d_ws, d_aux, d_desc, sel_big, info);

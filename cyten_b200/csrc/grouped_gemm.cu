@@ -202,17 +202,12 @@ __global__ void __launch_bounds__(1024) gemm_schedule_kernel(const int64_t* __re
     }
 }
 
-// IL: a warp's 8x8 groups are interleaved over the tile (group = w + i * WARPS) instead of contiguous;
-// WMFAST: wm = warp % WARPS_M (else warp / WARPS_N);  SKIP: groups beyond the block edge issue no DMMA
-template <bool CPLX, int BM_, int BN_, int BK_, int WARPS_M_, int WARPS_N_, int STAGES_, bool IL_ = true,
-          bool WMFAST_ = true, bool SKIP_ = true, int MINB_ = 1, bool WSKIP_ = false>
+// Warp (wm, wn) owns the contiguous WM x WN sub-tile = MI x NI groups of 8 x 8; of a ragged tile it computes only the groups
+// that reach into the block (compute_stage_edge)
+template <bool CPLX, int BM_, int BN_, int BK_, int WARPS_M_, int WARPS_N_, int STAGES_, int MINB_ = 1>
 struct GemmCfg {
     static constexpr int MINB = MINB_;      // resident CTAs per SM (persistent grid = MINB x #SMs)
-    // WSKIP: a warp whose whole WM x WN sub-tile lies beyond the block edge issues no DMMA for that tile (one uniform
-    // branch per pipeline stage, no predicates inside the unrolled k-steps); needs contiguous warp tiles (IL = false)
-    static constexpr bool WSKIP = WSKIP_;
     static constexpr bool cplx = CPLX;
-    static constexpr bool IL = IL_, WMFAST = WMFAST_, SKIP = SKIP_;
     static constexpr int BM = BM_, BN = BN_, BK = BK_, WARPS_M = WARPS_M_, WARPS_N = WARPS_N_, STAGES = STAGES_;
     static constexpr int THREADS = WARPS_M * WARPS_N * 32;
     static constexpr int WM = BM / WARPS_M, WN = BN / WARPS_N;
@@ -230,48 +225,42 @@ struct GemmCfg {
     static_assert(CPLX ? (LDA % 8 == 4 && LDB % 8 == 2) : (LDA % 16 == 4 && LDB % 16 == 4), "padding");
 };
 
-// all k-steps of one pipeline stage; FULL: every group of the warp is inside the block
-template <class Cfg, bool FULL>
-__device__ __forceinline__ void compute_stage(const double* __restrict__ tA, const double* __restrict__ tB,
-                                              double (&acc)[Cfg::cplx ? 2 : 1][Cfg::MI][Cfg::NI][2], int wm, int wn,
-                                              int lr, int lc, int mi_cnt, int nj_cnt)
+// Contiguous warp tiles: all k-steps of one stage for a warp of which only the first MIE x NJE 8 x 8 groups lie
+// inside the block.  The counts are template arguments, so the ragged variants are as free of predicates as the full one
+// (uniform `if (i >= mi_cnt) continue` predicates inside the k-steps cost more than the DMMAs they saved); the warp picks
+// its variant with one uniform switch per pipeline stage.  At chi = 4096 this takes the executed / algorithmic DMMA ratio
+// of the 64 x 64 tiling from 1.11 to the 8-row granularity of the instruction.
+template <class Cfg, int MIE, int NJE>
+__device__ __forceinline__ void compute_stage_edge(const double* __restrict__ tA, const double* __restrict__ tB,
+                                                   double (&acc)[Cfg::cplx ? 2 : 1][Cfg::MI][Cfg::NI][2], int wm, int wn, int lr, int lc)
 {
     constexpr int BK = Cfg::BK, LDA = Cfg::LDA, LDB = Cfg::LDB, MI = Cfg::MI, NI = Cfg::NI;
     constexpr bool CPLX = Cfg::cplx;
-#define CYB_GM(i) (Cfg::IL ? (wm + (i) * Cfg::WARPS_M) : (wm * MI + (i)))
-#define CYB_GN(j) (Cfg::IL ? (wn + (j) * Cfg::WARPS_N) : (wn * NI + (j)))
 #pragma unroll
     for (int kk = 0; kk < BK; kk += 4) {
         if (!CPLX) {
-            double a[MI], b[NI];
+            double a[MIE], b[NJE];
 #pragma unroll
-            for (int i = 0; i < MI; ++i) a[i] = tA[(size_t)(CYB_GM(i) * 8 + lr) * LDA + kk + lc];
+            for (int i = 0; i < MIE; ++i) a[i] = tA[(size_t)((wm * MI + i) * 8 + lr) * LDA + kk + lc];
 #pragma unroll
-            for (int j = 0; j < NI; ++j) b[j] = tB[(size_t)(kk + lc) * LDB + CYB_GN(j) * 8 + lr];
+            for (int j = 0; j < NJE; ++j) b[j] = tB[(size_t)(kk + lc) * LDB + (wn * NI + j) * 8 + lr];
 #pragma unroll
-            for (int i = 0; i < MI; ++i) {
-                if (!FULL && i >= mi_cnt) continue;
+            for (int i = 0; i < MIE; ++i)
 #pragma unroll
-                for (int j = 0; j < NI; ++j) {
-                    if (!FULL && j >= nj_cnt) continue;
-                    dmma884(acc[0][i][j][0], acc[0][i][j][1], a[i], b[j]);
-                }
-            }
+                for (int j = 0; j < NJE; ++j) dmma884(acc[0][i][j][0], acc[0][i][j][1], a[i], b[j]);
         } else {
-            double2 a[MI], b[NI];
+            double2 a[MIE], b[NJE];
 #pragma unroll
-            for (int i = 0; i < MI; ++i)
-                a[i] = *reinterpret_cast<const double2*>(tA + ((size_t)(CYB_GM(i) * 8 + lr) * LDA + kk + lc) * 2);
+            for (int i = 0; i < MIE; ++i)
+                a[i] = *reinterpret_cast<const double2*>(tA + ((size_t)((wm * MI + i) * 8 + lr) * LDA + kk + lc) * 2);
 #pragma unroll
-            for (int j = 0; j < NI; ++j)
-                b[j] = *reinterpret_cast<const double2*>(tB + ((size_t)(kk + lc) * LDB + CYB_GN(j) * 8 + lr) * 2);
+            for (int j = 0; j < NJE; ++j)
+                b[j] = *reinterpret_cast<const double2*>(tB + ((size_t)(kk + lc) * LDB + (wn * NI + j) * 8 + lr) * 2);
 #pragma unroll
-            for (int i = 0; i < MI; ++i) {
-                if (!FULL && i >= mi_cnt) continue;
+            for (int i = 0; i < MIE; ++i) {
                 const double nai = neg_bits(a[i].y);
 #pragma unroll
-                for (int j = 0; j < NI; ++j) {
-                    if (!FULL && j >= nj_cnt) continue;
+                for (int j = 0; j < NJE; ++j) {
                     dmma884(acc[0][i][j][0], acc[0][i][j][1], a[i].x, b[j].x);
                     dmma884(acc[0][i][j][0], acc[0][i][j][1], nai, b[j].y);
                     dmma884(acc[CPLX ? 1 : 0][i][j][0], acc[CPLX ? 1 : 0][i][j][1], a[i].x, b[j].y);
@@ -282,37 +271,13 @@ __device__ __forceinline__ void compute_stage(const double* __restrict__ tA, con
     }
 }
 
-// Real sectors, contiguous warp tiles: all k-steps of one stage for a warp of which only the first MIE x NJE 8 x 8 groups lie
-// inside the block.  The counts are template arguments, so the ragged variants are as free of predicates as the full one
-// (the uniform `if (i >= mi_cnt) continue` of compute_stage<.., false> cost more than the DMMAs it saved); the warp picks
-// its variant with one uniform switch per pipeline stage.  At chi = 4096 this takes the executed / algorithmic DMMA ratio
-// of the 64 x 64 tiling from 1.11 to the 8-row granularity of the instruction.
-template <class Cfg, int MIE, int NJE>
-__device__ __forceinline__ void compute_stage_edge(const double* __restrict__ tA, const double* __restrict__ tB,
-                                                   double (&acc)[1][Cfg::MI][Cfg::NI][2], int wm, int wn, int lr, int lc)
-{
-    constexpr int BK = Cfg::BK, LDA = Cfg::LDA, LDB = Cfg::LDB, MI = Cfg::MI, NI = Cfg::NI;
-    static_assert(!Cfg::cplx && !Cfg::IL, "compute_stage_edge: real sectors, contiguous warp tiles");
-#pragma unroll
-    for (int kk = 0; kk < BK; kk += 4) {
-        double a[MIE], b[NJE];
-#pragma unroll
-        for (int i = 0; i < MIE; ++i) a[i] = tA[(size_t)((wm * MI + i) * 8 + lr) * LDA + kk + lc];
-#pragma unroll
-        for (int j = 0; j < NJE; ++j) b[j] = tB[(size_t)(kk + lc) * LDB + (wn * NI + j) * 8 + lr];
-#pragma unroll
-        for (int i = 0; i < MIE; ++i)
-#pragma unroll
-            for (int j = 0; j < NJE; ++j) dmma884(acc[0][i][j][0], acc[0][i][j][1], a[i], b[j]);
-    }
-}
-
 template <class Cfg, int MIE>
 __device__ __forceinline__ void compute_stage_edge_n(const double* __restrict__ tA, const double* __restrict__ tB,
-                                                     double (&acc)[1][Cfg::MI][Cfg::NI][2], int wm, int wn, int lr, int lc, int nj)
+                                                     double (&acc)[Cfg::cplx ? 2 : 1][Cfg::MI][Cfg::NI][2], int wm, int wn, int lr, int lc, int nj)
 {
-    static_assert(Cfg::NI == 4, "compute_stage_edge_n: four column groups per warp");
+    static_assert(Cfg::MI == 4 && Cfg::NI == 4, "compute_stage_edge_n: 4 x 4 groups per warp");
     switch (nj) {
+    case 0: break;
     case 1: compute_stage_edge<Cfg, MIE, 1>(tA, tB, acc, wm, wn, lr, lc); break;
     case 2: compute_stage_edge<Cfg, MIE, 2>(tA, tB, acc, wm, wn, lr, lc); break;
     case 3: compute_stage_edge<Cfg, MIE, 3>(tA, tB, acc, wm, wn, lr, lc); break;
@@ -335,13 +300,7 @@ grouped_gemm_kernel(const double* __restrict__ A, const double* __restrict__ B, 
     __shared__ long long s_tile;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    // Warp (wm, wn) owns the 8-row groups wm, wm + WARPS_M, ... and the 8-column groups wn, wn + WARPS_N, ...
-    // of the tile (interleaved), and skips the groups that lie beyond the block edge.  With wm = warp % 4
-    // the two warps of every SM sub-partition (warp % 4) have the same wm and different wn, so the DMMA
-    // work of a ragged tile stays balanced over the four tensor pipes.
-    const int wm = Cfg::WMFAST ? warp % Cfg::WARPS_M : warp / Cfg::WARPS_N;
-    const int wn = Cfg::WMFAST ? warp / Cfg::WARPS_M : warp % Cfg::WARPS_N;
-    // 8x8 groups CYB_GM(i) / CYB_GN(j) of this warp inside the tile: see compute_stage
+    const int wm = warp / Cfg::WARPS_N, wn = warp % Cfg::WARPS_N;      // contiguous WM x WN warp tiles
     const int lr = lane >> 2, lc = lane & 3;
     const int64_t total_tiles = T.tile_start[T.nblocks];
 
@@ -363,16 +322,7 @@ grouped_gemm_kernel(const double* __restrict__ A, const double* __restrict__ B, 
         const int64_t local = tile - T.tile_start[lo];
         const int64_t m0 = (local / tiles_n) * BM, n0 = (local % tiles_n) * BN;
         const int64_t p_begin = T.out_pair_ptr[blk], p_end = T.out_pair_ptr[blk + 1];
-        // number of this warp's row / column groups inside the block (a prefix of its interleaved list)
-        const int64_t mg = (min((int64_t)BM, M - m0) + 7) / 8, ng = (min((int64_t)BN, N - n0) + 7) / 8;
-        const int mi_cnt = !Cfg::SKIP ? MI : Cfg::IL ? (int)max((int64_t)0, (mg - wm + Cfg::WARPS_M - 1) / Cfg::WARPS_M)
-                                                     : (int)min((int64_t)MI, max((int64_t)0, mg - wm * MI));
-        const int nj_cnt = !Cfg::SKIP ? NI : Cfg::IL ? (int)max((int64_t)0, (ng - wn + Cfg::WARPS_N - 1) / Cfg::WARPS_N)
-                                                     : (int)min((int64_t)NI, max((int64_t)0, ng - wn * NI));
-        const bool full_tile = (mi_cnt == MI) && (nj_cnt == NI);
-        // WSKIP: rows [wm WM, +WM) x columns [wn WN, +WN) of the tile against the block edge
-        const bool warp_live = !Cfg::WSKIP || ((int64_t)wm * Cfg::WM < M - m0 && (int64_t)wn * Cfg::WN < N - n0);
-        // WSKIP: 8 x 8 groups of this warp inside the block (contiguous warp tiles)
+        // 8 x 8 groups of this warp inside the block
         const int rem_m = (int)min((int64_t)BM, M - m0) - wm * Cfg::WM, rem_n = (int)min((int64_t)BN, N - n0) - wn * Cfg::WN;
         const int mi_eff = rem_m <= 0 ? 0 : min(MI, (rem_m + 7) >> 3), nj_eff = rem_n <= 0 ? 0 : min(NI, (rem_n + 7) >> 3);
         int64_t n_iters = 0;
@@ -437,20 +387,16 @@ grouped_gemm_kernel(const double* __restrict__ A, const double* __restrict__ B, 
             stage_ld = stage_ld + 1 == STAGES ? 0 : stage_ld + 1;
             const double* tA = sA + (size_t)stage * Cfg::A_STAGE;
             const double* tB = sB + (size_t)stage * Cfg::B_STAGE;
-            // the full / ragged decision is hoisted out of the unrolled k-steps: one basic block per stage,
-            // so the fragment loads of the next k-step are scheduled between the DMMAs of the current one
-            if constexpr (Cfg::WSKIP) {
-                if (mi_eff == MI && nj_eff == NI) compute_stage<Cfg, true>(tA, tB, acc, wm, wn, lr, lc, mi_cnt, nj_cnt);
-                else if (warp_live) {
-                    switch (mi_eff) {
-                    case 1: compute_stage_edge_n<Cfg, 1>(tA, tB, acc, wm, wn, lr, lc, nj_eff); break;
-                    case 2: compute_stage_edge_n<Cfg, 2>(tA, tB, acc, wm, wn, lr, lc, nj_eff); break;
-                    case 3: compute_stage_edge_n<Cfg, 3>(tA, tB, acc, wm, wn, lr, lc, nj_eff); break;
-                    default: compute_stage_edge_n<Cfg, 4>(tA, tB, acc, wm, wn, lr, lc, nj_eff); break;
-                    }
-                }
-            } else if (full_tile) compute_stage<Cfg, true>(tA, tB, acc, wm, wn, lr, lc, mi_cnt, nj_cnt);
-            else compute_stage<Cfg, false>(tA, tB, acc, wm, wn, lr, lc, mi_cnt, nj_cnt);
+            // the number of live groups is hoisted out of the unrolled k-steps: one uniform switch per stage, every variant
+            // free of predicates, so the fragment loads of the next k-step are scheduled between the DMMAs of the current one
+            if (mi_eff == MI && nj_eff == NI) compute_stage_edge<Cfg, MI, NI>(tA, tB, acc, wm, wn, lr, lc);     // the common case first
+            else switch (mi_eff) {
+            case 0: break;
+            case 1: compute_stage_edge_n<Cfg, 1>(tA, tB, acc, wm, wn, lr, lc, nj_eff); break;
+            case 2: compute_stage_edge_n<Cfg, 2>(tA, tB, acc, wm, wn, lr, lc, nj_eff); break;
+            case 3: compute_stage_edge_n<Cfg, 3>(tA, tB, acc, wm, wn, lr, lc, nj_eff); break;
+            default: compute_stage_edge_n<Cfg, 4>(tA, tB, acc, wm, wn, lr, lc, nj_eff); break;
+            }
         }
         cp_async_wait<0>();
 
@@ -458,11 +404,11 @@ grouped_gemm_kernel(const double* __restrict__ A, const double* __restrict__ B, 
         double* Cb = C + T.out_off[blk] * ES;
 #pragma unroll
         for (int i = 0; i < MI; ++i) {
-            const int64_t r = m0 + CYB_GM(i) * 8 + lr;
+            const int64_t r = m0 + (wm * MI + i) * 8 + lr;
             if (r >= M) continue;
 #pragma unroll
             for (int j = 0; j < NI; ++j) {
-                const int64_t c = n0 + CYB_GN(j) * 8 + lc * 2;
+                const int64_t c = n0 + (wn * NI + j) * 8 + lc * 2;
                 if (!CPLX) {
                     double* p = Cb + r * N + c;
                     if (c + 1 < N && ((N & 1) == 0)) {
@@ -825,9 +771,9 @@ __global__ void __launch_bounds__(SK_THREADS, 3) skinny_gemm_kernel(const double
 #endif
 #define CYB_GEMM_R CYB_GEMM_BM, CYB_GEMM_BN, CYB_GEMM_BK, CYB_GEMM_BM / 32, CYB_GEMM_BN / 32, CYB_GEMM_STAGES
 #define CYB_GEMM_R_MINB CYB_GEMM_MINB
-using CfgR0 = GemmCfg<false, CYB_GEMM_R, false, false, false, CYB_GEMM_R_MINB>;
-using CfgR = GemmCfg<false, CYB_GEMM_R, false, false, false, CYB_GEMM_R_MINB, true>;     // + warp-tile edge skipping
-using CfgC = GemmCfg<true, 128, 64, 8, 4, 2, 4>;      // 8 warps, 4 x 4 interleaved groups per warp, complex
+using CfgR = GemmCfg<false, CYB_GEMM_R, CYB_GEMM_R_MINB>;
+// complex128: 128 x 64 tiles, 8 warps, one CTA per SM (24.8 TFLOP/s real-equivalent on the chi = 8192 Hubbard tdot, 0.70 of the peak)
+using CfgC = GemmCfg<true, 128, 64, 8, 4, 2, 4>;
 
 template <class Cfg>
 static int launch_gemm(const void* a, const void* b, void* c, GemmTables T, cudaStream_t stream)
@@ -931,8 +877,7 @@ int cyb_grouped_gemm_run(const void* a, const void* b, void* c, int dtype, const
             CYB_LAUNCH_CHECK();
         }
         if (!run_mma) return CYB_OK;
-        static const bool wskip = !(getenv("CYB_GEMM_WSKIP") && atoi(getenv("CYB_GEMM_WSKIP")) == 0);
-        return wskip ? launch_gemm<CfgR>(a, b, c, T[0], stream) : launch_gemm<CfgR0>(a, b, c, T[0], stream);
+        return launch_gemm<CfgR>(a, b, c, T[0], stream);
     }
     if (run_sk) {
         skinny_gemm_kernel<true><<<sk_grid, SK_THREADS, SK_SMEM_RING, stream>>>(A, B, C, T[1]);
