@@ -20,7 +20,8 @@ def leg_from_reference(leg, symmetry: AbelianSymmetry):
     if sub is not None and hasattr(leg, "combine_cstyle"):
         return AbelianLegPipe([leg_from_reference(l, symmetry) for l in sub], is_dual=bool(leg.is_dual),
                               combine_cstyle=bool(leg.combine_cstyle))
-    ds = np.asarray(leg.defining_sectors, dtype=np.int64).reshape(int(leg.num_sectors), -1)
+    ds = leg.defining_sectors
+    ds = np.asarray(ds.to_numpy() if hasattr(ds, "to_numpy") else ds, dtype=np.int64).reshape(int(leg.num_sectors), -1)
     return ElementarySpace(symmetry, ds, np.asarray(leg.multiplicities, dtype=np.int64), bool(leg.is_dual))
 
 

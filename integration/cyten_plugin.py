@@ -57,6 +57,12 @@ _HOT_DTYPES = {cyten.Dtype.float64: "float64", cyten.Dtype.complex128: "complex1
 _REF_DTYPES = {"float64": cyten.Dtype.float64, "complex128": cyten.Dtype.complex128}
 
 
+def _sector_table(sa):
+    """``SectorArray`` -> numpy.  ``SectorArray.to_numpy()`` hands out the table in ~1 us; ``np.asarray(SectorArray)`` walks the
+    sequence protocol element by element (~350 us for 13 sectors -- that was most of the plugin's per-call overhead)."""
+    return sa.to_numpy() if hasattr(sa, "to_numpy") else np.asarray(sa)
+
+
 class _NotHot(Exception):
     """The operands are outside what the kernels cover (dtype, symmetry, tensor class): use the inner backend."""
 
@@ -138,7 +144,7 @@ class CytenB200Backend(TensorBackend):
             return m
         if not hasattr(leg, "defining_sectors"):
             raise _NotHot("leg type")
-        ds = np.ascontiguousarray(np.asarray(leg.defining_sectors, dtype=np.int64).reshape(int(leg.num_sectors), -1))
+        ds = np.ascontiguousarray(np.asarray(_sector_table(leg.defining_sectors), dtype=np.int64).reshape(int(leg.num_sectors), -1))
         mu = np.ascontiguousarray(np.asarray(leg.multiplicities, dtype=np.int64))
         key = (id(sym), bool(leg.is_dual), ds.tobytes(), mu.tobytes())
         m = self._leg_cache.get(key)
@@ -159,20 +165,25 @@ class CytenB200Backend(TensorBackend):
         dtype = _HOT_DTYPES.get(ref_data.dtype)
         if dtype is None:
             raise _NotHot("dtype")
-        blocks = ref_data.blocks
-        n = len(blocks)
-        bi = np.ascontiguousarray(np.asarray(ref_data.block_inds.to_numpy(), dtype=np.int64).reshape(n, nlegs))
+        bi = np.asarray(ref_data.block_inds.to_numpy(), dtype=np.int64)
+        n = bi.shape[0] if bi.ndim == 2 else bi.size // max(nlegs, 1)
+        bi = np.ascontiguousarray(bi.reshape(n, nlegs))
         if n == 0:
             return Arena.empty(dtype, self.fast.device, bi, np.zeros((0, nlegs), np.int64))
+        if not _STRICT:
+            # A complete, ordered arena is recognised from its first and last block (O(1); CYTEN_B200_STRICT=1 checks every
+            # block).  `ref_data.blocks` converts the whole vector<Block> into Python objects (~1 us per block, several
+            # hundred blocks per intermediate of the effective Hamiltonian): the two blocks are fetched by their index rows.
+            first = unwrap_block(ref_data.get_block(bi[0]))
+            owner = first.owner
+            if owner is not None and first.index == 0 and owner.num_blocks == n and owner.dtype == dtype:
+                last = first if n == 1 else unwrap_block(ref_data.get_block(bi[n - 1]))
+                if (last.owner is owner and last.index == n - 1 and owner.block_inds.shape == bi.shape
+                        and np.array_equal(owner.block_inds, bi)):
+                    return owner
+        blocks = ref_data.blocks
         first = unwrap_block(blocks[0])
         owner = first.owner
-        if owner is not None and first.index == 0 and owner.num_blocks == n and owner.dtype == dtype and not _STRICT:
-            # a complete, ordered arena: the last block closes the bracket (O(1) instead of one unwrap per block;
-            # CYTEN_B200_STRICT=1 checks every block)
-            last = first if n == 1 else unwrap_block(blocks[-1])
-            if (last.owner is owner and last.index == n - 1 and owner.block_inds.shape == bi.shape
-                    and np.array_equal(owner.block_inds, bi)):
-                return owner
         wrapped = [unwrap_block(b) for b in blocks]
         if (owner is not None and owner.num_blocks == n and owner.dtype == dtype
                 and all(w.owner is owner and w.index == i for i, w in enumerate(wrapped))):
@@ -347,7 +358,7 @@ class CytenB200Backend(TensorBackend):
         keep = np.asarray(keep, dtype=bool)
         keep_dev = torch.from_numpy(keep).to(self.fast.device) if len(keep) else torch.zeros(0, dtype=torch.bool)
         slices = np.asarray(large_leg.slices).reshape(-1, 2)
-        defining = np.asarray(large_leg.defining_sectors, dtype=np.int64).reshape(len(slices), -1)
+        defining = np.asarray(_sector_table(large_leg.defining_sectors), dtype=np.int64).reshape(len(slices), -1)
         perm = large_leg._basis_perm
         perm = None if perm is None else np.asarray(large_leg.basis_perm)
         blocks, rows, sectors, mults, ranks = [], [], [], [], []
