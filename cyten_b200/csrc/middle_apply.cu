@@ -39,11 +39,14 @@ middle_apply_kernel(const double* __restrict__ in, double* __restrict__ out, con
     // contiguous ranges of units per CTA: consecutive units share their group, whose tables are staged once
     const int64_t per = (nwork + gridDim.x - 1) / gridDim.x;
     const int64_t u0 = (int64_t)blockIdx.x * per, u1 = u0 + per < nwork ? u0 + per : nwork;
+    // (a, chunk) of the current unit are carried from unit to unit: the 64-bit divide / modulo per unit and thread that
+    // used to find them, with the index arithmetic around it, made this HBM-bound kernel issue-bound (ncu: 60 % issue
+    // slots active at 3.2 TB/s)
+    int64_t cur_end = 0, a = 0;
+    int nin = 0, nout = 0, nb = 0, chunks = 1, chunk = 0;
     for (int64_t u = u0; u < u1; ++u) {
-        int64_t lo = cur >= 0 ? cur : 0;
-        if (cur < 0 || u >= work0[cur + 1]) {
-            int64_t hi = ngroups;
-            lo = cur >= 0 ? cur : 0;
+        if (cur < 0 || u >= cur_end) {
+            int64_t lo = cur >= 0 ? cur : 0, hi = ngroups;
             while (hi - lo > 1) {
                 const int64_t mid = (lo + hi) >> 1;
                 if (work0[mid] <= u) lo = mid; else hi = mid;
@@ -51,17 +54,18 @@ middle_apply_kernel(const double* __restrict__ in, double* __restrict__ out, con
             __syncthreads();                     // everybody is done with the previous group's tables
             if (tid == 0) s_g = groups[lo];
             __syncthreads();
-            const int nin = (int)s_g.nin, nout = (int)s_g.nout;
+            nin = (int)s_g.nin; nout = (int)s_g.nout; nb = (int)s_g.nb;
             for (int e = tid; e < nin * nout * ES; e += MID_THREADS) s_coef[e] = coef[s_g.coef0 * ES + e];
             for (int e = tid; e < 2 * (nin + nout); e += MID_THREADS) s_desc[e >> 1][e & 1] = desc[2 * s_g.desc0 + e];
             __syncthreads();
             cur = lo;
+            cur_end = work0[cur + 1];
+            chunks = (nb + MID_COLS - 1) / MID_COLS;
+            const int64_t local = u - work0[cur];
+            a = local / chunks;
+            chunk = (int)(local - a * chunks);
         }
-        const int nin = (int)s_g.nin, nout = (int)s_g.nout;
-        const int64_t nb = s_g.nb;
-        const int64_t chunks = (nb + MID_COLS - 1) / MID_COLS;
-        const int64_t local = u - work0[cur];
-        const int64_t a = local / chunks, b0 = (local % chunks) * MID_COLS + tid, b1 = b0 + MID_THREADS;
+        const int b0 = chunk * MID_COLS + tid, b1 = b0 + MID_THREADS;
         const bool ok0 = b0 < nb, ok1 = b1 < nb;
         if (!CPLX) {
             double x0[MAXR], x1[MAXR];
@@ -110,6 +114,7 @@ middle_apply_kernel(const double* __restrict__ in, double* __restrict__ out, con
                 if (ok1) __stcs(q + b1, y1);
             }
         }
+        if (++chunk == chunks) { chunk = 0; ++a; }
     }
 }
 
