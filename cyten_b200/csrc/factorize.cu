@@ -9,7 +9,9 @@
 //           Replaces block_backend->matrix_svd per sector (abelian.cpp:3517; numpy.cpp:1247-1297,
 //           scipy.linalg.svd gesdd).  Singular values come out with Jacobi's high relative accuracy.
 //  * EIGH : the same kernel on W_0 = H + sigma*I (sigma = 1.5*||H||_F, positive definite), whose
-//           left/right singular vectors coincide with the eigenvectors; lambda = S - sigma.
+//           left/right singular vectors coincide with the eigenvectors; lambda = S - sigma.  The eigenvectors are
+//           read off the normalised rows of W_final (W_0^H W_0 = Vhat^H S^2 Vhat), so the left factor Z is neither
+//           initialised nor updated: half of the row updates of a sweep.
 //           Replaces block_backend->eigh (abelian.cpp:1781; numpy.cpp:658-680 np.linalg.eigh).
 //  * QR   : blocked Householder QR (compact WY, panels of QR_NB reflectors) on the transposed copy (columns of
 //           A become contiguous rows): the panel is factored in shared memory by CTA 0 of the team, every
@@ -179,7 +181,8 @@ jacobi_svd_kernel(const void* __restrict__ a_, void* __restrict__ o0_, double* _
         for (int64_t e = gtid; e < r * c; e += gthreads) E::stcg(&W[e], A[e]);
     }
     if (PH & PH_INIT) {
-        for (int64_t e = gtid; e < r * r; e += gthreads) E::stcg(&Z[e], (e / r == e % r) ? E::one() : E::zero());
+        if (!EIGH)
+            for (int64_t e = gtid; e < r * r; e += gthreads) E::stcg(&Z[e], (e / r == e % r) ? E::one() : E::zero());
         for (int64_t e = gtid; e < FZ_MAX_SWEEPS + 1; e += gthreads) rot_count[e] = 0ull;
         if (gtid == 0) __stcg(&misc[2], sigma);
     }
@@ -228,12 +231,14 @@ jacobi_svd_kernel(const void* __restrict__ a_, void* __restrict__ o0_, double* _
                     E::stcg(x + q, E::sub(E::scale(xv, cs), E::scale(yv, sn)));
                     E::stcg(y + q, E::add(E::scale(xv, sn), E::scale(yv, cs)));
                 }
-                T* zx = Z + i * r;
-                T* zy = Z + j * r;
-                for (int64_t q = lane; q < r; q += 32) {
-                    const T xv = E::ldcg(zx + q), yv = E::mul(phase, E::ldcg(zy + q));
-                    E::stcg(zx + q, E::sub(E::scale(xv, cs), E::scale(yv, sn)));
-                    E::stcg(zy + q, E::add(E::scale(xv, sn), E::scale(yv, cs)));
+                if (!EIGH) {
+                    T* zx = Z + i * r;
+                    T* zy = Z + j * r;
+                    for (int64_t q = lane; q < r; q += 32) {
+                        const T xv = E::ldcg(zx + q), yv = E::mul(phase, E::ldcg(zy + q));
+                        E::stcg(zx + q, E::sub(E::scale(xv, cs), E::scale(yv, sn)));
+                        E::stcg(zy + q, E::add(E::scale(xv, sn), E::scale(yv, cs)));
+                    }
                 }
                 ++my_rot;
             }
@@ -354,12 +359,12 @@ jacobi_svd_kernel(const void* __restrict__ a_, void* __restrict__ o0_, double* _
 
     // ---- outputs ----
     if (EIGH) {
-        // w (ascending) and V[j][p] = conj(Z[i][j]) with p = pos[i]
+        // w (ascending) and V[j][p] = conj(Vhat[i][j]) with p = pos[i] (Vhat = the normalised rows of W, c == r)
         T* V = static_cast<T*>(o2_) + D.o2_off;
         for (int64_t i = gtid; i < r; i += gthreads) s_out[D.o1_off + __ldcg(&pos[i])] = __ldcg(&S_raw[i]) - sigma;
         for (int64_t e = gtid; e < r * r; e += gthreads) {
             const int64_t j = e / r, i = e % r;   // consecutive threads -> consecutive i (scattered columns)
-            V[j * r + __ldcg(&pos[i])] = E::conj(E::ldcg(Z + i * r + j));
+            V[j * r + __ldcg(&pos[i])] = E::conj(E::ldcg(W + i * c + j));
         }
     } else {
         T* U = static_cast<T*>(o0_) + D.o0_off;
@@ -821,7 +826,7 @@ struct BjRounds {
 
 // items over the blocks [kb[mat], nb) of every listed matrix
 static void bj_build_rounds(BjRounds& R, const std::vector<FzDesc>& descs, const std::vector<int64_t>& mats,
-                            const std::vector<int>& rowbase, const std::vector<int>& first_block, int cm)
+                            const std::vector<int>& rowbase, const std::vector<int>& first_block, int cm, bool with_z)
 {
     R.rounds.assign(1, {});
     for (size_t q = 0; q < mats.size(); ++q) {
@@ -870,7 +875,8 @@ static void bj_build_rounds(BjRounds& R, const std::vector<FzDesc>& descs, const
             for (int32_t sl = 0; sl < nsl; ++sl) R.gworks.push_back(BjWork{(int32_t)idx, sl});
             w += nsl;
             for (int32_t ch = 0; ch < (int32_t)((D.c * cm + BJ_AC - 1) / BJ_AC); ++ch) R.aworks.push_back(BjWork{(int32_t)idx, ch});
-            for (int32_t ch = 0; ch < (int32_t)((D.r * cm + BJ_AC - 1) / BJ_AC); ++ch) R.aworks.push_back(BjWork{(int32_t)idx, (1 << 24) | ch});
+            if (with_z)          // eigh reads its eigenvectors off W: the accumulated left factor is not needed
+                for (int32_t ch = 0; ch < (int32_t)((D.r * cm + BJ_AC - 1) / BJ_AC); ++ch) R.aworks.push_back(BjWork{(int32_t)idx, (1 << 24) | ch});
         }
         R.max_items = std::max(R.max_items, rd.size());
         R.max_gworks = std::max(R.max_gworks, (size_t)w);
@@ -939,7 +945,7 @@ static int run_block_jacobi(const void* a, void* o0, double* s_out, void* o2, vo
     BjRounds R1[MAXG], R2[MAXG];
     size_t max_flat = 1, max_gw = 1, max_aw = 1, max_items = 1, max_gworks = 1;
     for (int g = 0; g < NG; ++g) {
-        bj_build_rounds(R1[g], descs, gmats[g], growbase[g], std::vector<int>(gmats[g].size(), 0), CM);
+        bj_build_rounds(R1[g], descs, gmats[g], growbase[g], std::vector<int>(gmats[g].size(), 0), CM, !EIGH);
         max_flat = std::max(max_flat, R1[g].flat.size()); max_gw = std::max(max_gw, R1[g].gworks.size());
         max_aw = std::max(max_aw, R1[g].aworks.size()); max_items = std::max(max_items, R1[g].max_items);
         max_gworks = std::max(max_gworks, R1[g].max_gworks);
@@ -1091,7 +1097,7 @@ static int run_block_jacobi(const void* a, void* o0, double* s_out, void* o2, vo
                 active[(size_t)mat] = nn > 1;
                 first_block[q] = nn > 1 ? (int)((r - nn) / BJ_B) : (int)((r + BJ_B - 1) / BJ_B);
             }
-            bj_build_rounds(R2[g], descs, gmats[g], growbase[g], first_block, CM);
+            bj_build_rounds(R2[g], descs, gmats[g], growbase[g], first_block, CM, !EIGH);
         }
         rc = run_sweeps(R2, false);
         if (rc != CYB_OK) return rc;
