@@ -365,6 +365,15 @@ def test_batched_eigh(lib, dtype):
         Hm = A + A.conj().T
         if n == 33:
             Hm = Hm * 0 + np.diag(np.repeat([1.0, -1.0, 2.0], 11)).astype(dtype)   # degenerate +-lambda
+        if n in (193, 300):
+            # block-Jacobi path (the eigenvectors are read off the working copy, not off an accumulated factor):
+            # n = 193: three eigenvalues of multiplicity 64 / 64 / 65 in a random basis; n = 300: a graded spectrum
+            # 1 ... 1e-14 with random signs (the shift by 1.5 ||H||_F must keep every eigenvalue to 1e-12 ||H||)
+            Qm, _ = np.linalg.qr(A)
+            ev = (np.repeat([1.0, -1.0, 2.0], 65)[:n] if n == 193
+                  else np.logspace(0, -14, n) * rng.choice([-1.0, 1.0], size=n))
+            Hm = (Qm * ev) @ Qm.conj().T
+            Hm = 0.5 * (Hm + Hm.conj().T)
         mats.append(np.ascontiguousarray(Hm))
     a, aoff = _pack(mats, dtype)
     w, woff = _pack([np.zeros(n) for n in ns], np.float64)
