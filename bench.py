@@ -446,6 +446,8 @@ def run_b200(args):
         return SH.matvec(t) if world > 1 else H.matvec(t)
 
     def local_chain(t):      # the part of a step without a collective: what a CUDA graph captures
+        # (the all_reduce as a node of the same graph was measured on 2 B200: 1.105 ms against 1.103 ms, and the process group
+        #  did not shut down cleanly afterwards -- the collective stays an eager launch between the replays)
         return SH.matvec_local(t) if world > 1 else H.matvec(t)
     captured = {}
 
@@ -541,8 +543,11 @@ def run_b200(args):
         y_sh = step()
         y_un = sh.expand_to_full(H.matvec(theta_full))
         same_blocks = bool(np.array_equal(y_sh.data.block_inds, y_un.data.block_inds))
-        scale = float(y_un.data.buf.abs().max())
-        diff = float((y_sh.data.buf - y_un.data.buf).abs().max()) if same_blocks else float("inf")
+        # block by block: the padding between blocks is not part of the tensor (and not zeroed when a result is complete already)
+        nblk = y_un.data.num_blocks if same_blocks else 0
+        scale = max((float(y_un.data.block(i).abs().max()) for i in range(nblk)), default=0.0)
+        diff = (max((float((y_sh.data.block(i) - y_un.data.block(i)).abs().max()) for i in range(nblk)), default=0.0)
+                if same_blocks else float("inf"))
         worst = total_over_ranks(diff / scale if scale > 0 else diff, dist.ReduceOp.MAX)
         sharded_check = {"max_abs_diff_over_max_abs": worst, "tolerance": 1e-12, "ok": bool(same_blocks and worst <= 1e-12),
                          "what": "graph-replayed sharded step (all ranks reduced) vs the unsharded fused operator, every element"}
