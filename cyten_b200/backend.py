@@ -107,7 +107,15 @@ class B200AbelianBackend(Blas1Mixin):
     # ------------------------------------------------------------------------------------------
     # small device-bookkeeping wrappers (a1)
     # ------------------------------------------------------------------------------------------
+    # entry points that only read / write integer tables (the plan-only mode may run them)
+    _TABLE_ONLY = frozenset(("cyb_lexsort_rows", "cyb_row_differences", "cyb_pack_rows", "cyb_take_rows", "cyb_common_sorted",
+                             "cyb_fuse_charges", "cyb_compose_plan", "cyb_copy_blocks_prepare", "cyb_grouped_gemm_prepare"))
+
     def _call(self, name, *args):
+        if self.dry_run and name not in self._TABLE_ONLY:
+            # arenas are 16-element dummies in plan-only mode: a kernel on them would read / write out of bounds
+            raise _lib.CytenB200Error(f"{name}: not available in plan-only mode (dry_run covers permute_legs / combine_legs / "
+                                      "split_legs / compose and their bookkeeping, not factorisations or reductions)")
         self.launches += 1
         self._lib_call(name, *args)
 

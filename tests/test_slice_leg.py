@@ -72,3 +72,22 @@ def test_valid_block_inds_join_equals_brute_force():
     want = want[np.lexsort(want.T)]
     assert len(bi) > 100 and np.array_equal(bi, want)
     assert valid_block_inds(TensorProduct([p]), TensorProduct([v], symmetry=sym)).shape[1] == 2
+
+
+def test_plan_only_mode_refuses_arena_kernels(backend):
+    """``dry_run`` arenas are 16-element dummies: an operation that would launch a kernel on them must raise, not fault."""
+    import pytest
+    from cyten_b200 import tensors as ct
+    from cyten_b200._lib import CytenB200Error
+    from cyten_b200.workloads import mps_tensor, u1_bond_leg, u1_phys_leg
+    v, p = u1_bond_leg(24, 2, 1.0), u1_phys_leg()
+    A = mps_tensor(v, p, v, backend, seed=1)
+    backend.dry_run = True
+    try:
+        th = ct.tdot(A, A, [2], [0])                       # bookkeeping only: fine
+        assert th.data.num_blocks > 0
+        with pytest.raises(CytenB200Error, match="plan-only"):
+            ct.svd(th)
+    finally:
+        backend.dry_run = False
+    assert float(ct.norm(ct.tdot(A, A, [2], [0]))) > 0     # the backend is usable again
