@@ -717,6 +717,27 @@ class B200AbelianBackend(Blas1Mixin):
         inv[order] = np.arange(len(order))
         return self._empty(dtype, self.device, block_inds[order], shapes[order]), inv
 
+    def _fz_out(self, dtype, block_inds, shapes, eye_rows=()):
+        """Plan entry for one output of a factorisation: the lexsorted structure (``_sorted_data``), the position of every
+        input row in it and the device tables of the blocks that are identity slices (absent sectors)."""
+        data, pos = self._sorted_data(dtype, block_inds, shapes)
+        eye = pos[np.asarray(eye_rows, dtype=np.int64)] if len(eye_rows) else np.zeros(0, np.int64)
+        ent = dict(bi=data.block_inds, shapes=data.shapes, sig=data.sig, pos=pos, offsets=data.offsets, neye=len(eye), eye=None)
+        if len(eye) and not self.dry_run:
+            with self._ctx():
+                ent["eye"] = (to_device_i64(data.shapes[eye], self.device), to_device_i64(data.offsets[eye], self.device))
+        return ent
+
+    def _fz_new(self, dtype, ent) -> AbelianBackendData:
+        """A fresh arena with the cached structure; identity slices written by one launch from cached device tables."""
+        data = self._empty(dtype, self.device, ent["bi"], ent["shapes"])
+        data._sig = ent["sig"]
+        if ent["neye"] and not self.dry_run:
+            with self._ctx():
+                self._call("cyb_fill_eye", ptr(data.buf), ptr(ent["eye"][0]), ptr(ent["eye"][1]), ent["neye"], data.cyb_dtype,
+                           self._stream())
+        return data
+
     def _fill_eye(self, data: AbelianBackendData, which):
         which = np.asarray(which, dtype=np.int64)
         if len(which) == 0 or self.dry_run:
@@ -734,37 +755,45 @@ class B200AbelianBackend(Blas1Mixin):
         other sectors are left to their owners (no block here)."""
         A: AbelianBackendData = a.data
         new_leg = new_co_domain.factors[0]
-        cod0, dom0 = a.codomain.factors[0], a.domain.factors[0]
-        rows = self._matched_sectors(a, new_leg)
-        if only_rows is not None:
-            rows = [rows[t] for t in only_rows]
-        u_bi = [(j, n) for j, n, k, i in rows]
-        vh_bi = [(n, k) for j, n, k, i in rows]
-        u_shapes = [(cod0.multiplicities[j], new_leg.multiplicities[n]) for j, n, k, i in rows]
-        vh_shapes = [(new_leg.multiplicities[n], dom0.multiplicities[k]) for j, n, k, i in rows]
-        present = [t for t, r in enumerate(rows) if r[3] >= 0]
-        s_bi = [(rows[t][1], rows[t][1]) for t in present]
-        s_shapes = [(new_leg.multiplicities[rows[t][1]],) for t in present]
-        U, u_pos = self._sorted_data(A.dtype, np.asarray(u_bi).reshape(-1, 2), np.asarray(u_shapes).reshape(-1, 2))
-        Vh, vh_pos = self._sorted_data(A.dtype, np.asarray(vh_bi).reshape(-1, 2), np.asarray(vh_shapes).reshape(-1, 2))
-        S, s_pos = self._sorted_data("float64", np.asarray(s_bi).reshape(-1, 2), np.asarray(s_shapes).reshape(-1, 1))
-        S.block_inds = np.asarray(S.block_inds).reshape(-1, 2)
-        absent = [t for t, r in enumerate(rows) if r[3] < 0]
-        self._fill_eye(U, u_pos[absent])
-        self._fill_eye(Vh, vh_pos[absent])
-        info = None
-        if present:
+        # The sector walk, the three output structures (three device lexsorts with a read-back each), the identity-slice
+        # tables and the descriptor table depend on the STRUCTURE of ``a`` only: a cached plan like every other operation
+        # (the host bookkeeping was 1-4 ms of every svd / qr call).
+        key = ("svd", A.sig, a.codomain.sig, a.domain.sig, new_leg.sig, None if only_rows is None else tuple(int(t) for t in only_rows))
+        plan = self._plan_get(key)
+        if plan is None:
+            cod0, dom0 = a.codomain.factors[0], a.domain.factors[0]
+            rows = self._matched_sectors(a, new_leg)
+            if only_rows is not None:
+                rows = [rows[t] for t in only_rows]
+            u_bi = [(j, n) for j, n, k, i in rows]
+            vh_bi = [(n, k) for j, n, k, i in rows]
+            u_shapes = [(cod0.multiplicities[j], new_leg.multiplicities[n]) for j, n, k, i in rows]
+            vh_shapes = [(new_leg.multiplicities[n], dom0.multiplicities[k]) for j, n, k, i in rows]
+            present = [t for t, r in enumerate(rows) if r[3] >= 0]
+            absent = [t for t, r in enumerate(rows) if r[3] < 0]
+            s_bi = [(rows[t][1], rows[t][1]) for t in present]
+            s_shapes = [(new_leg.multiplicities[rows[t][1]],) for t in present]
+            pu = self._fz_out(A.dtype, np.asarray(u_bi).reshape(-1, 2), np.asarray(u_shapes).reshape(-1, 2), absent)
+            pv = self._fz_out(A.dtype, np.asarray(vh_bi).reshape(-1, 2), np.asarray(vh_shapes).reshape(-1, 2), absent)
+            ps = self._fz_out("float64", np.asarray(s_bi).reshape(-1, 2), np.asarray(s_shapes).reshape(-1, 1))
+            ps["bi"] = np.asarray(ps["bi"]).reshape(-1, 2)
             desc = np.zeros((len(present), 6), dtype=np.int64)
             for q, t in enumerate(present):
                 i = rows[t][3]
                 m, n = A.shapes[i]
-                if min(m, n) != S.shapes[s_pos[q], 0]:
+                if min(m, n) != ps["shapes"][ps["pos"][q], 0]:
                     raise _lib.CytenB200Error("svd: new leg multiplicity != min(m, n)")
-                desc[q] = (m, n, A.offsets[i], U.offsets[u_pos[t]], S.offsets[s_pos[q]], Vh.offsets[vh_pos[t]])
+                desc[q] = (m, n, A.offsets[i], pu["offsets"][pu["pos"][t]], ps["offsets"][ps["pos"][q]], pv["offsets"][pv["pos"][t]])
+            plan = self._plan_put(key, dict(U=pu, Vh=pv, S=ps, desc=desc))
+        U, Vh, S = self._fz_new(A.dtype, plan["U"]), self._fz_new(A.dtype, plan["Vh"]), self._fz_new("float64", plan["S"])
+        S.block_inds = plan["S"]["bi"]
+        desc = plan["desc"]
+        info = None
+        if len(desc):
             with self._ctx():
-                info = torch.zeros(len(present), dtype=torch.int64, device=self.device)
+                info = torch.zeros(len(desc), dtype=torch.int64, device=self.device)
                 self._call("cyb_batched_svd", ptr(A.buf), ptr(U.buf), ptr(S.buf), ptr(Vh.buf),
-                           desc.ctypes.data_as(C.c_void_p), len(present), A.cyb_dtype, ptr(info), self._stream())
+                           desc.ctypes.data_as(C.c_void_p), len(desc), A.cyb_dtype, ptr(info), self._stream())
         self.last_info = info
         self._check_converged(info, "svd")
         return U, S, Vh
@@ -774,26 +803,31 @@ class B200AbelianBackend(Blas1Mixin):
         absent sectors, no R block there."""
         A: AbelianBackendData = a.data
         new_leg = new_co_domain.factors[0]
-        cod0, dom0 = a.codomain.factors[0], a.domain.factors[0]
-        rows = self._matched_sectors(a, new_leg)
-        present = [t for t, r in enumerate(rows) if r[3] >= 0]
-        absent = [t for t, r in enumerate(rows) if r[3] < 0]
-        q_bi = np.asarray([(j, n) for j, n, k, i in rows]).reshape(-1, 2)
-        q_shapes = np.asarray([(cod0.multiplicities[j], new_leg.multiplicities[n]) for j, n, k, i in rows]).reshape(-1, 2)
-        r_bi = np.asarray([(rows[t][1], rows[t][2]) for t in present]).reshape(-1, 2)
-        r_shapes = np.asarray([(new_leg.multiplicities[rows[t][1]], dom0.multiplicities[rows[t][2]]) for t in present]).reshape(-1, 2)
-        Q, q_pos = self._sorted_data(A.dtype, q_bi, q_shapes)
-        R, r_pos = self._sorted_data(A.dtype, r_bi, r_shapes)
-        self._fill_eye(Q, q_pos[absent])
-        if present:
+        key = ("qr", A.sig, a.codomain.sig, a.domain.sig, new_leg.sig)
+        plan = self._plan_get(key)
+        if plan is None:                    # structure-only bookkeeping, cached (see svd)
+            cod0, dom0 = a.codomain.factors[0], a.domain.factors[0]
+            rows = self._matched_sectors(a, new_leg)
+            present = [t for t, r in enumerate(rows) if r[3] >= 0]
+            absent = [t for t, r in enumerate(rows) if r[3] < 0]
+            q_bi = np.asarray([(j, n) for j, n, k, i in rows]).reshape(-1, 2)
+            q_shapes = np.asarray([(cod0.multiplicities[j], new_leg.multiplicities[n]) for j, n, k, i in rows]).reshape(-1, 2)
+            r_bi = np.asarray([(rows[t][1], rows[t][2]) for t in present]).reshape(-1, 2)
+            r_shapes = np.asarray([(new_leg.multiplicities[rows[t][1]], dom0.multiplicities[rows[t][2]]) for t in present]).reshape(-1, 2)
+            pq = self._fz_out(A.dtype, q_bi, q_shapes, absent)
+            pr = self._fz_out(A.dtype, r_bi, r_shapes)
             desc = np.zeros((len(present), 6), dtype=np.int64)
             for q, t in enumerate(present):
                 i = rows[t][3]
                 m, n = A.shapes[i]
-                desc[q] = (m, n, A.offsets[i], Q.offsets[q_pos[t]], R.offsets[r_pos[q]], 0)
+                desc[q] = (m, n, A.offsets[i], pq["offsets"][pq["pos"][t]], pr["offsets"][pr["pos"][q]], 0)
+            plan = self._plan_put(key, dict(Q=pq, R=pr, desc=desc))
+        Q, R = self._fz_new(A.dtype, plan["Q"]), self._fz_new(A.dtype, plan["R"])
+        desc = plan["desc"]
+        if len(desc):
             with self._ctx():
                 self._call("cyb_batched_qr", ptr(A.buf), ptr(Q.buf), ptr(R.buf),
-                           desc.ctypes.data_as(C.c_void_p), len(present), A.cyb_dtype, self._stream())
+                           desc.ctypes.data_as(C.c_void_p), len(desc), A.cyb_dtype, self._stream())
         return Q, R
 
     def eigh(self, a, new_leg_dual: bool, sort=None):
@@ -804,21 +838,27 @@ class B200AbelianBackend(Blas1Mixin):
         A: AbelianBackendData = a.data
         dom0 = a.domain.factors[0]
         new_leg = a.domain.as_ElementarySpace(new_leg_dual)
-        nsec = dom0.num_sectors
-        v_bi = np.stack([np.arange(nsec), np.arange(nsec)], axis=1).astype(np.int64)
-        v_shapes = np.stack([dom0.multiplicities, dom0.multiplicities], axis=1)
-        V = self._empty(A.dtype, self.device, v_bi, v_shapes)
-        w_shapes = A.shapes[:, :1]
-        W = self._empty("float64", self.device, A.block_inds, w_shapes)
-        has = np.zeros(nsec, dtype=bool)
-        has[A.block_inds[:, 0]] = True
-        self._fill_eye(V, np.nonzero(~has)[0])
-        info = None
-        if A.num_blocks:
+        key = ("eigh", A.sig, a.domain.sig)
+        plan = self._plan_get(key)
+        if plan is None:                    # structure-only bookkeeping, cached (see svd)
+            nsec = dom0.num_sectors
+            v_bi = np.stack([np.arange(nsec), np.arange(nsec)], axis=1).astype(np.int64)
+            v_shapes = np.stack([dom0.multiplicities, dom0.multiplicities], axis=1)
+            has = np.zeros(nsec, dtype=bool)
+            has[A.block_inds[:, 0]] = True
+            pv = self._fz_out(A.dtype, v_bi, v_shapes, np.nonzero(~has)[0])      # v_bi is sorted already: pos = identity
+            Wl = self._empty("float64", self.device, A.block_inds, A.shapes[:, :1])
             desc = np.zeros((A.num_blocks, 6), dtype=np.int64)
             for i in range(A.num_blocks):
                 m, n = A.shapes[i]
-                desc[i] = (m, n, A.offsets[i], 0, W.offsets[i], V.offsets[A.block_inds[i, 0]])
+                desc[i] = (m, n, A.offsets[i], 0, Wl.offsets[i], pv["offsets"][pv["pos"][A.block_inds[i, 0]]])
+            plan = self._plan_put(key, dict(V=pv, w_shapes=A.shapes[:, :1].copy(), w_sig=Wl.sig, desc=desc))
+        V = self._fz_new(A.dtype, plan["V"])
+        W = self._empty("float64", self.device, A.block_inds, plan["w_shapes"])
+        W._sig = plan["w_sig"]
+        desc = plan["desc"]
+        info = None
+        if A.num_blocks:
             with self._ctx():
                 info = torch.zeros(A.num_blocks, dtype=torch.int64, device=self.device)
                 self._call("cyb_batched_eigh", ptr(A.buf), ptr(W.buf), ptr(V.buf),
