@@ -15,7 +15,7 @@
 //      Gram matrix; if some pair fails, runs one cyclic pass of plane rotations over the item's pairs
 //      entirely in shared memory (32 disjoint rotations per step; G is updated two-sidedly, the product of
 //      the rotations is accumulated in Q),
-//   3. applies Q to the rows of W and of the accumulated transformation Z with DMMA GEMMs
+//   3. applies Q to the rows of W and (svd only: eigh reads its eigenvectors off W) of the accumulated transformation Z with DMMA GEMMs
 //      ([W_I; W_J] <- Q [W_I; W_J]), in place, 64 columns at a time.
 // The items of one round-robin round touch disjoint rows, so a round is one kernel launch over all
 // large sectors of the batch; a sweep = 1 launch for the within-block pairs + (#blocks - 1) launches
